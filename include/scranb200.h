@@ -1,0 +1,165 @@
+/* scranb200.h — C ABI of the B200-native marker-scoring path.
+ *
+ * This is the boundary a maintainer of the reference binds instead of the reference's own
+ * native routines (INTEGRATION.md shows the Rcpp-side stubs). Plain C: pointers, sizes, int
+ * status codes. Unless a parameter is marked DEVICE, every pointer is HOST memory owned by the
+ * caller; outputs are written into caller-allocated buffers and nothing allocated here is
+ * ever handed to the caller except the two opaque handles below.
+ *
+ * Every function returns 0 on success. On failure it returns non-zero and
+ * scranb200_last_error() (thread-local) describes the problem; messages that the reference's
+ * tests match are kept verbatim ("indices in 'groups' out of range").
+ *
+ * There is no CPU fallback: without a CUDA device every compute call fails.
+ *
+ * Citations are to /root/reference (scran 1.41.1).
+ */
+#ifndef SCRANB200_H
+#define SCRANB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct scranb200_ctx scranb200_ctx; /* one device, its stream and its scratch memory */
+typedef struct scranb200_mat scranb200_mat; /* a sparse genes x cells matrix resident in HBM  */
+
+#define SCRANB200_NA_INT INT32_MIN /* R's NA_integer_ (src/utils.h:8-10) */
+
+const char* scranb200_last_error(void);
+int scranb200_version(void);
+
+/* Context: binds CUDA device `device` (cudaSetDevice ordinal). Not shareable across fork(). */
+int scranb200_ctx_create(int device, scranb200_ctx** out);
+void scranb200_ctx_destroy(scranb200_ctx* ctx);
+/* Blocks until all work queued by this context has finished. */
+int scranb200_ctx_sync(scranb200_ctx* ctx);
+/* The cudaStream_t this context launches on, as an integer (for callers that own events). */
+uint64_t scranb200_ctx_stream(scranb200_ctx* ctx);
+/* Number of kernels launched by this context since creation (bench.py's gpu_launches). */
+int64_t scranb200_ctx_launches(scranb200_ctx* ctx);
+/* Device-time breakdown of the last score_markers/overlap/blocked_stats call in milliseconds,
+ * measured with CUDA events on the context's stream: out[0..7] = transpose, stats, sort, count,
+ * effects, summaries, minrank, total. Returns how many entries were written. */
+int scranb200_ctx_last_timing(scranb200_ctx* ctx, double* out_ms, int n);
+
+/* ---- matrix upload: replaces beachmat::read_lin_block on the reference side ----------------
+ * (src/overlap_exprs.cpp:141, src/compute_blocked_stats.cpp:16). A dgCMatrix maps directly:
+ * p = @p (ncol + 1), i = @i (0-based rows, strictly increasing within a column), x = @x.
+ * 64-bit column pointers because 33,538 x 1.3M at 7 % has more than 2^31 non-zeros; the _csc32
+ * form takes R's own int @p. A device matrix is limited to 2^32 - 1 stored entries. */
+int scranb200_upload_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const int64_t* p, const int32_t* i,
+                         const double* x, scranb200_mat** out);
+int scranb200_upload_csc32(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const int32_t* p, const int32_t* i,
+                           const double* x, scranb200_mat** out);
+/* Ordinary column-major double matrix; exact zeros are not stored (the reference's dense branch
+ * skips them too: src/compute_blocked_stats.cpp:74, src/overlap_exprs.cpp:43-47). */
+int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const double* x, scranb200_mat** out);
+/* Borrow CSC arrays that already live in this device's memory (DEVICE pointers; not copied, not
+ * freed). Used by the multi-GPU harness and by bench.py's device-resident timing. */
+int scranb200_wrap_device_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, int64_t nnz, const int64_t* d_p,
+                              const int32_t* d_i, const double* d_x, scranb200_mat** out);
+void scranb200_mat_free(scranb200_mat* mat);
+int64_t scranb200_mat_nnz(const scranb200_mat* mat);
+
+/* ---- compute_blocked_stats_none: src/compute_blocked_stats.cpp:205-208 (template :15-123) ---
+ * Per gene and block: mean and unbiased variance over ALL cells of the block, zeros included,
+ * with the reference's operation order (running update over stored values in cell order, then
+ * the closed-form zero fill), so results are bit-identical to the reference's sparse branch.
+ * block: one id per cell, 0-based, SCRANB200_NA_INT (or any negative) = skip the cell (:39-42).
+ * mean_out, var_out: nrow x nblocks column-major, like the reference's NumericMatrix pair.
+ * ndetected_out (nullable, same shape): number of values > 0, i.e. what
+ * scuttle::summarizeAssayByGroup(statistics="num.detected") gives at R/scoreMarkers.R:361-363.
+ * Empty block: mean and variance NaN (:86-88); one cell: variance NaN (:91-94). */
+int scranb200_blocked_stats(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* block, int nblocks,
+                            double* mean_out, double* var_out, double* ndetected_out);
+
+/* ---- overlap_exprs_paired: src/overlap_exprs.cpp:196-220 ------------------------------------
+ * groups: the reference's list of 0-based cell-index vectors, flattened: group g owns
+ * group_cells[group_ptr[g] .. group_ptr[g+1]). A cell may belong to at most one group (the
+ * reference's R callers guarantee it: R/scoreMarkers.R:341-345).
+ * left/right: 1-based group indices, exactly as the reference takes them (:215).
+ * u_out: npairs x nrow column-major (pairs contiguous within a gene), U = #(a - lfc > b) +
+ * 0.5 #(a - lfc == b) over a in left group, b in right group; exact half-integers.
+ * ties_out (nullable, same shape): the tie term sum t(t^2 - 1) the reference computes alongside
+ * (:121-124) but only returns from overlap_exprs. */
+int scranb200_overlap_exprs_paired(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* left,
+                                   const int32_t* right, int64_t npairs, int ngroups, const int64_t* group_ptr,
+                                   const int32_t* group_cells, double lfc, double* u_out, double* ties_out);
+
+/* ---- overlap_exprs: src/overlap_exprs.cpp:140-193 -------------------------------------------
+ * All pairs i2 < i1 of the given groups; the reference's ragged list-of-matrices is returned
+ * flattened as [ngroups][ngroups][nrow]: entry (i1, i2) holds column i2 of matrix i1. With
+ * lfc != 0 entry (i2, i1) holds the "-lfc" contrast (:183-187). Entries the reference does not
+ * allocate (i2 >= i1 when lfc == 0) are NaN; pairs with an empty group stay 0 (:175,177). */
+int scranb200_overlap_exprs(scranb200_ctx* ctx, const scranb200_mat* mat, int ngroups, const int64_t* group_ptr,
+                            const int32_t* group_cells, double lfc, double* u_out, double* ties_out);
+
+/* ---- fused scoreMarkers: replaces .compute_all_effect_sizes + computeMinRank ----------------
+ * (R/scoreMarkers.R:351-414 and :251-256, R/computeMinRank.R:45-50), so that R never
+ * materialises the genes x block-pairs matrices.
+ *
+ * groups: per cell, the index of the cell's group in sort(unique(groups)) (R/scoreMarkers.R:192);
+ *         negative = NA (cell ignored). block: nullable; per cell block code, any non-negative ints.
+ * des_left/des_right: the desired comparisons as group indices, in the order
+ *         .expand_pairings gives them (R/expandPairings.R:1-58); nullable = all ordered pairs
+ *         of the ngroups groups in expand.grid order (first index fastest).
+ * A "score plan" holds the bookkeeping of R/scoreMarkers.R:196-217, 293-345, 463-521. */
+typedef struct scranb200_plan scranb200_plan;
+
+int scranb200_plan_create(scranb200_ctx* ctx, int64_t ncells, const int32_t* groups, int ngroups,
+                          const int32_t* block, const int32_t* des_left, const int32_t* des_right,
+                          int64_t ndesired, double lfc, scranb200_plan** out);
+void scranb200_plan_destroy(scranb200_plan* plan);
+/* info[0] = number of output groups K (distinct left groups, ascending), [1] = ndesired,
+ * [2] = number of block-averaged comparisons Q, [3] = block-level pairs, [4] = combinations. */
+int scranb200_plan_info(const scranb200_plan* plan, int64_t* info, int n);
+/* out_groups[K]: group index of each output table; right_ptr[K+1], right_group[ndesired]: the
+ * compared-against groups of each table in column order; weight[ndesired]: combined weights
+ * (mcols(full)$weight, R/scoreMarkers.R:487, 571-574). Any pointer may be null. */
+int scranb200_plan_tables(const scranb200_plan* plan, int32_t* out_groups, int64_t* right_ptr,
+                          int32_t* right_group, double* weight);
+
+#define SCRANB200_NCOLS 19 /* self.average, other.average, self.detected, other.detected, then
+                              {mean,min,median,max,rank} x {logFC.cohen, AUC, logFC.detected}:
+                              the reference's column order (R/scoreMarkers.R:370,392,401-411,562-576) */
+
+/* out: [K][19][nrow] doubles (rank columns hold integers). full_out (nullable):
+ * [3][ndesired][nrow], effect-major in the order cohen, AUC, detected, then comparisons grouped
+ * by output table in column order: the full.* matrices of full.stats=TRUE. */
+int scranb200_score_markers(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan,
+                            double* out, double* full_out);
+
+/* ---- staged form for gene-sharded multi-GPU runs (all buffers are DEVICE pointers) ----------
+ * stage 1 on each gene shard: effects d_eff [3][Q][ld] (gene-contiguous columns, this shard's
+ * rows at [row0, row0 + nrow_shard)), and the non-rank columns of d_out [K][19][ld].
+ * stage 2 after the gather, on columns [q0, q1): min-ranks over all ngenes rows, combined into
+ * d_minrank [K][3][ngenes] (int32, pre-filled with INT32_MAX by scranb200_fill_i32) with atomicMin.
+ * stage 3: write d_minrank into the rank columns of d_out. */
+int scranb200_score_effects_dev(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan,
+                                int64_t ld, int64_t row0, double* d_eff, double* d_out);
+int scranb200_score_minrank_dev(scranb200_ctx* ctx, const scranb200_plan* plan, int64_t ngenes, int64_t ld,
+                                const double* d_eff, int64_t q0, int64_t q1, int32_t* d_minrank);
+int scranb200_score_finish_dev(scranb200_ctx* ctx, const scranb200_plan* plan, int64_t ngenes, int64_t ld,
+                               const int32_t* d_minrank, double* d_out);
+int scranb200_fill_i32(scranb200_ctx* ctx, int32_t* d_ptr, int64_t n, int32_t value);
+
+/* ---- computeMinRank: R/computeMinRank.R:45-50 (ties.method="min", decreasing=TRUE) ----------
+ * x: nrow x ncol column-major; out[nrow]: min over columns of (1 + number of non-NaN entries of
+ * the column strictly greater), NaN entries ignored; INT32_MAX if a row has none. */
+int scranb200_compute_min_rank(scranb200_ctx* ctx, const double* x, int64_t nrow, int64_t ncol, int32_t* out);
+
+/* ---- synthetic input (bench.py), generated on the device -------------
+ * Writes a CSC matrix of genes [g0, g1) x ncells log-counts into device memory owned by the
+ * returned matrix. density < 0: natural Poisson density (config 1). */
+int scranb200_synth_csc(scranb200_ctx* ctx, int64_t ngenes_total, int64_t g0, int64_t g1, int64_t ncells,
+                        const int32_t* groups, int ngroups, double density, uint64_t seed, scranb200_mat** out);
+/* Copy a device matrix's CSC arrays to host buffers (sizes from nrow/ncol/scranb200_mat_nnz). */
+int scranb200_download_csc(scranb200_ctx* ctx, const scranb200_mat* mat, int64_t* p, int32_t* i, double* x);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

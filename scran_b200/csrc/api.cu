@@ -1,0 +1,613 @@
+// The extern "C" surface declared in include/scranb200.h. Every entry point converts C++
+// exceptions into a status code plus a thread-local message, like Rcpp's BEGIN_RCPP/END_RCPP
+// does for the reference (src/RcppExports.cpp:16,22).
+#include <climits>
+#include <cmath>
+
+#include "score.h"
+
+namespace sb {
+
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& m) { g_last_error = m; }
+
+void ctx_guard(scranb200_ctx* ctx) {
+    if (!ctx) throw Error("null context");
+    if (ctx->owner != getpid()) throw Error("this context was created in another process (fork); create a new one");
+    SB_CUDA(cudaSetDevice(ctx->device));
+}
+
+void phase_collect(scranb200_ctx* ctx) {
+    for (int k = 0; k < PH_N; ++k) ctx->timing[k] = 0.0;
+    for (int i = 1; i <= ctx->nev; ++i) {
+        float ms = 0.f;
+        SB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[i - 1], ctx->ev[i]));
+        ctx->timing[ctx->ev_phase[i]] += ms;
+    }
+    if (ctx->nev > 0) {
+        float ms = 0.f;
+        SB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[ctx->nev]));
+        ctx->timing[PH_TOTAL] = ms;
+    }
+}
+
+namespace {
+
+template <typename T>
+T* dev_alloc(size_t n) {
+    void* p = nullptr;
+    SB_CUDA(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+    return reinterpret_cast<T*>(p);
+}
+
+__global__ void widen_i32(const int32_t* in, int64_t n, int64_t* out) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) out[t] = in[t];
+}
+
+// Dense column-major -> CSC without the exact zeros. One warp per column, rows in order.
+__global__ void dense_count(const double* x, int64_t nrow, int64_t ncol, int64_t* counts) {
+    const int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (c >= ncol) return;
+    int64_t n = 0;
+    for (int64_t r = lane; r < nrow; r += 32) n += x[c * nrow + r] != 0.0;
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
+    if (lane == 0) counts[c] = n;
+}
+__global__ void dense_fill(const double* x, int64_t nrow, int64_t ncol, const int64_t* p, int32_t* idx, double* val) {
+    const int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (c >= ncol) return;
+    int64_t at = p[c];
+    for (int64_t r0 = 0; r0 < nrow; r0 += 32) {
+        const int64_t r = r0 + lane;
+        const double v = r < nrow ? x[c * nrow + r] : 0.0;
+        const bool keep = r < nrow && v != 0.0;
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+            const int64_t o = at + __popc(m & ((1u << lane) - 1u));
+            idx[o] = (int32_t)r;
+            val[o] = v;
+        }
+        at += __popc(m);
+    }
+}
+// counts[0..n) -> exclusive prefix in out[0..n], one CTA.
+__global__ void __launch_bounds__(1024) scan_i64(const int64_t* counts, int64_t n, int64_t* out) {
+    __shared__ int64_t part[1024];
+    const int t = threadIdx.x;
+    const int64_t per = (n + 1023) / 1024;
+    const int64_t lo = min(n, t * per), hi = min(n, lo + per);
+    int64_t s = 0;
+    for (int64_t k = lo; k < hi; ++k) s += counts[k];
+    part[t] = s;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        const int64_t v = t >= d ? part[t - d] : 0;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    int64_t run = part[t] - s;
+    for (int64_t k = lo; k < hi; ++k) {
+        const int64_t c = counts[k];
+        out[k] = run;
+        run += c;
+    }
+    if (t == 1023) out[n] = part[1023];
+}
+
+scranb200_mat* new_mat(scranb200_ctx* ctx, int64_t nrow, int64_t ncol) {
+    if (nrow < 0 || ncol < 0 || nrow > INT32_MAX || ncol > INT32_MAX - 1) throw Error("matrix dimensions out of range");
+    scranb200_mat* m = new scranb200_mat();
+    m->ctx = ctx;
+    m->nrow = nrow;
+    m->ncol = ncol;
+    m->owned = true;
+    return m;
+}
+
+void finish_upload(scranb200_ctx* ctx, scranb200_mat* m, const int32_t* i, const double* x) {
+    m->d_i = dev_alloc<int32_t>(m->nnz);
+    m->d_x = dev_alloc<double>(m->nnz);
+    if (m->nnz > 0) {
+        SB_CUDA(cudaMemcpyAsync(m->d_i, i, (size_t)m->nnz * 4, cudaMemcpyHostToDevice, ctx->stream));
+        SB_CUDA(cudaMemcpyAsync(m->d_x, x, (size_t)m->nnz * 8, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+}
+
+// Cell -> group from the reference's list-of-index-vectors form (src/overlap_exprs.cpp:13-32).
+void groups_to_ids(int64_t ncells, int ngroups, const int64_t* gptr, const int32_t* gcells, std::vector<int32_t>& ids) {
+    ids.assign(ncells, -1);
+    for (int g = 0; g < ngroups; ++g) {
+        for (int64_t k = gptr[g]; k < gptr[g + 1]; ++k) {
+            const int32_t c = gcells[k];
+            if (c < 0 || c >= ncells) throw Error("indices in 'groups' out of range");
+            if (ids[c] >= 0) throw Error("a cell listed in more than one group (or twice) is not supported");
+            ids[c] = g;
+        }
+    }
+}
+
+struct PairRun {
+    PairLayout L;
+    Transposed T;
+};
+
+// transpose (+ optional stats) (+ optional U / ties) for one layout; results stay on the device.
+void run_pairs(scranb200_ctx* ctx, const scranb200_mat* mat, PairLayout& L, DevBuf& lbuf, bool want_stats, double lfc,
+               bool want_u, bool want_t) {
+    Transposed T;
+    run_transpose(ctx, mat, L, T);
+    phase_mark(ctx, PH_TRANSPOSE);
+    const size_t cells = (size_t)std::max<int64_t>(1, mat->nrow) * std::max(1, L.C);
+    if (want_stats) {
+        ctx->mean.reserve(cells * 8);
+        ctx->var.reserve(cells * 8);
+        ctx->ndet.reserve(cells * 8);
+        run_stats(ctx, T, L, ctx->mean.as<double>(), ctx->var.as<double>(), ctx->ndet.as<double>());
+        phase_mark(ctx, PH_STATS);
+    }
+    if (want_u) {
+        const size_t n = (size_t)std::max<int64_t>(1, mat->nrow) * std::max<int64_t>(1, L.npairs);
+        ctx->u_pairs.reserve(n * 8);
+        if (want_t) ctx->t_pairs.reserve(n * 8);
+        run_wilcox(ctx, T, L, lfc, ctx->u_pairs.as<double>(), want_t ? ctx->t_pairs.as<double>() : nullptr);
+    }
+}
+
+void score_stage1(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan, int64_t ld, int64_t row0,
+                  double* d_eff, double* d_out) {
+    if (mat->ncol != plan->ncells) throw Error("plan was built for a different number of cells");
+    PairLayout& L = const_cast<PairLayout&>(plan->layout);
+    run_pairs(ctx, mat, L, const_cast<DevBuf&>(plan->d_layout), true, plan->lfc, true, false);
+    run_effects(ctx, *plan, (int)mat->nrow, ld, row0, ctx->mean.as<double>(), ctx->var.as<double>(),
+                ctx->ndet.as<double>(), ctx->u_pairs.as<double>(), d_eff, d_out);
+    phase_mark(ctx, PH_EFFECTS);
+    run_summaries(ctx, *plan, (int)mat->nrow, ld, row0, d_eff, d_out);
+    phase_mark(ctx, PH_SUMMARY);
+}
+
+}  // namespace
+}  // namespace sb
+
+using namespace sb;
+
+#define API_BEGIN try {
+#define API_END                           \
+    }                                     \
+    catch (const std::exception& e) {     \
+        sb::set_last_error(e.what());     \
+        return 1;                         \
+    }                                     \
+    catch (...) {                         \
+        sb::set_last_error("unknown error"); \
+        return 1;                         \
+    }                                     \
+    return 0;
+
+extern "C" {
+
+const char* scranb200_last_error(void) { return g_last_error.c_str(); }
+int scranb200_version(void) { return 100; }
+
+int scranb200_ctx_create(int device, scranb200_ctx** out) {
+    API_BEGIN
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        throw Error(std::string("no CUDA device available (there is no CPU fallback): ") + cudaGetErrorString(e));
+    }
+    if (device < 0 || device >= count) throw Error("device ordinal out of range");
+    SB_CUDA(cudaSetDevice(device));
+    scranb200_ctx* ctx = new scranb200_ctx();
+    ctx->device = device;
+    ctx->owner = getpid();
+    cudaDeviceProp prop;
+    SB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        delete ctx;
+        throw Error("this library is built for sm_100a (B200) only");
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    SB_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (int k = 0; k < 16; ++k) SB_CUDA(cudaEventCreate(&ctx->ev[k]));
+    *out = ctx;
+    API_END
+}
+
+void scranb200_ctx_destroy(scranb200_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->owner == getpid()) {
+        cudaSetDevice(ctx->device);
+        cudaStreamSynchronize(ctx->stream);
+        sb::DevBuf* bufs[] = {&ctx->table, &ctx->seg_off, &ctx->row_total, &ctx->row_ptr, &ctx->vals, &ctx->stream_lab,
+                              &ctx->unit_m, &ctx->sort_keys, &ctx->sort_labs, &ctx->flags, &ctx->mean, &ctx->var,
+                              &ctx->ndet, &ctx->u_pairs, &ctx->t_pairs, &ctx->layout_i32, &ctx->layout_f64, &ctx->eff,
+                              &ctx->out, &ctx->minrank, &ctx->rank_keys, &ctx->rank_idx, &ctx->plan_tmp, &ctx->io_a,
+                              &ctx->io_b, &ctx->io_c};
+        for (sb::DevBuf* b : bufs) b->release();
+        for (int k = 0; k < 16; ++k) {
+            if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+        }
+        cudaStreamDestroy(ctx->stream);
+    }
+    delete ctx;
+}
+
+int scranb200_ctx_sync(scranb200_ctx* ctx) {
+    API_BEGIN
+    ctx_guard(ctx);
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+uint64_t scranb200_ctx_stream(scranb200_ctx* ctx) { return ctx ? (uint64_t)(uintptr_t)ctx->stream : 0; }
+int64_t scranb200_ctx_launches(scranb200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int scranb200_ctx_last_timing(scranb200_ctx* ctx, double* out_ms, int n) {
+    if (!ctx || !out_ms) return 0;
+    const int m = n < (int)PH_N ? n : (int)PH_N;
+    for (int k = 0; k < m; ++k) out_ms[k] = ctx->timing[k];
+    return m;
+}
+
+int scranb200_upload_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const int64_t* p, const int32_t* i,
+                         const double* x, scranb200_mat** out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    scranb200_mat* m = new_mat(ctx, nrow, ncol);
+    m->nnz = p[ncol];
+    if (m->nnz < 0) throw Error("negative number of stored entries");
+    m->d_p = dev_alloc<int64_t>(ncol + 1);
+    SB_CUDA(cudaMemcpyAsync(m->d_p, p, (size_t)(ncol + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    finish_upload(ctx, m, i, x);
+    *out = m;
+    API_END
+}
+
+int scranb200_upload_csc32(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const int32_t* p, const int32_t* i,
+                           const double* x, scranb200_mat** out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    scranb200_mat* m = new_mat(ctx, nrow, ncol);
+    m->nnz = p[ncol];
+    if (m->nnz < 0) throw Error("negative number of stored entries");
+    m->d_p = dev_alloc<int64_t>(ncol + 1);
+    ctx->io_a.reserve((size_t)(ncol + 1) * 4);
+    SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, p, (size_t)(ncol + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    SB_LAUNCH(ctx, widen_i32, (unsigned)ceil_div(ncol + 1, 256), 256, 0, ctx->io_a.as<int32_t>(), ncol + 1, m->d_p);
+    finish_upload(ctx, m, i, x);
+    *out = m;
+    API_END
+}
+
+int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const double* x, scranb200_mat** out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    scranb200_mat* m = new_mat(ctx, nrow, ncol);
+    const size_t cells = (size_t)nrow * ncol;
+    ctx->io_a.reserve(std::max<size_t>(cells, 1) * 8);
+    ctx->io_b.reserve((size_t)(ncol + 1) * 8);
+    if (cells) SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, x, cells * 8, cudaMemcpyHostToDevice, ctx->stream));
+    m->d_p = dev_alloc<int64_t>(ncol + 1);
+    if (ncol > 0) {
+        SB_LAUNCH(ctx, dense_count, (unsigned)ceil_div(ncol * 32, 256), 256, 0, ctx->io_a.as<double>(), nrow, ncol,
+                  ctx->io_b.as<int64_t>());
+    }
+    SB_LAUNCH(ctx, scan_i64, 1, 1024, 0, ctx->io_b.as<int64_t>(), ncol, m->d_p);
+    SB_CUDA(cudaMemcpyAsync(&m->nnz, m->d_p + ncol, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    m->d_i = dev_alloc<int32_t>(m->nnz);
+    m->d_x = dev_alloc<double>(m->nnz);
+    if (ncol > 0 && m->nnz > 0) {
+        SB_LAUNCH(ctx, dense_fill, (unsigned)ceil_div(ncol * 32, 256), 256, 0, ctx->io_a.as<double>(), nrow, ncol, m->d_p,
+                  m->d_i, m->d_x);
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    *out = m;
+    API_END
+}
+
+int scranb200_wrap_device_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, int64_t nnz, const int64_t* d_p,
+                              const int32_t* d_i, const double* d_x, scranb200_mat** out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    scranb200_mat* m = new_mat(ctx, nrow, ncol);
+    m->owned = false;
+    m->nnz = nnz;
+    m->d_p = const_cast<int64_t*>(d_p);
+    m->d_i = const_cast<int32_t*>(d_i);
+    m->d_x = const_cast<double*>(d_x);
+    *out = m;
+    API_END
+}
+
+void scranb200_mat_free(scranb200_mat* mat) {
+    if (!mat) return;
+    if (mat->owned && mat->ctx && mat->ctx->owner == getpid()) {
+        cudaSetDevice(mat->ctx->device);
+        cudaFree(mat->d_p);
+        cudaFree(mat->d_i);
+        cudaFree(mat->d_x);
+    }
+    delete mat;
+}
+
+int64_t scranb200_mat_nnz(const scranb200_mat* mat) { return mat ? mat->nnz : 0; }
+
+int scranb200_download_csc(scranb200_ctx* ctx, const scranb200_mat* mat, int64_t* p, int32_t* i, double* x) {
+    API_BEGIN
+    ctx_guard(ctx);
+    SB_CUDA(cudaMemcpyAsync(p, mat->d_p, (size_t)(mat->ncol + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (mat->nnz > 0) {
+        SB_CUDA(cudaMemcpyAsync(i, mat->d_i, (size_t)mat->nnz * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        SB_CUDA(cudaMemcpyAsync(x, mat->d_x, (size_t)mat->nnz * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+int scranb200_blocked_stats(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* block, int nblocks,
+                            double* mean_out, double* var_out, double* ndetected_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    if (nblocks < 0) throw Error("negative number of blocks");
+    for (int64_t c = 0; c < mat->ncol; ++c) {
+        if (block[c] >= nblocks) throw Error("block id out of range");
+    }
+    PairLayout L;
+    build_layout(block, mat->ncol, nblocks, nullptr, nullptr, 0, ctx->sm_count * 4, L);
+    upload_layout(ctx, L, ctx->layout_i32);
+    phase_begin(ctx);
+    run_pairs(ctx, mat, L, ctx->layout_i32, true, 0.0, false, false);
+    const size_t bytes = (size_t)mat->nrow * nblocks * 8;
+    if (bytes) {
+        SB_CUDA(cudaMemcpyAsync(mean_out, ctx->mean.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        SB_CUDA(cudaMemcpyAsync(var_out, ctx->var.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        if (ndetected_out) SB_CUDA(cudaMemcpyAsync(ndetected_out, ctx->ndet.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
+    API_END
+}
+
+int scranb200_overlap_exprs_paired(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* left,
+                                   const int32_t* right, int64_t npairs, int ngroups, const int64_t* group_ptr,
+                                   const int32_t* group_cells, double lfc, double* u_out, double* ties_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    std::vector<int32_t> ids;
+    groups_to_ids(mat->ncol, ngroups, group_ptr, group_cells, ids);
+    std::vector<int32_t> l0(npairs), r0(npairs);
+    for (int64_t k = 0; k < npairs; ++k) {
+        l0[k] = left[k] - 1;  // 1-based, src/overlap_exprs.cpp:215
+        r0[k] = right[k] - 1;
+        if (l0[k] < 0 || l0[k] >= ngroups || r0[k] < 0 || r0[k] >= ngroups) throw Error("pair index out of range");
+    }
+    PairLayout L;
+    build_layout(ids.data(), mat->ncol, ngroups, l0.data(), r0.data(), npairs, ctx->sm_count * 4, L);
+    upload_layout(ctx, L, ctx->layout_i32);
+    phase_begin(ctx);
+    run_pairs(ctx, mat, L, ctx->layout_i32, false, lfc, true, ties_out != nullptr);
+    const size_t bytes = (size_t)mat->nrow * npairs * 8;
+    if (bytes) {
+        SB_CUDA(cudaMemcpyAsync(u_out, ctx->u_pairs.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        if (ties_out) SB_CUDA(cudaMemcpyAsync(ties_out, ctx->t_pairs.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
+    API_END
+}
+
+int scranb200_overlap_exprs(scranb200_ctx* ctx, const scranb200_mat* mat, int ngroups, const int64_t* group_ptr,
+                            const int32_t* group_cells, double lfc, double* u_out, double* ties_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    std::vector<int32_t> ids;
+    groups_to_ids(mat->ncol, ngroups, group_ptr, group_cells, ids);
+    std::vector<int32_t> l0, r0;
+    for (int a = 0; a < ngroups; ++a) {
+        if (group_ptr[a + 1] == group_ptr[a]) continue;  // src/overlap_exprs.cpp:175
+        for (int b = 0; b < a; ++b) {
+            if (group_ptr[b + 1] == group_ptr[b]) continue;  // :177
+            l0.push_back(a);
+            r0.push_back(b);
+        }
+    }
+    const int64_t npairs = (int64_t)l0.size();
+    const int64_t ngenes = mat->nrow;
+    const size_t G = (size_t)ngroups;
+    const double nan = std::nan("");
+    for (size_t a = 0; a < G; ++a) {
+        for (size_t b = 0; b < G; ++b) {
+            const bool present = lfc == 0.0 ? b < a : true;  // :153-166
+            for (int64_t g = 0; g < ngenes; ++g) {
+                u_out[(a * G + b) * ngenes + g] = present ? 0.0 : nan;
+                if (ties_out) ties_out[(a * G + b) * ngenes + g] = present ? 0.0 : nan;
+            }
+        }
+    }
+    if (npairs == 0 || ngenes == 0) return 0;
+    PairLayout L;
+    build_layout(ids.data(), mat->ncol, ngroups, l0.data(), r0.data(), npairs, ctx->sm_count * 4, L);
+    upload_layout(ctx, L, ctx->layout_i32);
+    std::vector<double> hu((size_t)ngenes * npairs), ht(ties_out ? (size_t)ngenes * npairs : 0);
+    phase_begin(ctx);
+    for (int pass = 0; pass < (lfc == 0.0 ? 1 : 2); ++pass) {
+        const double shift = pass == 0 ? lfc : -lfc;  // :179-187
+        run_pairs(ctx, mat, L, ctx->layout_i32, false, shift, true, ties_out != nullptr);
+        SB_CUDA(cudaMemcpyAsync(hu.data(), ctx->u_pairs.p, hu.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        if (ties_out) SB_CUDA(cudaMemcpyAsync(ht.data(), ctx->t_pairs.p, ht.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        SB_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (int64_t k = 0; k < npairs; ++k) {
+            const size_t a = pass == 0 ? l0[k] : r0[k], b = pass == 0 ? r0[k] : l0[k];
+            for (int64_t g = 0; g < ngenes; ++g) {
+                u_out[(a * G + b) * ngenes + g] = hu[(size_t)g * npairs + k];
+                if (ties_out) ties_out[(a * G + b) * ngenes + g] = ht[(size_t)g * npairs + k];
+            }
+        }
+    }
+    phase_collect(ctx);
+    API_END
+}
+
+int scranb200_plan_create(scranb200_ctx* ctx, int64_t ncells, const int32_t* groups, int ngroups,
+                          const int32_t* block, const int32_t* des_left, const int32_t* des_right,
+                          int64_t ndesired, double lfc, scranb200_plan** out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    scranb200_plan* P = new scranb200_plan();
+    try {
+        build_plan(*P, ncells, groups, ngroups, block, des_left, des_right, ndesired, lfc);
+        upload_plan(ctx, *P);
+    } catch (...) {
+        delete P;
+        throw;
+    }
+    *out = P;
+    API_END
+}
+
+void scranb200_plan_destroy(scranb200_plan* plan) {
+    if (!plan) return;
+    if (plan->ctx && plan->ctx->owner == getpid()) {
+        cudaSetDevice(plan->ctx->device);
+        plan->d_layout.release();
+        plan->d_ints.release();
+        plan->d_dbls.release();
+    }
+    delete plan;
+}
+
+int scranb200_plan_info(const scranb200_plan* plan, int64_t* info, int n) {
+    API_BEGIN
+    const int64_t v[5] = {plan->K, plan->ndesired, plan->Q, (int64_t)plan->left.size(), plan->C};
+    for (int k = 0; k < n && k < 5; ++k) info[k] = v[k];
+    API_END
+}
+
+int scranb200_plan_tables(const scranb200_plan* plan, int32_t* out_groups, int64_t* right_ptr, int32_t* right_group,
+                          double* weight) {
+    API_BEGIN
+    for (int k = 0; k < plan->K; ++k) {
+        if (out_groups) out_groups[k] = plan->out_group[k];
+    }
+    for (int k = 0; k <= plan->K; ++k) {
+        if (right_ptr) right_ptr[k] = plan->right_ptr[k];
+    }
+    for (int64_t k = 0; k < plan->ndesired; ++k) {
+        if (right_group) right_group[k] = plan->right_group[k];
+        if (weight) weight[k] = plan->right_weight[k];
+    }
+    API_END
+}
+
+int scranb200_fill_i32(scranb200_ctx* ctx, int32_t* d_ptr, int64_t n, int32_t value) {
+    API_BEGIN
+    ctx_guard(ctx);
+    run_fill_i32(ctx, d_ptr, n, value);
+    API_END
+}
+
+int scranb200_score_effects_dev(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan,
+                                int64_t ld, int64_t row0, double* d_eff, double* d_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    phase_begin(ctx);
+    score_stage1(ctx, mat, plan, ld, row0, d_eff, d_out);
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
+    API_END
+}
+
+int scranb200_score_minrank_dev(scranb200_ctx* ctx, const scranb200_plan* plan, int64_t ngenes, int64_t ld,
+                                const double* d_eff, int64_t q0, int64_t q1, int32_t* d_minrank) {
+    API_BEGIN
+    ctx_guard(ctx);
+    if (q0 < 0 || q1 > plan->Q || q0 > q1) throw Error("comparison range out of bounds");
+    phase_begin(ctx);
+    run_minrank(ctx, *plan, ngenes, ld, d_eff, q0, q1, d_minrank);
+    phase_mark(ctx, PH_MINRANK);
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
+    API_END
+}
+
+int scranb200_score_finish_dev(scranb200_ctx* ctx, const scranb200_plan* plan, int64_t ngenes, int64_t ld,
+                               const int32_t* d_minrank, double* d_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    run_finish(ctx, *plan, ngenes, ld, d_minrank, d_out);
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+int scranb200_score_markers(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan, double* out,
+                            double* full_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    const int64_t ngenes = mat->nrow;
+    const size_t n_eff = (size_t)3 * std::max(1, plan->Q) * std::max<int64_t>(1, ngenes);
+    const size_t n_out = (size_t)std::max(1, plan->K) * SCRANB200_NCOLS * std::max<int64_t>(1, ngenes);
+    const size_t n_rank = (size_t)std::max(1, plan->K) * 3 * std::max<int64_t>(1, ngenes);
+    ctx->eff.reserve(n_eff * 8);
+    ctx->out.reserve(n_out * 8);
+    ctx->minrank.reserve(n_rank * 4);
+    double* d_eff = ctx->eff.as<double>();
+    double* d_out = ctx->out.as<double>();
+    int32_t* d_rank = ctx->minrank.as<int32_t>();
+    phase_begin(ctx);
+    score_stage1(ctx, mat, plan, ngenes, 0, d_eff, d_out);
+    run_fill_i32(ctx, d_rank, (int64_t)plan->K * 3 * ngenes, INT32_MAX);
+    run_minrank(ctx, *plan, ngenes, ngenes, d_eff, 0, plan->Q, d_rank);
+    run_finish(ctx, *plan, ngenes, ngenes, d_rank, d_out);
+    phase_mark(ctx, PH_MINRANK);
+    if (ngenes > 0 && plan->K > 0) {
+        SB_CUDA(cudaMemcpyAsync(out, d_out, (size_t)plan->K * SCRANB200_NCOLS * ngenes * 8, cudaMemcpyDeviceToHost,
+                                ctx->stream));
+    }
+    std::vector<double> heff;
+    if (full_out && ngenes > 0 && plan->Q > 0) {
+        heff.resize((size_t)3 * plan->Q * ngenes);
+        SB_CUDA(cudaMemcpyAsync(heff.data(), d_eff, heff.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
+    if (full_out && ngenes > 0) {  // full.* matrices: R/scoreMarkers.R:536-555, 571-574
+        const double nan = std::nan("");
+        for (int e = 0; e < 3; ++e) {
+            for (int64_t j = 0; j < plan->ndesired; ++j) {
+                double* dst = full_out + ((size_t)e * plan->ndesired + j) * ngenes;
+                const int qd = plan->q_direct[j], qf = plan->q_flipped[j];
+                if (qd >= 0) {
+                    memcpy(dst, heff.data() + ((size_t)e * plan->Q + qd) * ngenes, (size_t)ngenes * 8);
+                } else if (qf >= 0) {
+                    const double* src = heff.data() + ((size_t)e * plan->Q + qf) * ngenes;
+                    for (int64_t g = 0; g < ngenes; ++g) dst[g] = e == 1 ? 1.0 - src[g] : -src[g];
+                } else {
+                    for (int64_t g = 0; g < ngenes; ++g) dst[g] = nan;
+                }
+            }
+        }
+    }
+    API_END
+}
+
+int scranb200_compute_min_rank(scranb200_ctx* ctx, const double* x, int64_t nrow, int64_t ncol, int32_t* out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    if (nrow == 0) return 0;
+    ctx->io_a.reserve(std::max<size_t>(1, (size_t)nrow * ncol) * 8);
+    ctx->io_b.reserve((size_t)nrow * 4);
+    if (ncol > 0) SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, x, (size_t)nrow * ncol * 8, cudaMemcpyHostToDevice, ctx->stream));
+    run_min_rank_matrix(ctx, ctx->io_a.as<double>(), nrow, ncol, ctx->io_b.as<int32_t>());
+    SB_CUDA(cudaMemcpyAsync(out, ctx->io_b.p, (size_t)nrow * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+}  // extern "C"

@@ -1,0 +1,214 @@
+// K4: the three effect sizes per block-level pair, folded straight into the block-averaged
+// comparison they belong to, and the self./other. columns.
+//
+//   Cohen's d        R/scoreMarkers.R:417-426   (mL - mR - lfc) / sqrt((vL + vR) / 2), 0 if the
+//                                               numerator is exactly 0
+//   AUC              R/scoreMarkers.R:442-445   U / (nL * nR)
+//   logFC.detected   R/scoreMarkers.R:428-440   log2 of the ratio of shrunken detected fractions
+//   block average    R/scoreMarkers.R:479-492   matrixStats::rowWeightedMeans(na.rm=TRUE) with
+//                                               w = nL * nR (:369): weights divided by their sum
+//                                               first, then sum(w_i * e_i); the reference's row
+//                                               sum runs in long double, here in double-double
+//   self./other.     R/scoreMarkers.R:395-411   per-group average / detected fraction
+//
+// The reference materialises genes x block-pairs matrices for all three effects (7.9 GB at
+// config 3); here each (gene, comparison) thread consumes its block-level values on the fly.
+#include "score.h"
+
+namespace sb {
+
+namespace {
+
+struct DD {
+    double hi, lo;
+};
+__device__ inline void dd_add(DD& s, double x) {  // s += x, error-free (Knuth two-sum)
+    const double t = s.hi + x;
+    const double bp = t - s.hi;
+    const double err = (s.hi - (t - bp)) + (x - bp);
+    s.hi = t;
+    s.lo += err;
+}
+__device__ inline double dd_value(const DD& s) { return s.hi + s.lo; }
+
+__device__ inline double effect_cohen(double mL, double mR, double vL, double vR, double lfc) {
+    const double delta = mL - mR - lfc;
+    if (delta == 0.0) return 0.0;
+    return delta / sqrt((vL + vR) / 2.0);
+}
+
+__device__ inline double effect_detected(double dL, double dR, double nL, double nR) {
+    const double mn = fmin(nL, nR);
+    const double pl = 1.0 * nL / mn, pr = 1.0 * nR / mn;
+    const double lp = (dL + pl) / (nL + pl * 2.0);
+    const double rp = (dR + pr) / (nR + pr * 2.0);
+    return log2(lp / rp);
+}
+
+struct EffParams {
+    int ngenes, Q;
+    int64_t ld, row0;
+    const double *mean, *var, *ndet, *u;  // [C][ngenes], u: [ngenes][npairs]
+    int64_t npairs;
+    const int32_t *left, *right, *avg_ptr, *avg_idx;
+    const double* ncells;
+    double lfc;
+    double* eff;  // [3][Q][ld]
+};
+
+__global__ void __launch_bounds__(256) k4_effects(EffParams P) {
+    // 4 consecutive genes per comparison share a 32-byte sector of every [.][ngenes] array.
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t tiles = (P.ngenes + 3) / 4;
+    const int64_t tile = t / ((int64_t)4 * P.Q);
+    if (tile >= tiles) return;
+    const int rem = (int)(t % ((int64_t)4 * P.Q));
+    const int q = rem / 4;
+    const int g = (int)(tile * 4 + (rem & 3));
+    if (g >= P.ngenes) return;
+
+    const int j0 = P.avg_ptr[q], j1 = P.avg_ptr[q + 1];
+    // Pass 1: sum of weights over the blocks where each effect is defined.
+    double wsum[3] = {0.0, 0.0, 0.0};
+    for (int j = j0; j < j1; ++j) {
+        const int p = P.avg_idx[j];
+        const int l = P.left[p], r = P.right[p];
+        const double nL = P.ncells[l], nR = P.ncells[r];
+        const double w = nL * nR;
+        const size_t al = (size_t)l * P.ngenes + g, ar = (size_t)r * P.ngenes + g;
+        const double d = effect_cohen(P.mean[al], P.mean[ar], P.var[al], P.var[ar], P.lfc);
+        if (!isnan(d)) wsum[0] += w;
+        const double a = P.u[(size_t)g * P.npairs + p] / w;
+        if (!isnan(a)) wsum[1] += w;
+        const double f = effect_detected(P.ndet[al], P.ndet[ar], nL, nR);
+        if (!isnan(f)) wsum[2] += w;
+    }
+    // Pass 2: sum of (w / wsum) * effect.
+    DD acc[3] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
+    for (int j = j0; j < j1; ++j) {
+        const int p = P.avg_idx[j];
+        const int l = P.left[p], r = P.right[p];
+        const double nL = P.ncells[l], nR = P.ncells[r];
+        const double w = nL * nR;
+        const size_t al = (size_t)l * P.ngenes + g, ar = (size_t)r * P.ngenes + g;
+        const double d = effect_cohen(P.mean[al], P.mean[ar], P.var[al], P.var[ar], P.lfc);
+        if (!isnan(d)) dd_add(acc[0], (w / wsum[0]) * d);
+        const double a = P.u[(size_t)g * P.npairs + p] / w;
+        if (!isnan(a)) dd_add(acc[1], (w / wsum[1]) * a);
+        const double f = effect_detected(P.ndet[al], P.ndet[ar], nL, nR);
+        if (!isnan(f)) dd_add(acc[2], (w / wsum[2]) * f);
+    }
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    for (int e = 0; e < 3; ++e) {
+        P.eff[((size_t)e * P.Q + q) * P.ld + P.row0 + g] = wsum[e] > 0.0 ? dd_value(acc[e]) : nan;
+    }
+}
+
+struct SelfParams {
+    int ngenes, K;
+    int64_t ld, row0;
+    const double *mean, *ndet;  // [C][ngenes]
+    const double* ncells;
+    const int32_t *out_group, *proj_ptr, *proj_comb, *other_ptr, *other_group;
+    const double* proj_coef;
+    int blocked;
+    double* out;  // [K][19][ld]
+};
+
+__device__ inline double group_value(const SelfParams& P, int grp, int g, bool detected) {
+    const int a = P.proj_ptr[grp], b = P.proj_ptr[grp + 1];
+    if (!P.blocked) {  // one combination per group: the summary itself
+        const int c = P.proj_comb[a];
+        return detected ? P.ndet[(size_t)c * P.ngenes + g] / P.ncells[c] : P.mean[(size_t)c * P.ngenes + g];
+    }
+    DD s = {0.0, 0.0};
+    for (int k = a; k < b; ++k) {
+        const int c = P.proj_comb[k];
+        double y;
+        if (detected) {
+            const double prop = P.ndet[(size_t)c * P.ngenes + g] / P.ncells[c];
+            const double x = (prop + 0.01) / (1.0 + 2.0 * 0.01);
+            y = log(x / (1.0 - x));
+        } else {
+            y = P.mean[(size_t)c * P.ngenes + g];
+        }
+        dd_add(s, P.proj_coef[k] * y);
+    }
+    double v = dd_value(s);
+    if (detected) {
+        v = exp(v);
+        v = v / (v + 1.0);
+        v = v * (1.0 + 2.0 * 0.01) - 0.01;
+        v = fmin(fmax(v, 0.0), 1.0);
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(256) k4_selfother(SelfParams P) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)P.ngenes * P.K) return;
+    const int g = (int)(t % P.ngenes), k = (int)(t / P.ngenes);
+    const int grp = P.out_group[k];
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    const bool has_self = P.proj_ptr[grp + 1] > P.proj_ptr[grp];
+    for (int which = 0; which < 2; ++which) {
+        const bool det = which == 1;
+        const double self = has_self ? group_value(P, grp, g, det) : nan;
+        DD s = {0.0, 0.0};
+        const int o0 = P.other_ptr[k], o1 = P.other_ptr[k + 1];
+        for (int o = o0; o < o1; ++o) dd_add(s, group_value(P, P.other_group[o], g, det));
+        const double other = o1 > o0 ? dd_value(s) / (double)(o1 - o0) : nan;
+        double* base = P.out + ((size_t)k * SCRANB200_NCOLS + 2 * which) * P.ld + P.row0 + g;
+        base[0] = self;
+        base[P.ld] = other;
+    }
+}
+
+}  // namespace
+
+void run_effects(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int64_t ld, int64_t row0, const double* d_mean,
+                 const double* d_var, const double* d_ndet, const double* d_u, double* d_eff, double* d_out) {
+    if (ngenes == 0) return;
+    if (P.Q > 0) {
+        EffParams ep;
+        ep.ngenes = ngenes;
+        ep.Q = P.Q;
+        ep.ld = ld;
+        ep.row0 = row0;
+        ep.mean = d_mean;
+        ep.var = d_var;
+        ep.ndet = d_ndet;
+        ep.u = d_u;
+        ep.npairs = (int64_t)P.left.size();
+        ep.left = P.d_left;
+        ep.right = P.d_right;
+        ep.avg_ptr = P.d_avg_ptr;
+        ep.avg_idx = P.d_avg_idx;
+        ep.ncells = P.d_ncells_comb;
+        ep.lfc = P.lfc;
+        ep.eff = d_eff;
+        const int64_t threads = ceil_div(ngenes, 4) * 4 * P.Q;
+        SB_LAUNCH(ctx, k4_effects, (unsigned)ceil_div(threads, 256), 256, 0, ep);
+    }
+    if (P.K > 0) {
+        SelfParams sp;
+        sp.ngenes = ngenes;
+        sp.K = P.K;
+        sp.ld = ld;
+        sp.row0 = row0;
+        sp.mean = d_mean;
+        sp.ndet = d_ndet;
+        sp.ncells = P.d_ncells_comb;
+        sp.out_group = P.d_out_group;
+        sp.proj_ptr = P.d_proj_ptr;
+        sp.proj_comb = P.d_proj_comb;
+        sp.other_ptr = P.d_other_ptr;
+        sp.other_group = P.d_other_group;
+        sp.proj_coef = P.d_proj_coef;
+        sp.blocked = P.blocked ? 1 : 0;
+        sp.out = d_out;
+        SB_LAUNCH(ctx, k4_selfother, (unsigned)ceil_div((int64_t)ngenes * P.K, 256), 256, 0, sp);
+    }
+}
+
+}  // namespace sb

@@ -1,0 +1,151 @@
+// A CTA-wide stable LSD radix sort of (uint64 key, payload) pairs. The ping-pong buffers may
+// live in shared memory (small inputs) or in global memory (inputs beyond the shared-memory
+// capacity; one CTA streams them through L2). Used for the value order of a gene's non-zeros
+// inside a unit (K3) and for ranking effect columns across genes (K5).
+//
+// Stability per pass: every warp owns a contiguous slice of the input, walks it 32 elements at a
+// time and ranks equal digits inside the 32 by lane order (match.any + popc); the per-warp digit
+// histograms are scanned in (digit, warp) order. Passes whose digit is constant over the whole
+// input are detected from the histogram and skipped.
+#pragma once
+
+#include <stdint.h>
+
+namespace sb {
+
+constexpr int SORT_THREADS = 1024;
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+constexpr int SORT_HIST_WORDS = SORT_WARPS * 256 + 64;  // + aux words
+
+// whist: SORT_HIST_WORDS uint32 of shared memory. Returns 0 if the result is in (ka, pa), 1 if
+// in (kb, pb). Must be called by all SORT_THREADS threads with identical arguments.
+template <typename P>
+__device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, int bit_lo, int bit_hi,
+                                uint32_t* whist) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t* aux = whist + SORT_WARPS * 256;  // [0..7] warp sums, [32] skip flag
+    const int per = (((n + SORT_WARPS - 1) / SORT_WARPS) + 31) & ~31;
+    const int s_lo = min(n, warp * per), s_hi = min(n, s_lo + per);
+    uint32_t* mine = whist + warp * 256;
+    int cur = 0;
+    for (int bit = bit_lo; bit < bit_hi; bit += 8) {
+        uint64_t* sk = cur ? kb : ka;
+        P* sp = cur ? pb : pa;
+        uint64_t* dk = cur ? ka : kb;
+        P* dp = cur ? pa : pb;
+        for (int i = lane; i < 256; i += 32) mine[i] = 0;
+        if (tid == 0) aux[32] = 0;
+        __syncwarp();
+        for (int t = s_lo; t < s_hi; t += 32) {
+            const int i = t + lane;
+            const bool valid = i < s_hi;
+            const unsigned act = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const unsigned d = (unsigned)(sk[i] >> bit) & 255u;
+                const unsigned peers = __match_any_sync(act, d);
+                if (lane == __ffs(peers) - 1) mine[d] += __popc(peers);
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        if (tid < 256) {
+            uint32_t run = 0;
+            for (int w = 0; w < SORT_WARPS; ++w) {
+                const uint32_t v = whist[w * 256 + tid];
+                whist[w * 256 + tid] = run;
+                run += v;
+            }
+            const uint32_t tot = run;
+            uint32_t inc = tot;
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += y;
+            }
+            if (lane == 31) aux[warp] = inc;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            uint32_t wbase = 0;
+            for (int w = 0; w < warp; ++w) wbase += aux[w];
+            const uint32_t dbase = wbase + inc - tot;
+            for (int w = 0; w < SORT_WARPS; ++w) whist[w * 256 + tid] += dbase;
+            if (tot == (uint32_t)n) aux[32] = 1;
+        }
+        __syncthreads();
+        const bool skip = aux[32] != 0;
+        if (!skip) {
+            for (int t = s_lo; t < s_hi; t += 32) {
+                const int i = t + lane;
+                const bool valid = i < s_hi;
+                const unsigned act = __ballot_sync(0xffffffffu, valid);
+                if (valid) {
+                    const uint64_t k = sk[i];
+                    const P pl = sp[i];
+                    const unsigned d = (unsigned)(k >> bit) & 255u;
+                    const unsigned peers = __match_any_sync(act, d);
+                    const uint32_t base = mine[d];
+                    const uint32_t at = base + __popc(peers & ((1u << lane) - 1u));
+                    dk[at] = k;
+                    dp[at] = pl;
+                    __syncwarp(act);
+                    if (lane == __ffs(peers) - 1) mine[d] = base + __popc(peers);
+                    __syncwarp(act);
+                }
+            }
+            cur ^= 1;
+        }
+        __syncthreads();
+    }
+    return cur;
+}
+
+// After a sort on the high 32 key bits: order every run of equal high words by the full key,
+// stably. Runs longer than 32 are left alone and reported through *overflow (shared memory).
+template <typename P>
+__device__ void fixup_low_bits(uint64_t* k, P* p, int n, uint32_t* overflow) {
+    for (int j = threadIdx.x; j < n; j += blockDim.x) {
+        const uint32_t h = (uint32_t)(k[j] >> 32);
+        if (j > 0 && (uint32_t)(k[j - 1] >> 32) == h) continue;
+        int e = j + 1;
+        while (e < n && e - j <= 32 && (uint32_t)(k[e] >> 32) == h) ++e;
+        const int len = e - j;
+        if (len > 32) {
+            *overflow = 1;
+        } else if (len >= 2) {
+            for (int a = j + 1; a < e; ++a) {
+                const uint64_t ka = k[a];
+                const P pa = p[a];
+                int b = a - 1;
+                while (b >= j && k[b] > ka) {
+                    k[b + 1] = k[b];
+                    p[b + 1] = p[b];
+                    --b;
+                }
+                k[b + 1] = ka;
+                p[b + 1] = pa;
+            }
+        }
+    }
+}
+
+// Full 64-bit stable sort: high word first with the low-bit fix-up, falling back to all eight
+// digits when the keys share long runs of equal high words. Returns the buffer index (0 / 1).
+template <typename P>
+__device__ int block_sort_keys(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, uint32_t* whist) {
+    uint32_t* overflow = whist + SORT_WARPS * 256 + 33;
+    if (threadIdx.x == 0) *overflow = 0;
+    int cur = block_radix_sort<P>(ka, pa, kb, pb, n, 32, 64, whist);
+    uint64_t* k = cur ? kb : ka;
+    P* p = cur ? pb : pa;
+    fixup_low_bits<P>(k, p, n, overflow);
+    __syncthreads();
+    if (*overflow) {
+        // (k, p) is the current input; the other pair is scratch.
+        uint64_t* ok = cur ? ka : kb;
+        P* op = cur ? pa : pb;
+        const int c2 = block_radix_sort<P>(k, p, ok, op, n, 0, 64, whist);
+        cur = c2 ? (cur ^ 1) : cur;
+    }
+    __syncthreads();
+    return cur;
+}
+
+}  // namespace sb

@@ -1,0 +1,210 @@
+// K1: cell-major CSC -> gene-major values bucketed by (gene, device combination), stable in cell
+// order. Replaces the reference's per-gene dense row extraction and per-group gather
+// (src/overlap_exprs.cpp:171,211 and :37-47) and the column walk of
+// src/compute_blocked_stats.cpp:53-56 with one O(nnz) counting sort.
+//
+// Why it is stable without atomics: the cells are visited in (combination, cell) order, one
+// chunk of columns per CTA, one column at a time. Inside one column every gene occurs at most
+// once (dgCMatrix invariant, validated in the counting pass), so the threads of a CTA can bump
+// the per-gene cursor in shared memory with plain loads and stores; the barrier between two
+// columns orders the cursor updates of consecutive cells. The per-chunk gene histograms are
+// scanned in (gene, chunk) order, which yields for every (gene, combination) a contiguous
+// segment holding that gene's stored values of that combination in ascending cell order:
+// exactly the sequence the reference's running mean/variance update consumes.
+#include "kernels.h"
+
+namespace sb {
+
+namespace {
+
+constexpr int K1_THREADS = 1024;
+
+// Pass A: table[chunk][gene] = stored entries of `gene` in the chunk's columns.
+__global__ void __launch_bounds__(K1_THREADS)
+k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const int32_t* __restrict__ perm,
+         const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen, uint32_t* __restrict__ table,
+         int* __restrict__ bad) {
+    extern __shared__ uint32_t cnt[];
+    for (int g = threadIdx.x; g < glen; g += blockDim.x) cnt[g] = 0;
+    __syncthreads();
+    const int chunk = blockIdx.x;
+    const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
+    int flag = 0;
+    // The column bounds of the next cell are fetched while the current one is processed.
+    int64_t lo = 0, hi = 0;
+    if (c_lo < c_hi) {
+        const int c = perm[c_lo];
+        lo = p[c];
+        hi = p[c + 1];
+    }
+    for (int cc = c_lo; cc < c_hi; ++cc) {
+        int64_t nlo = 0, nhi = 0;
+        if (cc + 1 < c_hi) {
+            const int cn = perm[cc + 1];
+            nlo = p[cn];
+            nhi = p[cn + 1];
+        }
+        for (int64_t k = lo + threadIdx.x; k < hi; k += blockDim.x) {
+            const int g = idx[k];
+            if (g < 0 || g >= ngenes || (k > lo && idx[k - 1] >= g)) {
+                flag = 1;
+            } else {
+                const unsigned gl = (unsigned)(g - g0);
+                if (gl < (unsigned)glen) cnt[gl] += 1;
+            }
+        }
+        __syncthreads();
+        lo = nlo;
+        hi = nhi;
+    }
+    if (flag) *bad = 1;
+    for (int g = threadIdx.x; g < glen; g += blockDim.x) table[(size_t)chunk * ngenes + g0 + g] = cnt[g];
+}
+
+// Exclusive scan of the table along chunks for every gene; also records where every
+// combination's segment starts inside the gene's row (seg_off: [C + 1][ngenes]).
+__global__ void k1_scan_table(uint32_t* __restrict__ table, int nchunks, int ngenes, int C,
+                              const int32_t* __restrict__ first_chunk, uint32_t* __restrict__ seg_off,
+                              uint32_t* __restrict__ row_total) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= ngenes) return;
+    uint32_t run = 0;
+    int dc = 0;
+    int next_first = first_chunk[0];
+    for (int k = 0; k < nchunks; ++k) {
+        while (dc <= C && next_first == k) {
+            seg_off[(size_t)dc * ngenes + g] = run;
+            ++dc;
+            next_first = dc <= C ? first_chunk[dc] : -1;
+        }
+        const size_t at = (size_t)k * ngenes + g;
+        const uint32_t v = table[at];
+        table[at] = run;
+        run += v;
+    }
+    while (dc <= C) {
+        seg_off[(size_t)dc * ngenes + g] = run;
+        ++dc;
+    }
+    row_total[g] = run;
+}
+
+// row_ptr[g] = sum of row_total[0..g); one CTA. Also reports nnz of the used cells.
+__global__ void __launch_bounds__(1024) k1_scan_rows(const uint32_t* __restrict__ row_total, int ngenes,
+                                                      int64_t* __restrict__ row_ptr) {
+    __shared__ int64_t part[1024];
+    const int t = threadIdx.x;
+    const int per = (ngenes + 1023) / 1024;
+    const int lo = min(ngenes, t * per), hi = min(ngenes, lo + per);
+    int64_t s = 0;
+    for (int g = lo; g < hi; ++g) s += row_total[g];
+    part[t] = s;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        int64_t v = t >= d ? part[t - d] : 0;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    int64_t run = part[t] - s;
+    for (int g = lo; g < hi; ++g) {
+        row_ptr[g] = run;
+        run += row_total[g];
+    }
+    if (t == 1023) row_ptr[ngenes] = part[1023];
+}
+
+// Pass B: scatter the values. cursor[g] starts at row_ptr[g] + table[chunk][g].
+__global__ void __launch_bounds__(K1_THREADS)
+k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
+           const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen,
+           const uint32_t* __restrict__ table, const int64_t* __restrict__ row_ptr, double* __restrict__ vals) {
+    extern __shared__ uint32_t cursor[];
+    const int chunk = blockIdx.x;
+    for (int g = threadIdx.x; g < glen; g += blockDim.x) {
+        cursor[g] = (uint32_t)(row_ptr[g0 + g] + table[(size_t)chunk * ngenes + g0 + g]);
+    }
+    __syncthreads();
+    const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
+    int64_t lo = 0, hi = 0;
+    if (c_lo < c_hi) {
+        const int c = perm[c_lo];
+        lo = p[c];
+        hi = p[c + 1];
+    }
+    for (int cc = c_lo; cc < c_hi; ++cc) {
+        int64_t nlo = 0, nhi = 0;
+        if (cc + 1 < c_hi) {
+            const int cn = perm[cc + 1];
+            nlo = p[cn];
+            nhi = p[cn + 1];
+        }
+        for (int64_t k = lo + threadIdx.x; k < hi; k += blockDim.x) {
+            const unsigned gl = (unsigned)(idx[k] - g0);
+            const double v = x[k];
+            if (gl < (unsigned)glen) {
+                const uint32_t at = cursor[gl];
+                cursor[gl] = at + 1;
+                vals[at] = v;
+            }
+        }
+        __syncthreads();
+        lo = nlo;
+        hi = nhi;
+    }
+}
+
+}  // namespace
+
+void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayout& L, Transposed& T) {
+    const int ngenes = (int)mat->nrow;
+    const int C = L.C;
+    if (mat->nnz > 4294967295ll) throw Error("matrix has more than 2^32-1 stored entries; split it into row blocks");
+    T.ngenes = ngenes;
+    T.C = C;
+    ctx->table.reserve((size_t)std::max(1, L.nchunks) * ngenes * 4);
+    ctx->seg_off.reserve((size_t)(C + 1) * ngenes * 4);
+    ctx->row_total.reserve((size_t)ngenes * 4 + 4);
+    ctx->row_ptr.reserve((size_t)(ngenes + 1) * 8);
+    ctx->vals.reserve((size_t)std::max<int64_t>(1, mat->nnz) * 8);
+    ctx->flags.reserve(64);
+    T.seg_off = ctx->seg_off.as<uint32_t>();
+    T.row_ptr = ctx->row_ptr.as<int64_t>();
+    T.vals = ctx->vals.as<double>();
+    uint32_t* table = ctx->table.as<uint32_t>();
+    int* bad = ctx->flags.as<int>();
+    SB_CUDA(cudaMemsetAsync(bad, 0, 64, ctx->stream));
+
+    // Genes are handled in ranges whose cursors fit in shared memory (one range for <= ~50k genes).
+    const int max_glen = (int)((ctx->smem_optin - 1024) / 4);
+    const int nranges = std::max(1, (int)ceil_div(ngenes, max_glen));
+    const int glen_all = (int)ceil_div(ngenes, nranges);
+    allow_smem(k1_count, (size_t)glen_all * 4);
+    allow_smem(k1_scatter, (size_t)glen_all * 4);
+
+    if (L.nchunks > 0 && ngenes > 0) {
+        for (int r = 0; r < nranges; ++r) {
+            const int g0 = r * glen_all, glen = std::min(glen_all, ngenes - g0);
+            SB_LAUNCH(ctx, k1_count, L.nchunks, K1_THREADS, (size_t)glen * 4, mat->d_p, mat->d_i, L.d_perm,
+                      L.d_chunk_start, ngenes, g0, glen, table, bad);
+        }
+    }
+    if (ngenes > 0) {
+        SB_LAUNCH(ctx, k1_scan_table, (int)ceil_div(ngenes, 128), 128, 0, table, L.nchunks, ngenes, C, L.d_first_chunk,
+                  ctx->seg_off.as<uint32_t>(), ctx->row_total.as<uint32_t>());
+    }
+    SB_LAUNCH(ctx, k1_scan_rows, 1, 1024, 0, ctx->row_total.as<uint32_t>(), ngenes, ctx->row_ptr.as<int64_t>());
+    if (L.nchunks > 0 && ngenes > 0) {
+        for (int r = 0; r < nranges; ++r) {
+            const int g0 = r * glen_all, glen = std::min(glen_all, ngenes - g0);
+            SB_LAUNCH(ctx, k1_scatter, L.nchunks, K1_THREADS, (size_t)glen * 4, mat->d_p, mat->d_i, mat->d_x, L.d_perm,
+                      L.d_chunk_start, ngenes, g0, glen, table, T.row_ptr, T.vals);
+        }
+    }
+    int h_bad = 0;
+    SB_CUDA(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (h_bad) throw Error("row indices of the sparse matrix must be in range and strictly increasing within a column");
+}
+
+}  // namespace sb

@@ -1,0 +1,237 @@
+"""GPU parity: libscranb200 through the C ABI vs the CPU oracle on the same seeded inputs.
+Integer results (U, tie term, min-rank) must be bit-exact; means and variances are bit-exact too
+(same operation order, no FMA); everything else within 1e-12 relative."""
+import numpy as np
+import pytest
+
+from helpers import all_pairs, as_csc, assert_tables_match, make_matrix
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sb():
+    import scran_b200
+    scran_b200.default_context()
+    return scran_b200
+
+
+# ---------------------------------------------------------------------------------------------
+# compute_blocked_stats_none  (tests/testthat/test-model-var.R:14-57, 97-131, 195-212)
+# ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("sparse", [True, False])
+def test_blocked_stats_bit_exact(sb, oracle_lib, sparse):
+    from oracle import native
+    x = make_matrix(300, 257, seed=11)
+    rng = np.random.default_rng(3)
+    block = rng.integers(0, 5, 257).astype(np.int32)
+    block[::19] = native.NA_INT          # NA block ids are skipped
+    block[block == 4] = 3
+    block[7] = 4                         # a one-cell block; block 5 stays empty
+    m = as_csc(x) if sparse else x
+    mean, var, det = sb.compute_blocked_stats_none(m, block, 6, want_detected=True)
+    rmean, rvar = oracle_lib.blocked_stats(m, block, 6)
+    assert np.array_equal(mean, rmean, equal_nan=True)
+    assert np.array_equal(var, rvar, equal_nan=True)
+    assert np.isnan(mean[:, 5]).all() and np.isnan(var[:, 5]).all() and np.isnan(var[:, 4]).all()
+    for b in range(5):
+        assert np.array_equal(det[:, b], (x[:, block == b] > 0).sum(1))
+    # the reference's own check: equal to rowMeans / rowVars (test-model-var.R:14-30)
+    keep = block == 1
+    assert np.allclose(mean[:, 1], x[:, keep].mean(1), rtol=1e-12, atol=1e-14)
+    assert np.allclose(var[:, 1], x[:, keep].var(1, ddof=1), rtol=1e-10, atol=1e-14)
+
+
+def test_blocked_stats_stored_zeros_follow_sparse_branch(sb, oracle_lib):
+    import scipy.sparse as sp
+    x = make_matrix(50, 120, seed=5)
+    m = as_csc(x)
+    # explicit zeros stay stored: the reference's sparse branch runs them through the update
+    data = m.data.copy()
+    data[::7] = 0.0
+    m2 = sp.csc_matrix((data, m.indices, m.indptr), shape=m.shape)
+    block = (np.arange(120) % 3).astype(np.int32)
+    mean, var = sb.compute_blocked_stats_none(m2, block, 3)
+    rmean, rvar = oracle_lib.blocked_stats(m2, block, 3)
+    assert np.array_equal(mean, rmean, equal_nan=True)
+    assert np.array_equal(var, rvar, equal_nan=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# overlap_exprs_paired / overlap_exprs  (tests/testthat/test-pairwise-wilcox.R:4-60, 160-175)
+# ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("lfc", [0.0, 0.5, -1.0, 1.0, 1.7])
+@pytest.mark.parametrize("sparse", [True, False])
+def test_overlap_paired_exact(sb, oracle_lib, port_lib, lfc, sparse):
+    x = make_matrix(200, 311, seed=21)
+    rng = np.random.default_rng(9)
+    g = rng.integers(0, 6, 311)
+    groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(5)]  # group 5: cells in no group
+    groups.append(np.zeros(0, np.int32))                                    # an empty group
+    left, right = all_pairs(6)
+    m = as_csc(x) if sparse else x
+    u, t = sb.overlap_exprs_paired(m, left, right, groups, lfc, want_ties=True)
+    ru = oracle_lib.overlap_paired(m, left, right, groups, lfc)
+    assert np.array_equal(u, ru)
+    pu, pt = port_lib.overlap_paired(m, left, right, groups, lfc, want_ties=True)
+    keep = np.array([len(groups[a - 1]) > 0 and len(groups[b - 1]) > 0 for a, b in zip(left, right)])
+    assert np.array_equal(t[:, keep], pt[:, keep])
+
+
+def test_overlap_paired_matches_scipy(sb):
+    import scipy.stats as st
+    x = make_matrix(60, 150, seed=2)
+    g = np.arange(150) % 3
+    groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(3)]
+    u = sb.overlap_exprs_paired(as_csc(x), [1, 3], [2, 1], groups)
+    for k, (a, b) in enumerate([(0, 1), (2, 0)]):
+        ref = [st.mannwhitneyu(x[r, groups[a]], x[r, groups[b]]).statistic for r in range(60)]
+        assert np.array_equal(u[:, k], np.array(ref))
+
+
+@pytest.mark.parametrize("lfc", [0.0, 0.7])
+def test_overlap_exprs_exact(sb, oracle_lib, lfc):
+    x = make_matrix(120, 203, seed=33)
+    g = np.random.default_rng(4).integers(0, 4, 203)
+    groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(4)]
+    groups.insert(2, np.zeros(0, np.int32))
+    U, T = sb.overlap_exprs(as_csc(x), groups, lfc)
+    rU, rT = oracle_lib.overlap(as_csc(x), groups, lfc)
+    assert np.array_equal(U, rU, equal_nan=True)
+    assert np.array_equal(T, rT, equal_nan=True)
+
+
+def test_overlap_out_of_range_message(sb):
+    x = make_matrix(10, 20, seed=1)
+    with pytest.raises(sb.ScranB200Error, match="indices in 'groups' out of range"):
+        sb.overlap_exprs_paired(x, [1], [2], [np.array([0, 1]), np.array([2, 20])])
+
+
+def test_overlap_large_units(sb, port_lib):
+    """Units beyond the shared-memory sort capacity (global-memory sort) and beyond 65536
+    entries (64-bit count table)."""
+    rng = np.random.default_rng(77)
+    ncells = 150000
+    x = np.zeros((4, ncells))
+    x[0] = np.where(rng.random(ncells) < 0.6, np.log2(1 + rng.poisson(3, ncells) + rng.random(ncells)), 0)
+    x[1] = np.where(rng.random(ncells) < 0.2, rng.poisson(2, ncells), 0)          # ties, > cap
+    x[2] = np.where(rng.random(ncells) < 0.03, rng.random(ncells), 0)             # fits shared memory
+    x[3] = 1.0 + 1e-13 * rng.integers(0, 1000, ncells)                             # equal high words
+    g = rng.integers(0, 3, ncells)
+    groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(3)]
+    left, right = all_pairs(3)
+    for lfc in (0.0, 0.25):
+        u, t = sb.overlap_exprs_paired(as_csc(x), left, right, groups, lfc, want_ties=True)
+        pu, pt = port_lib.overlap_paired(as_csc(x), left, right, groups, lfc, want_ties=True)
+        assert np.array_equal(u, pu)
+        assert np.array_equal(t, pt)
+
+
+# ---------------------------------------------------------------------------------------------
+# computeMinRank
+# ---------------------------------------------------------------------------------------------
+
+def test_compute_min_rank(sb):
+    from oracle import rlevel
+    rng = np.random.default_rng(8)
+    x = rng.normal(size=(500, 7))
+    x[::5, 2] = np.nan
+    x[10:40, 3] = 0.25          # ties
+    x[3, :] = np.nan            # a row with no value
+    got = sb.compute_min_rank(x)
+    want = rlevel.compute_min_rank(x)
+    assert np.array_equal(got.astype(np.int64), want)
+
+
+def test_compute_min_rank_many_rows(sb):
+    from oracle import rlevel
+    rng = np.random.default_rng(18)
+    x = np.round(rng.normal(size=(40000, 3)), 2)   # beyond the shared-memory sort, many ties
+    assert np.array_equal(sb.compute_min_rank(x).astype(np.int64), rlevel.compute_min_rank(x))
+
+
+# ---------------------------------------------------------------------------------------------
+# scoreMarkers  (tests/testthat/test-score-markers.R)
+# ---------------------------------------------------------------------------------------------
+
+def _score_both(sb, x, groups, **kw):
+    from oracle import native, rlevel
+    got = sb.score_markers(as_csc(x), groups, **kw)
+    want = rlevel.score_markers(as_csc(x), groups, lib=native.load("best"), **kw)
+    return got, want
+
+
+@pytest.mark.parametrize("full", [False, True])
+def test_score_markers_unblocked(sb, full):
+    x = make_matrix(400, 300, seed=101)
+    groups = np.random.default_rng(1).integers(0, 5, 300)
+    got, want = _score_both(sb, x, groups, full_stats=full)
+    assert_tables_match(got, want)
+
+
+def test_score_markers_dense_equals_sparse(sb):
+    x = make_matrix(150, 200, seed=102)
+    groups = np.arange(200) % 4
+    a = sb.score_markers(x, groups)
+    b = sb.score_markers(as_csc(x), groups)
+    for g in a:
+        for c in a[g]:
+            assert np.array_equal(a[g][c], b[g][c], equal_nan=True)
+
+
+def test_score_markers_character_groups_and_lfc(sb):
+    x = make_matrix(250, 260, seed=103)
+    labels = np.array(["b", "a", "d", "c"])[np.random.default_rng(2).integers(0, 4, 260)]
+    got, want = _score_both(sb, x, list(labels), lfc=0.5, full_stats=True)
+    assert_tables_match(got, want)
+
+
+def test_score_markers_blocked(sb):
+    x = make_matrix(300, 400, seed=104)
+    rng = np.random.default_rng(3)
+    groups = rng.integers(0, 4, 400)
+    block = rng.integers(0, 3, 400)
+    got, want = _score_both(sb, x, groups, block=block, full_stats=True)
+    assert_tables_match(got, want, skip_selfother=True)
+
+
+def test_score_markers_blocked_lfc_missing_combinations(sb):
+    """Group-specific batches: some pairs never share a block -> NaN columns
+    (test-score-markers.R:259-344)."""
+    x = make_matrix(200, 360, seed=105)
+    rng = np.random.default_rng(4)
+    groups = rng.integers(0, 4, 360)
+    block = rng.integers(0, 3, 360)
+    block[groups == 3] = 2          # group 3 only in block 2
+    block[(groups == 0) & (block == 2)] = 0   # group 0 never in block 2
+    got, want = _score_both(sb, x, groups, block=block, lfc=0.3, full_stats=True)
+    assert_tables_match(got, want, skip_selfother=True)
+    assert np.isnan(got[0]["full.AUC"][:, list(got[0]["full.AUC.right"]).index(3)]).all()
+
+
+def test_score_markers_pairings(sb):
+    x = make_matrix(180, 240, seed=106)
+    groups = np.random.default_rng(5).integers(0, 5, 240)
+    for pairings in ([1, 3, 4], ([0, 1], [2, 3, 4]), np.array([[0, 1], [2, 1], [4, 0]])):
+        got, want = _score_both(sb, x, groups, pairings=pairings, full_stats=True)
+        assert_tables_match(got, want)
+
+
+def test_score_markers_many_groups(sb):
+    """More labels than one warp of count lanes (G + 1 > 32)."""
+    x = make_matrix(120, 2000, seed=107, rate=1.0)
+    groups = np.random.default_rng(6).integers(0, 40, 2000)
+    got, want = _score_both(sb, x, groups)
+    assert_tables_match(got, want)
+
+
+def test_score_markers_one_cell_groups(sb):
+    """A group with a single cell: variance NA, so Cohen's d is NA unless the difference is 0
+    (R/scoreMarkers.R:417-426); AUC and logFC.detected stay defined."""
+    x = make_matrix(100, 90, seed=108)
+    groups = np.arange(90) % 3
+    groups[0] = 3
+    got, want = _score_both(sb, x, groups, full_stats=True)
+    assert_tables_match(got, want)
