@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""bench.py - scoreMarkers throughput on B200 (BASELINE.json metric: gene·pair scores/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload config3] [--impl ours|reference]
+
+One "step" = one full scoreMarkers pass (transpose -> blocked stats -> sort + U count -> effects
+-> summaries -> min-rank, plus the exchange when N > 1) over one synthetic matrix of the named
+config. For N > 1 launch under torchrun (one rank per GPU); the genes of the SAME matrix are
+sharded over the ranks (strong scaling), which is BASELINE.json's "gene-sharded over 8xB200".
+
+Prints ONE JSON line on rank 0. `value` = gene·pairs / s with inputs resident in HBM; `e2e` = the
+same through the host-buffer C-ABI call (H2D of the CSC arrays and D2H of the result tables
+inside the timed region); `roofline` = the dominant kernel phase against the measured HBM peak;
+`cpu_baseline` = the CPU oracle (the reference's own object code when oracle/_ref is present)
+timed on a bounded gene sample of the same workload on this box's host cores.
+
+--impl reference times that CPU path alone with all host threads (R + BiocParallel cannot run:
+R is not installed on either machine).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: genes, cells, groups, batches, density, seed (1000 + config id)
+    "config1": dict(ngenes=10000, ncells=3000, G=10, B=1, density=0.63, seed=1001),
+    "config2": dict(ngenes=33538, ncells=100000, G=20, B=4, density=0.07, seed=1002),
+    "config3": dict(ngenes=33538, ncells=1300000, G=50, B=8, density=0.07, seed=1003),
+    "config5": dict(ngenes=20000, ncells=500000, G=200, B=1, density=0.07, seed=1005),
+    "tiny": dict(ngenes=2000, ncells=20000, G=8, B=2, density=0.07, seed=1999),
+}
+PHASES = ["transpose", "stats", "sort", "count", "effects", "summaries", "minrank"]
+
+
+def labels_for(w):
+    """Uniform group and batch labels with every combination non-empty."""
+    rng = np.random.default_rng(w["seed"])
+    groups = rng.integers(0, w["G"], w["ncells"]).astype(np.int32)
+    block = rng.integers(0, w["B"], w["ncells"]).astype(np.int32)
+    k = 0
+    for g in range(w["G"]):
+        for b in range(w["B"]):
+            groups[k], block[k] = g, b
+            k += 1
+    return groups, (block if w["B"] > 1 else None)
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (profiling recipe's line)."""
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [s for s in sm if s > 0]
+        return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(w, nnz, P, K):
+    """what one pass must move at least, in bytes."""
+    E = 3 * w["ngenes"] * P * 8
+    S = w["ngenes"] * K * 19 * 8
+    return nnz * 12 + (w["ncells"] + 1) * 8 + w["ncells"] * 4 + 2 * E + S
+
+
+def phase_bytes(w, nnz, plan):
+    """Algorithmic bytes per kernel phase."""
+    ng, C, PB, Q, K = w["ngenes"], plan.C, plan.npairs, plan.Q, plan.K
+    return {
+        "transpose": nnz * (4 + 12) + nnz * 8,          # count pass reads row indices, scatter reads 12 B, writes 8 B
+        "stats": nnz * 8 + 3 * ng * C * 8,
+        "sort": nnz * 8 + nnz * 2,                      # values in, 2-byte label stream out
+        "count": nnz * 2 + ng * PB * 8,                 # label stream in, U per block-level pair out
+        "effects": ng * PB * 8 + 3 * ng * C * 8 + 3 * ng * Q * 8,
+        "summaries": 3 * ng * Q * 8 + ng * K * 16 * 8,
+        "minrank": 3 * ng * Q * 8 + ng * K * 3 * 4 * 2,
+    }
+
+
+def cpu_sample(w, groups, block, ctx, nsample, threads):
+    """Times the CPU oracle on `nsample` genes x all cells of the same synthetic workload."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    import scipy.sparse as sp
+
+    import scran_b200
+    from oracle import native, rlevel
+    lib = native.load("best")
+    g0 = min(1000, max(0, w["ngenes"] - nsample))
+    m = scran_b200.DeviceMatrix.synthetic(ctx, w["ngenes"], g0, g0 + nsample, w["ncells"], groups, w["G"], w["density"],
+                                          w["seed"])
+    p, i, x = m.download()
+    m.free()
+    full = sp.csc_matrix((x, i, p), shape=(nsample, w["ncells"]))
+    st = rlevel.ScoreSetup(groups.tolist(), None if block is None else block.tolist(), None, 0.0)
+    parts = np.array_split(np.arange(nsample), threads)
+    rows = full.tocsr()
+    pieces = [rows[idx].tocsc() for idx in parts if len(idx)]
+
+    def work(piece):  # what one rowBlockApply worker does (R/scoreMarkers.R:351-366)
+        lib.blocked_stats(piece, st.comb_id.astype(np.int32), len(st.combos))
+        lib.overlap_paired(piece, st.left + 1, st.right + 1, st.involved, 0.0)
+
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(work, pieces))
+    dt = time.perf_counter() - t0
+    return dt, lib.kind, nsample
+
+
+def run_reference(args, w):
+    """--impl reference: the reference's CPU path on the host cores, bounded sample per step."""
+    import scran_b200
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    groups, block = labels_for(w)
+    ctx = scran_b200.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    threads = os.cpu_count() or 1
+    P = w["G"] * (w["G"] - 1) // 2
+    per_gene = {"config3": 0.09, "config5": 0.12, "config2": 0.006}.get(args.workload, 0.001)
+    nsample = int(max(threads, min(w["ngenes"], threads * max(1, int(6.0 / per_gene)))))
+    nsample = min(nsample, 4096)
+    times = []
+    for s in range(args.warmup + args.steps):
+        dt, kind, n = cpu_sample(w, groups, block, ctx, nsample, threads)
+        if s >= args.warmup:
+            times.append(dt)
+    t = float(np.mean(times))
+    value = nsample * P / t
+    line = {
+        "impl": "reference", "metric": "scoreMarkers gene·pair scores/sec", "value": value, "unit": "gene·pairs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, **{k: w[k] for k in ("ngenes", "ncells", "G", "B", "density")}},
+        "cpu_baseline": {"value": value, "unit": "gene·pairs/s", "cores": threads,
+                         "kind": "reference" if kind == "ref" else "port",
+                         "sample": "%d genes x all %d cells per step, native kernels only (blocked stats + U for every "
+                                   "block-level pair), %d threads" % (nsample, w["ncells"], threads)},
+        "e2e": {"value": value, "unit": "gene·pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "R + BiocParallel unavailable on this box; this is the reference's own C++ compiled unmodified "
+                "(oracle/_ref) when kind=reference, else the C port",
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=os.environ.get("SCRANB200_WORKLOAD", "config3"))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-genes", type=int, default=0, help="genes in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    w = dict(WORKLOADS[args.workload])
+    args.warmup = max(args.warmup, 0)
+
+    if args.impl == "reference":
+        run_reference(args, w)
+        return
+
+    import torch
+
+    import scran_b200
+    from scran_b200._lib import check, lib, ptr
+    from scran_b200.distributed import ShardedScorer, shard_ranges
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx = scran_b200.Context(local)
+    groups, block = labels_for(w)
+    granges, per = shard_ranges(w["ngenes"], world)
+    g0, g1 = granges[rank]
+    t_gen = time.perf_counter()
+    mat = scran_b200.DeviceMatrix.synthetic(ctx, w["ngenes"], g0, g1, w["ncells"], groups, w["G"], w["density"], w["seed"])
+    t_gen = time.perf_counter() - t_gen
+    nnz_local = mat.nnz
+    nnz_t = torch.tensor([nnz_local], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(nnz_t)
+    nnz = int(nnz_t.item())
+
+    plan = scran_b200.ScorePlan(groups.tolist(), None if block is None else block.tolist(), None, 0.0, ctx=ctx)
+    scorer = ShardedScorer(ctx, plan, w["ngenes"], rank, world, dist)
+    P = w["G"] * (w["G"] - 1) // 2
+    gene_pairs = w["ngenes"] * P
+    ext = torch.cuda.ExternalStream(lib().scranb200_ctx_stream(ctx.handle), device=torch.device("cuda", local))
+
+    for _ in range(args.warmup):
+        scorer.step(mat)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    phase_ms = {k: 0.0 for k in PHASES}
+    ev0.record(ext)
+    for _ in range(args.steps):
+        scorer.step(mat)
+        for k in PHASES:
+            phase_ms[k] += scorer.last_timing.get(k, 0.0)
+    ev1.record(ext)
+    barrier()
+    launches = ctx.launches - launches0
+    ms_total = ev0.elapsed_time(ev1)
+    t_ms = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms_step = float(t_ms.item()) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    for k in PHASES:
+        phase_ms[k] /= args.steps
+    value = gene_pairs / (ms_step * 1e-3)
+
+    # ---- end to end through the host-buffer C-ABI call --------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        p_h, i_h, x_h = mat.download()
+        mat.free()
+        del scorer
+        torch.cuda.empty_cache()
+        pin = [torch.from_numpy(a).pin_memory() for a in (p_h, i_h, x_h)]
+        del p_h, i_h, x_h
+        nrow = g1 - g0
+        out_h = torch.empty((max(1, plan.K), 19, nrow), dtype=torch.float64).pin_memory()
+        L = lib()
+
+        def e2e_step():
+            import ctypes as C
+            h = C.c_void_p()
+            check(L.scranb200_upload_csc(ctx.handle, nrow, w["ncells"], ptr(pin[0]), ptr(pin[1]), ptr(pin[2]), C.byref(h)))
+            try:
+                check(L.scranb200_score_markers(ctx.handle, h, plan.handle, ptr(out_h), None))
+            finally:
+                L.scranb200_mat_free(h)
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        n_e2e = max(1, min(args.steps, 2))
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        dt = (time.perf_counter() - t0) / n_e2e
+        t_e = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+        h2d = sum(int(a.numel() * a.element_size()) for a in pin)
+        d2h = int(out_h.numel() * 8)
+        # N > 1: every rank scores its own gene shard end to end; ranks are local (min-rank over the shard),
+        # so the multi-GPU e2e figure is the per-shard pipeline, stated here rather than hidden.
+        e2e = {"value": gene_pairs / float(t_e.item()), "unit": "gene·pairs/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": float(t_e.item()) * 1e3,
+               "call": "scranb200_upload_csc + scranb200_score_markers (host buffers, pinned)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    pb = phase_bytes(w, nnz, plan)
+    dom = max(PHASES, key=lambda k: phase_ms[k])
+    kernels = {}
+    for k in PHASES:
+        ms = phase_ms[k]
+        gbs = (pb[k] / world) / (ms * 1e-3) / 1e9 if ms > 0 else None
+        kernels[k] = {"ms": round(ms, 4), "alg_bytes": int(pb[k] / world),
+                      "gbs": None if gbs is None else round(gbs, 1), "frac": None if gbs is None else round(gbs / peak, 4)}
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",
+                "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                "pipeline_alg_bytes": int(algorithmic_bytes(w, nnz, P, plan.K)),
+                "pipeline_frac": round(algorithmic_bytes(w, nnz, P, plan.K) / (ms_step * 1e-3) / 1e9 / (peak * world), 4)}
+
+    cpu = None
+    if not args.no_cpu and world == 1:
+        threads = os.cpu_count() or 1
+        per_gene = {"config3": 0.09, "config5": 0.12, "config2": 0.006}.get(args.workload, 0.001)
+        nsample = args.cpu_genes or int(max(4, min(w["ngenes"], 15.0 / per_gene)))
+        nsample = min(nsample, 1024)
+        dt, kind, n = cpu_sample(w, groups, block, ctx, nsample, 1)
+        cpu = {"value": n * P / dt, "unit": "gene·pairs/s", "cores": 1, "kind": "reference" if kind == "ref" else "port",
+               "sample": "%d genes x all %d cells, native kernels only (blocked stats + U for %d block-level pairs), "
+                         "%.1f s" % (n, w["ncells"], plan.npairs, dt),
+               "host_cores_available": threads}
+
+    line = {
+        "metric": "scoreMarkers gene·pair scores/sec", "value": value, "unit": "gene·pairs/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, **{k: w[k] for k in ("ngenes", "ncells", "G", "B", "density")},
+                   "nnz": nnz, "pairs": P, "block_level_pairs": plan.npairs, "sharding": "genes x%d" % world,
+                   "l2": "inputs (%.1f GB) larger than L2" % (nnz * 12 / 1e9)},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
+        "cpu_baseline": cpu, "synth_seconds": round(t_gen, 2),
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

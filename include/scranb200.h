@@ -106,7 +106,8 @@ int scranb200_overlap_exprs(scranb200_ctx* ctx, const scranb200_mat* mat, int ng
  * des_left/des_right: the desired comparisons as group indices, in the order
  *         .expand_pairings gives them (R/expandPairings.R:1-58); nullable = all ordered pairs
  *         of the ngroups groups in expand.grid order (first index fastest).
- * A "score plan" holds the bookkeeping of R/scoreMarkers.R:196-217, 293-345, 463-521. */
+ * A "score plan" holds the bookkeeping of R/scoreMarkers.R:196-217, 293-345, 463-521.
+ * ctx may be null: the plan is then host-only (plan_info / plan_tables work, compute calls refuse it). */
 typedef struct scranb200_plan scranb200_plan;
 
 int scranb200_plan_create(scranb200_ctx* ctx, int64_t ncells, const int32_t* groups, int ngroups,
@@ -121,6 +122,15 @@ int scranb200_plan_info(const scranb200_plan* plan, int64_t* info, int n);
  * (mcols(full)$weight, R/scoreMarkers.R:487, 571-574). Any pointer may be null. */
 int scranb200_plan_tables(const scranb200_plan* plan, int32_t* out_groups, int64_t* right_ptr,
                           int32_t* right_group, double* weight);
+
+/* The plan's internals, for checking the bookkeeping against R/scoreMarkers.R:293-345, 463-521:
+ * combinations (group, block index, cells), block-level pairs (0-based combination ids), the
+ * averaged comparisons with their fold lists, per desired comparison the direct / flipped
+ * averaged comparison (-1 = none), and each cell's combination (-1 = dropped). Sizes from
+ * scranb200_plan_info; any pointer may be null. */
+int scranb200_plan_pairs(const scranb200_plan* plan, int32_t* comb_group, int32_t* comb_block, double* ncells_comb,
+                         int32_t* left, int32_t* right, int32_t* avg_left, int32_t* avg_right, int32_t* avg_ptr,
+                         int32_t* avg_idx, int32_t* q_direct, int32_t* q_flipped, int32_t* comb_id);
 
 #define SCRANB200_NCOLS 19 /* self.average, other.average, self.detected, other.detected, then
                               {mean,min,median,max,rank} x {logFC.cohen, AUC, logFC.detected}:

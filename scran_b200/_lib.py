@@ -53,6 +53,7 @@ def _signatures():
         "scranb200_plan_destroy": (None, [c_plan]),
         "scranb200_plan_info": (C.c_int, [c_plan, _p, C.c_int]),
         "scranb200_plan_tables": (C.c_int, [c_plan, _p, _p, _p, _p]),
+        "scranb200_plan_pairs": (C.c_int, [c_plan] + [_p] * 12),
         "scranb200_score_markers": (C.c_int, [c_ctx, c_mat, c_plan, _p, _p]),
         "scranb200_score_effects_dev": (C.c_int, [c_ctx, c_mat, c_plan, i64, i64, _p, _p]),
         "scranb200_score_minrank_dev": (C.c_int, [c_ctx, c_plan, i64, i64, _p, i64, i64, _p]),

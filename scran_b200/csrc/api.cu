@@ -161,6 +161,7 @@ void run_pairs(scranb200_ctx* ctx, const scranb200_mat* mat, PairLayout& L, DevB
 void score_stage1(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan, int64_t ld, int64_t row0,
                   double* d_eff, double* d_out) {
     if (mat->ncol != plan->ncells) throw Error("plan was built for a different number of cells");
+    if (plan->ctx != ctx) throw Error("plan was built without or for another context");
     PairLayout& L = const_cast<PairLayout&>(plan->layout);
     run_pairs(ctx, mat, L, const_cast<DevBuf&>(plan->d_layout), true, plan->lfc, true, false);
     run_effects(ctx, *plan, (int)mat->nrow, ld, row0, ctx->mean.as<double>(), ctx->var.as<double>(),
@@ -459,11 +460,11 @@ int scranb200_plan_create(scranb200_ctx* ctx, int64_t ncells, const int32_t* gro
                           const int32_t* block, const int32_t* des_left, const int32_t* des_right,
                           int64_t ndesired, double lfc, scranb200_plan** out) {
     API_BEGIN
-    ctx_guard(ctx);
+    if (ctx) ctx_guard(ctx);  // a null context gives a host-only plan (bookkeeping tests without a GPU)
     scranb200_plan* P = new scranb200_plan();
     try {
         build_plan(*P, ncells, groups, ngroups, block, des_left, des_right, ndesired, lfc);
-        upload_plan(ctx, *P);
+        if (ctx) upload_plan(ctx, *P);
     } catch (...) {
         delete P;
         throw;
@@ -611,3 +612,40 @@ int scranb200_compute_min_rank(scranb200_ctx* ctx, const double* x, int64_t nrow
 }
 
 }  // extern "C"
+
+// Host-only view of a plan's block-level pairs and averaging map (bookkeeping tests).
+extern "C" int scranb200_plan_pairs(const scranb200_plan* plan, int32_t* comb_group, int32_t* comb_block,
+                                    double* ncells_comb, int32_t* left, int32_t* right, int32_t* avg_left,
+                                    int32_t* avg_right, int32_t* avg_ptr, int32_t* avg_idx, int32_t* q_direct,
+                                    int32_t* q_flipped, int32_t* comb_id) {
+    try {
+        for (int c = 0; c < plan->C; ++c) {
+            if (comb_group) comb_group[c] = plan->comb_group[c];
+            if (comb_block) comb_block[c] = plan->comb_block[c];
+            if (ncells_comb) ncells_comb[c] = plan->ncells_comb[c];
+        }
+        for (size_t k = 0; k < plan->left.size(); ++k) {
+            if (left) left[k] = plan->left[k];
+            if (right) right[k] = plan->right[k];
+            if (avg_idx) avg_idx[k] = plan->avg_idx[k];
+        }
+        for (int q = 0; q < plan->Q; ++q) {
+            if (avg_left) avg_left[q] = plan->avg_left[q];
+            if (avg_right) avg_right[q] = plan->avg_right[q];
+        }
+        for (int q = 0; q <= plan->Q; ++q) {
+            if (avg_ptr) avg_ptr[q] = plan->avg_ptr[q];
+        }
+        for (int64_t j = 0; j < plan->ndesired; ++j) {
+            if (q_direct) q_direct[j] = plan->q_direct[j];
+            if (q_flipped) q_flipped[j] = plan->q_flipped[j];
+        }
+        if (comb_id) {
+            for (int64_t c = 0; c < plan->ncells; ++c) comb_id[c] = plan->comb_id[c];
+        }
+    } catch (const std::exception& e) {
+        sb::set_last_error(e.what());
+        return 1;
+    }
+    return 0;
+}

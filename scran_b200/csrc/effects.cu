@@ -24,6 +24,11 @@ struct DD {
 };
 __device__ inline void dd_add(DD& s, double x) {  // s += x, error-free (Knuth two-sum)
     const double t = s.hi + x;
+    if (isinf(t) || isnan(t)) {  // infinite effects (zero variance) propagate like a plain sum
+        s.hi = t;
+        s.lo = 0.0;
+        return;
+    }
     const double bp = t - s.hi;
     const double err = (s.hi - (t - bp)) + (x - bp);
     s.hi = t;

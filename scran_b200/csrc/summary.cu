@@ -22,8 +22,13 @@ namespace {
 struct DD {
     double hi, lo;
 };
-__device__ inline void dd_add(DD& s, double x) {
+__device__ inline void dd_add(DD& s, double x) {  // s += x, error-free (Knuth two-sum)
     const double t = s.hi + x;
+    if (isinf(t) || isnan(t)) {  // infinite effects (zero variance) propagate like a plain sum
+        s.hi = t;
+        s.lo = 0.0;
+        return;
+    }
     const double bp = t - s.hi;
     const double err = (s.hi - (t - bp)) + (x - bp);
     s.hi = t;
@@ -78,7 +83,7 @@ __global__ void __launch_bounds__(SUM_WARPS * 32) k5_summaries(SumParams P) {
             const double oh = __shfl_down_sync(0xffffffffu, sum.hi, o);
             const double ol = __shfl_down_sync(0xffffffffu, sum.lo, o);
             dd_add(sum, oh);
-            sum.lo += ol;
+            if (!isinf(sum.hi) && !isnan(sum.hi)) sum.lo += ol;
             mn = fmin(mn, __shfl_down_sync(0xffffffffu, mn, o));
             mx = fmax(mx, __shfl_down_sync(0xffffffffu, mx, o));
             cnt += __shfl_down_sync(0xffffffffu, cnt, o);
