@@ -110,43 +110,59 @@ __global__ void __launch_bounds__(256) k4_effects(EffParams P) {
 }
 
 struct SelfParams {
-    int ngenes, K;
+    int ngenes, K, C, ngroups;
     int64_t ld, row0;
     const double *mean, *ndet;  // [C][ngenes]
     const double* ncells;
     const int32_t *out_group, *proj_ptr, *proj_comb, *other_ptr, *other_group;
     const double* proj_coef;
     int blocked;
-    double* out;  // [K][19][ld]
+    double* logit;    // [C][ngenes]: logit of the shrunken detected fraction (blocked only)
+    double* grp_avg;  // [2][ngroups][ngenes]: per-group average and detected fraction
+    double* out;      // [K][19][ld]
 };
 
-__device__ inline double group_value(const SelfParams& P, int grp, int g, bool detected) {
+// scuttle::correctGroupSummary(transform="logit"): (p + 0.01) / 1.02, then log(x / (1 - x)).
+__global__ void __launch_bounds__(256) k4_logit(SelfParams P) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)P.ngenes * P.C) return;
+    const int c = (int)(t / P.ngenes);
+    const double prop = P.ndet[t] / P.ncells[c];
+    const double x = (prop + 0.01) / (1.0 + 2.0 * 0.01);
+    P.logit[t] = log(x / (1.0 - x));
+}
+
+// One value per (gene, group): the group's own summary when there is no blocking, else the
+// group coefficient of the weighted fit (a fixed projector row applied to the C summaries).
+__global__ void __launch_bounds__(256) k4_group_avg(SelfParams P) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)P.ngenes * P.ngroups) return;
+    const int g = (int)(t % P.ngenes), grp = (int)(t / P.ngenes);
     const int a = P.proj_ptr[grp], b = P.proj_ptr[grp + 1];
-    if (!P.blocked) {  // one combination per group: the summary itself
-        const int c = P.proj_comb[a];
-        return detected ? P.ndet[(size_t)c * P.ngenes + g] / P.ncells[c] : P.mean[(size_t)c * P.ngenes + g];
-    }
-    DD s = {0.0, 0.0};
-    for (int k = a; k < b; ++k) {
-        const int c = P.proj_comb[k];
-        double y;
-        if (detected) {
-            const double prop = P.ndet[(size_t)c * P.ngenes + g] / P.ncells[c];
-            const double x = (prop + 0.01) / (1.0 + 2.0 * 0.01);
-            y = log(x / (1.0 - x));
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    double avg = nan, det = nan;
+    if (b > a) {
+        if (!P.blocked) {
+            const int c = P.proj_comb[a];
+            avg = P.mean[(size_t)c * P.ngenes + g];
+            det = P.ndet[(size_t)c * P.ngenes + g] / P.ncells[c];
         } else {
-            y = P.mean[(size_t)c * P.ngenes + g];
+            DD sa = {0.0, 0.0}, sd = {0.0, 0.0};
+            for (int k = a; k < b; ++k) {
+                const size_t at = (size_t)P.proj_comb[k] * P.ngenes + g;
+                const double w = P.proj_coef[k];
+                dd_add(sa, w * P.mean[at]);
+                dd_add(sd, w * P.logit[at]);
+            }
+            avg = dd_value(sa);
+            double v = exp(dd_value(sd));
+            v = v / (v + 1.0);
+            v = v * (1.0 + 2.0 * 0.01) - 0.01;
+            det = fmin(fmax(v, 0.0), 1.0);
         }
-        dd_add(s, P.proj_coef[k] * y);
     }
-    double v = dd_value(s);
-    if (detected) {
-        v = exp(v);
-        v = v / (v + 1.0);
-        v = v * (1.0 + 2.0 * 0.01) - 0.01;
-        v = fmin(fmax(v, 0.0), 1.0);
-    }
-    return v;
+    P.grp_avg[(size_t)grp * P.ngenes + g] = avg;
+    P.grp_avg[((size_t)P.ngroups + grp) * P.ngenes + g] = det;
 }
 
 __global__ void __launch_bounds__(256) k4_selfother(SelfParams P) {
@@ -155,13 +171,12 @@ __global__ void __launch_bounds__(256) k4_selfother(SelfParams P) {
     const int g = (int)(t % P.ngenes), k = (int)(t / P.ngenes);
     const int grp = P.out_group[k];
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
-    const bool has_self = P.proj_ptr[grp + 1] > P.proj_ptr[grp];
     for (int which = 0; which < 2; ++which) {
-        const bool det = which == 1;
-        const double self = has_self ? group_value(P, grp, g, det) : nan;
+        const double* src = P.grp_avg + (size_t)which * P.ngroups * P.ngenes;
+        const double self = src[(size_t)grp * P.ngenes + g];
         DD s = {0.0, 0.0};
         const int o0 = P.other_ptr[k], o1 = P.other_ptr[k + 1];
-        for (int o = o0; o < o1; ++o) dd_add(s, group_value(P, P.other_group[o], g, det));
+        for (int o = o0; o < o1; ++o) dd_add(s, src[(size_t)P.other_group[o] * P.ngenes + g]);
         const double other = o1 > o0 ? dd_value(s) / (double)(o1 - o0) : nan;
         double* base = P.out + ((size_t)k * SCRANB200_NCOLS + 2 * which) * P.ld + P.row0 + g;
         base[0] = self;
@@ -199,6 +214,8 @@ void run_effects(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int64_
         SelfParams sp;
         sp.ngenes = ngenes;
         sp.K = P.K;
+        sp.C = P.C;
+        sp.ngroups = P.ngroups;
         sp.ld = ld;
         sp.row0 = row0;
         sp.mean = d_mean;
@@ -211,7 +228,16 @@ void run_effects(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int64_
         sp.other_group = P.d_other_group;
         sp.proj_coef = P.d_proj_coef;
         sp.blocked = P.blocked ? 1 : 0;
+        ctx->grp_avg.reserve((size_t)2 * P.ngroups * ngenes * 8);
+        sp.grp_avg = ctx->grp_avg.as<double>();
+        sp.logit = nullptr;
+        if (P.blocked) {
+            ctx->logit.reserve((size_t)P.C * ngenes * 8);
+            sp.logit = ctx->logit.as<double>();
+            SB_LAUNCH(ctx, k4_logit, (unsigned)ceil_div((int64_t)ngenes * P.C, 256), 256, 0, sp);
+        }
         sp.out = d_out;
+        SB_LAUNCH(ctx, k4_group_avg, (unsigned)ceil_div((int64_t)ngenes * P.ngroups, 256), 256, 0, sp);
         SB_LAUNCH(ctx, k4_selfother, (unsigned)ceil_div((int64_t)ngenes * P.K, 256), 256, 0, sp);
     }
 }

@@ -88,6 +88,7 @@ void build_layout(const int32_t* comb_id, int64_t ncells, int C, const int32_t* 
     // Chunks: about target_chunks of them, none straddling a combination.
     const int64_t used = start[C];
     int64_t chunk_cols = std::max<int64_t>(1, ceil_div(used, std::max(1, target_chunks)));
+    chunk_cols = std::min<int64_t>(chunk_cols, MAX_CHUNK_COLS);
     L.first_chunk.assign(C + 1, 0);
     L.chunk_start.clear();
     for (int d = 0; d < C; ++d) {

@@ -10,6 +10,8 @@
 
 namespace sb {
 
+constexpr int MAX_CHUNK_COLS = 2048;  // the transpose stages a chunk's column bounds in shared memory
+
 struct PairLayout {
     int64_t ncells = 0;
     int C = 0;  // combinations as the caller numbers them

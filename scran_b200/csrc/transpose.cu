@@ -18,44 +18,109 @@ namespace sb {
 namespace {
 
 constexpr int K1_THREADS = 1024;
+constexpr int K1_R = 3;          // elements per thread held in registers per column (covers 3072 per column)
+constexpr int K1_MAXCOLS = MAX_CHUNK_COLS;  // columns per chunk (their bounds are staged in shared memory)
+
+// A column's first K1_R * K1_THREADS entries, prefetched into registers while earlier columns
+// are being applied; three of these rotate so that three columns are in flight per CTA.
+template <bool WITH_VALUES>
+struct ColStage {
+    int32_t g[K1_R];
+    double v[K1_R];
+    int64_t lo;
+    int n;
+    __device__ __forceinline__ void load(const int64_t* s_lo, const int* s_n, int j, int ncols,
+                                         const int32_t* __restrict__ idx, const double* __restrict__ x) {
+        n = 0;
+        lo = 0;
+        if (j < ncols) {
+            lo = s_lo[j];
+            n = s_n[j];
+        }
+#pragma unroll
+        for (int r = 0; r < K1_R; ++r) {
+            const int k = r * K1_THREADS + (int)threadIdx.x;
+            g[r] = -1;
+            if (k < n) {
+                g[r] = idx[lo + k];
+                if (WITH_VALUES) v[r] = x[lo + k];
+            }
+        }
+    }
+};
+
+// Stages the bounds of the chunk's columns in shared memory. Returns the number of columns.
+__device__ inline int stage_bounds(const int64_t* __restrict__ p, const int32_t* __restrict__ perm, int c_lo, int c_hi,
+                                   int64_t* s_lo, int* s_n) {
+    const int ncols = c_hi - c_lo;
+    for (int j = threadIdx.x; j < ncols; j += blockDim.x) {
+        const int c = perm[c_lo + j];
+        const int64_t a = p[c], b = p[c + 1];
+        s_lo[j] = a;
+        s_n[j] = (int)(b - a);
+    }
+    return ncols;
+}
 
 // Pass A: table[chunk][gene] = stored entries of `gene` in the chunk's columns.
 __global__ void __launch_bounds__(K1_THREADS)
 k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const int32_t* __restrict__ perm,
          const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen, uint32_t* __restrict__ table,
          int* __restrict__ bad) {
-    extern __shared__ uint32_t cnt[];
+    extern __shared__ __align__(16) unsigned char k1_smem[];
+    int64_t* s_lo = reinterpret_cast<int64_t*>(k1_smem);
+    int* s_n = reinterpret_cast<int*>(s_lo + K1_MAXCOLS);
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(s_n + K1_MAXCOLS);
     for (int g = threadIdx.x; g < glen; g += blockDim.x) cnt[g] = 0;
-    __syncthreads();
     const int chunk = blockIdx.x;
     const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
+    const int ncols = stage_bounds(p, perm, c_lo, c_hi, s_lo, s_n);
+    __syncthreads();
     int flag = 0;
-    // The column bounds of the next cell are fetched while the current one is processed.
-    int64_t lo = 0, hi = 0;
-    if (c_lo < c_hi) {
-        const int c = perm[c_lo];
-        lo = p[c];
-        hi = p[c + 1];
-    }
-    for (int cc = c_lo; cc < c_hi; ++cc) {
-        int64_t nlo = 0, nhi = 0;
-        if (cc + 1 < c_hi) {
-            const int cn = perm[cc + 1];
-            nlo = p[cn];
-            nhi = p[cn + 1];
+    const int lane = threadIdx.x & 31;
+
+    auto apply = [&](ColStage<false>& st) {
+#pragma unroll
+        for (int r = 0; r < K1_R; ++r) {
+            const int g = st.g[r];
+            // strictly increasing rows inside a column: compare with the left neighbour
+            int prev = __shfl_up_sync(0xffffffffu, g, 1);
+            const int k = r * K1_THREADS + (int)threadIdx.x;
+            if (k < st.n) {
+                if (lane == 0) prev = k > 0 ? idx[st.lo + k - 1] : -1;
+                if (g < 0 || g >= ngenes || prev >= g) {
+                    flag = 1;
+                } else {
+                    const unsigned gl = (unsigned)(g - g0);
+                    if (gl < (unsigned)glen) cnt[gl] += 1;
+                }
+            }
         }
-        for (int64_t k = lo + threadIdx.x; k < hi; k += blockDim.x) {
-            const int g = idx[k];
-            if (g < 0 || g >= ngenes || (k > lo && idx[k - 1] >= g)) {
+        for (int k = K1_R * K1_THREADS + (int)threadIdx.x; k < st.n; k += K1_THREADS) {  // very long columns
+            const int g = idx[st.lo + k];
+            if (g < 0 || g >= ngenes || idx[st.lo + k - 1] >= g) {
                 flag = 1;
             } else {
                 const unsigned gl = (unsigned)(g - g0);
                 if (gl < (unsigned)glen) cnt[gl] += 1;
             }
         }
+    };
+
+    ColStage<false> s0, s1, s2;
+    s0.load(s_lo, s_n, 0, ncols, idx, nullptr);
+    s1.load(s_lo, s_n, 1, ncols, idx, nullptr);
+    s2.load(s_lo, s_n, 2, ncols, idx, nullptr);
+    for (int j = 0; j < ncols; j += 3) {
+        apply(s0);
         __syncthreads();
-        lo = nlo;
-        hi = nhi;
+        s0.load(s_lo, s_n, j + 3, ncols, idx, nullptr);
+        if (j + 1 < ncols) apply(s1);
+        __syncthreads();
+        s1.load(s_lo, s_n, j + 4, ncols, idx, nullptr);
+        if (j + 2 < ncols) apply(s2);
+        __syncthreads();
+        s2.load(s_lo, s_n, j + 5, ncols, idx, nullptr);
     }
     if (flag) *bad = 1;
     for (int g = threadIdx.x; g < glen; g += blockDim.x) table[(size_t)chunk * ngenes + g0 + g] = cnt[g];
@@ -119,38 +184,53 @@ __global__ void __launch_bounds__(K1_THREADS)
 k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
            const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen,
            const uint32_t* __restrict__ table, const int64_t* __restrict__ row_ptr, double* __restrict__ vals) {
-    extern __shared__ uint32_t cursor[];
+    extern __shared__ __align__(16) unsigned char k1_smem[];
+    int64_t* s_lo = reinterpret_cast<int64_t*>(k1_smem);
+    int* s_n = reinterpret_cast<int*>(s_lo + K1_MAXCOLS);
+    uint32_t* cursor = reinterpret_cast<uint32_t*>(s_n + K1_MAXCOLS);
     const int chunk = blockIdx.x;
     for (int g = threadIdx.x; g < glen; g += blockDim.x) {
         cursor[g] = (uint32_t)(row_ptr[g0 + g] + table[(size_t)chunk * ngenes + g0 + g]);
     }
-    __syncthreads();
     const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
-    int64_t lo = 0, hi = 0;
-    if (c_lo < c_hi) {
-        const int c = perm[c_lo];
-        lo = p[c];
-        hi = p[c + 1];
-    }
-    for (int cc = c_lo; cc < c_hi; ++cc) {
-        int64_t nlo = 0, nhi = 0;
-        if (cc + 1 < c_hi) {
-            const int cn = perm[cc + 1];
-            nlo = p[cn];
-            nhi = p[cn + 1];
+    const int ncols = stage_bounds(p, perm, c_lo, c_hi, s_lo, s_n);
+    __syncthreads();
+
+    auto apply = [&](ColStage<true>& st) {
+#pragma unroll
+        for (int r = 0; r < K1_R; ++r) {
+            const unsigned gl = (unsigned)(st.g[r] - g0);
+            if (st.g[r] >= 0 && gl < (unsigned)glen) {
+                const uint32_t at = cursor[gl];
+                cursor[gl] = at + 1;
+                vals[at] = st.v[r];
+            }
         }
-        for (int64_t k = lo + threadIdx.x; k < hi; k += blockDim.x) {
-            const unsigned gl = (unsigned)(idx[k] - g0);
-            const double v = x[k];
+        for (int k = K1_R * K1_THREADS + (int)threadIdx.x; k < st.n; k += K1_THREADS) {
+            const unsigned gl = (unsigned)(idx[st.lo + k] - g0);
+            const double v = x[st.lo + k];
             if (gl < (unsigned)glen) {
                 const uint32_t at = cursor[gl];
                 cursor[gl] = at + 1;
                 vals[at] = v;
             }
         }
+    };
+
+    ColStage<true> s0, s1, s2;
+    s0.load(s_lo, s_n, 0, ncols, idx, x);
+    s1.load(s_lo, s_n, 1, ncols, idx, x);
+    s2.load(s_lo, s_n, 2, ncols, idx, x);
+    for (int j = 0; j < ncols; j += 3) {
+        apply(s0);
         __syncthreads();
-        lo = nlo;
-        hi = nhi;
+        s0.load(s_lo, s_n, j + 3, ncols, idx, x);
+        if (j + 1 < ncols) apply(s1);
+        __syncthreads();
+        s1.load(s_lo, s_n, j + 4, ncols, idx, x);
+        if (j + 2 < ncols) apply(s2);
+        __syncthreads();
+        s2.load(s_lo, s_n, j + 5, ncols, idx, x);
     }
 }
 
@@ -176,16 +256,17 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
     SB_CUDA(cudaMemsetAsync(bad, 0, 64, ctx->stream));
 
     // Genes are handled in ranges whose cursors fit in shared memory (one range for <= ~50k genes).
-    const int max_glen = (int)((ctx->smem_optin - 1024) / 4);
+    const size_t bounds_bytes = (size_t)K1_MAXCOLS * 12;
+    const int max_glen = (int)((ctx->smem_optin - bounds_bytes - 1024) / 4);
     const int nranges = std::max(1, (int)ceil_div(ngenes, max_glen));
     const int glen_all = (int)ceil_div(ngenes, nranges);
-    allow_smem(k1_count, (size_t)glen_all * 4);
-    allow_smem(k1_scatter, (size_t)glen_all * 4);
+    allow_smem(k1_count, (size_t)glen_all * 4 + bounds_bytes);
+    allow_smem(k1_scatter, (size_t)glen_all * 4 + bounds_bytes);
 
     if (L.nchunks > 0 && ngenes > 0) {
         for (int r = 0; r < nranges; ++r) {
             const int g0 = r * glen_all, glen = std::min(glen_all, ngenes - g0);
-            SB_LAUNCH(ctx, k1_count, L.nchunks, K1_THREADS, (size_t)glen * 4, mat->d_p, mat->d_i, L.d_perm,
+            SB_LAUNCH(ctx, k1_count, L.nchunks, K1_THREADS, (size_t)glen * 4 + bounds_bytes, mat->d_p, mat->d_i, L.d_perm,
                       L.d_chunk_start, ngenes, g0, glen, table, bad);
         }
     }
@@ -197,7 +278,7 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
     if (L.nchunks > 0 && ngenes > 0) {
         for (int r = 0; r < nranges; ++r) {
             const int g0 = r * glen_all, glen = std::min(glen_all, ngenes - g0);
-            SB_LAUNCH(ctx, k1_scatter, L.nchunks, K1_THREADS, (size_t)glen * 4, mat->d_p, mat->d_i, mat->d_x, L.d_perm,
+            SB_LAUNCH(ctx, k1_scatter, L.nchunks, K1_THREADS, (size_t)glen * 4 + bounds_bytes, mat->d_p, mat->d_i, mat->d_x, L.d_perm,
                       L.d_chunk_start, ngenes, g0, glen, table, T.row_ptr, T.vals);
         }
     }
