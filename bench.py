@@ -37,6 +37,8 @@ WORKLOADS = {
     "config3": dict(ngenes=33538, ncells=1300000, G=50, B=8, density=0.07, seed=1003),
     "config5": dict(ngenes=20000, ncells=500000, G=200, B=1, density=0.07, seed=1005),
     "tiny": dict(ngenes=2000, ncells=20000, G=8, B=2, density=0.07, seed=1999),
+    # one eighth of config 3's genes over all its cells: the per-GPU share of the 8-GPU run, for profiling
+    "config3s": dict(ngenes=4192, ncells=1300000, G=50, B=8, density=0.07, seed=1003),
 }
 PHASES = ["transpose", "stats", "sort", "count", "effects", "summaries", "minrank"]
 

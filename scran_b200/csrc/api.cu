@@ -229,7 +229,7 @@ void scranb200_ctx_destroy(scranb200_ctx* ctx) {
                               &ctx->unit_m, &ctx->sort_keys, &ctx->sort_labs, &ctx->flags, &ctx->mean, &ctx->var,
                               &ctx->ndet, &ctx->u_pairs, &ctx->t_pairs, &ctx->layout_i32, &ctx->layout_f64, &ctx->eff,
                               &ctx->out, &ctx->minrank, &ctx->rank_keys, &ctx->rank_idx, &ctx->plan_tmp, &ctx->io_a,
-                              &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit};
+                              &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit, &ctx->jobs, &ctx->split};
         for (sb::DevBuf* b : bufs) b->release();
         for (int k = 0; k < 16; ++k) {
             if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);

@@ -19,7 +19,7 @@ constexpr int SORT_HIST_WORDS = SORT_WARPS * 256 + 64;  // + aux words
 
 // whist: SORT_HIST_WORDS uint32 of shared memory. Returns 0 if the result is in (ka, pa), 1 if
 // in (kb, pb). Must be called by all SORT_THREADS threads with identical arguments.
-template <typename P>
+template <typename P, bool FROM_PAYLOAD = false>
 __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, int bit_lo, int bit_hi,
                                 uint32_t* whist) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -41,7 +41,7 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
             const bool valid = i < s_hi;
             const unsigned act = __ballot_sync(0xffffffffu, valid);
             if (valid) {
-                const unsigned d = (unsigned)(sk[i] >> bit) & 255u;
+                const unsigned d = FROM_PAYLOAD ? ((unsigned)(sp[i] >> bit) & 255u) : ((unsigned)(sk[i] >> bit) & 255u);
                 const unsigned peers = __match_any_sync(act, d);
                 if (lane == __ffs(peers) - 1) mine[d] += __popc(peers);
             }
@@ -79,7 +79,7 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
                 if (valid) {
                     const uint64_t k = sk[i];
                     const P pl = sp[i];
-                    const unsigned d = (unsigned)(k >> bit) & 255u;
+                    const unsigned d = FROM_PAYLOAD ? ((unsigned)(pl >> bit) & 255u) : ((unsigned)(k >> bit) & 255u);
                     const unsigned peers = __match_any_sync(act, d);
                     const uint32_t base = mine[d];
                     const uint32_t at = base + __popc(peers & ((1u << lane) - 1u));
@@ -98,18 +98,29 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
 }
 
 // After a sort on the high 32 key bits: order every run of equal high words by the full key,
-// stably. Runs longer than 32 are left alone and reported through *overflow (shared memory).
+// stably. Runs of up to 32 entries are insertion-sorted by the thread at their start. A longer
+// run is fine as long as all its keys are equal (heavy ties); if one holds different keys,
+// *overflow is raised and the caller falls back to sorting all eight digits.
 template <typename P>
 __device__ void fixup_low_bits(uint64_t* k, P* p, int n, uint32_t* overflow) {
     for (int j = threadIdx.x; j < n; j += blockDim.x) {
-        const uint32_t h = (uint32_t)(k[j] >> 32);
-        if (j > 0 && (uint32_t)(k[j - 1] >> 32) == h) continue;
+        const uint64_t kj = k[j];
+        const uint32_t h = (uint32_t)(kj >> 32);
+        if (j > 0 && (uint32_t)(k[j - 1] >> 32) == h) {
+            // inside a run: entries 32 or more past the run start report unsorted neighbours
+            if (j >= 32 && (uint32_t)(k[j - 32] >> 32) == h && k[j - 1] != kj) *overflow = 1;
+            continue;
+        }
         int e = j + 1;
-        while (e < n && e - j <= 32 && (uint32_t)(k[e] >> 32) == h) ++e;
+        bool differ = false;
+        while (e < n && e - j <= 32 && (uint32_t)(k[e] >> 32) == h) {
+            differ |= k[e] != kj;
+            ++e;
+        }
         const int len = e - j;
         if (len > 32) {
-            *overflow = 1;
-        } else if (len >= 2) {
+            if (differ) *overflow = 1;
+        } else if (len >= 2 && differ) {
             for (int a = j + 1; a < e; ++a) {
                 const uint64_t ka = k[a];
                 const P pa = p[a];

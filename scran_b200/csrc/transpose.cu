@@ -179,45 +179,126 @@ __global__ void __launch_bounds__(1024) k1_scan_rows(const uint32_t* __restrict_
     if (t == 1023) row_ptr[ngenes] = part[1023];
 }
 
-// Pass B: scatter the values. cursor[g] starts at row_ptr[g] + table[chunk][g].
-__global__ void __launch_bounds__(K1_THREADS)
-k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
-           const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen,
-           const uint32_t* __restrict__ table, const int64_t* __restrict__ row_ptr, double* __restrict__ vals) {
-    extern __shared__ __align__(16) unsigned char k1_smem[];
-    int64_t* s_lo = reinterpret_cast<int64_t*>(k1_smem);
-    int* s_n = reinterpret_cast<int*>(s_lo + K1_MAXCOLS);
-    uint32_t* cursor = reinterpret_cast<uint32_t*>(s_n + K1_MAXCOLS);
-    const int chunk = blockIdx.x;
-    for (int g = threadIdx.x; g < glen; g += blockDim.x) {
-        cursor[g] = (uint32_t)(row_ptr[g0 + g] + table[(size_t)chunk * ngenes + g0 + g]);
+// For every used column (in permuted order) and every gene range r: where the entries with
+// gene >= r * GR start inside the column. split: [nranges + 1][ncols] offsets relative to p[c].
+__global__ void __launch_bounds__(256)
+k1_split(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const int32_t* __restrict__ perm, int ncols,
+         int GR, int nranges, uint32_t* __restrict__ split) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= ncols) return;
+    const int c = perm[pos];
+    const int64_t lo = p[c];
+    const uint32_t len = (uint32_t)(p[c + 1] - lo);
+    split[pos] = 0;
+    uint32_t from = 0;
+    for (int r = 1; r < nranges; ++r) {
+        const int target = r * GR;
+        uint32_t a = from, b = len;  // first entry with gene >= target
+        while (a < b) {
+            const uint32_t mid = (a + b) >> 1;
+            if (idx[lo + mid] < target) a = mid + 1; else b = mid;
+        }
+        split[(size_t)r * ncols + pos] = a;
+        from = a;
     }
-    const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
-    const int ncols = stage_bounds(p, perm, c_lo, c_hi, s_lo, s_n);
-    __syncthreads();
+    split[(size_t)nranges * ncols + pos] = len;
+}
 
-    auto apply = [&](ColStage<true>& st) {
+constexpr int K1S_THREADS = 256;
+constexpr int K1S_GR = 2048;  // genes per scatter CTA: cursor + start + 4 staged values = 40 B per gene
+constexpr int K1S_R = 2;      // entries per thread per column slice held in registers
+
+struct SliceStage {
+    int32_t g[K1S_R];
+    double v[K1S_R];
+    int64_t lo;
+    int n;
+    __device__ __forceinline__ void load(const int64_t* s_lo, const int* s_n, int j, int ncols,
+                                         const int32_t* __restrict__ idx, const double* __restrict__ x) {
+        n = 0;
+        lo = 0;
+        if (j < ncols) {
+            lo = s_lo[j];
+            n = s_n[j];
+        }
 #pragma unroll
-        for (int r = 0; r < K1_R; ++r) {
-            const unsigned gl = (unsigned)(st.g[r] - g0);
-            if (st.g[r] >= 0 && gl < (unsigned)glen) {
-                const uint32_t at = cursor[gl];
-                cursor[gl] = at + 1;
-                vals[at] = st.v[r];
+        for (int r = 0; r < K1S_R; ++r) {
+            const int k = r * K1S_THREADS + (int)threadIdx.x;
+            g[r] = -1;
+            if (k < n) {
+                g[r] = idx[lo + k];
+                v[r] = x[lo + k];
             }
         }
-        for (int k = K1_R * K1_THREADS + (int)threadIdx.x; k < st.n; k += K1_THREADS) {
-            const unsigned gl = (unsigned)(idx[st.lo + k] - g0);
-            const double v = x[st.lo + k];
-            if (gl < (unsigned)glen) {
-                const uint32_t at = cursor[gl];
-                cursor[gl] = at + 1;
+    }
+};
+
+// Pass B: scatter the values. One CTA owns (chunk of columns) x (range of GR genes). Per gene it
+// keeps the write cursor and the last up-to-4 values in shared memory, and writes a 32-byte
+// sector to HBM only when the sector is complete (or at the end of the chunk), so that the
+// gene-major array is written in whole sectors instead of one scattered 8-byte store per entry.
+__global__ void __launch_bounds__(K1S_THREADS)
+k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
+           const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int GR, int nranges,
+           int ncols_all, const uint32_t* __restrict__ split, const uint32_t* __restrict__ table,
+           const int64_t* __restrict__ row_ptr, double* __restrict__ vals) {
+    extern __shared__ __align__(16) unsigned char k1_smem[];
+    int64_t* s_lo = reinterpret_cast<int64_t*>(k1_smem);
+    double* stage = reinterpret_cast<double*>(s_lo + K1_MAXCOLS);       // [GR][4]
+    int* s_n = reinterpret_cast<int*>(stage + (size_t)GR * 4);
+    uint32_t* cursor = reinterpret_cast<uint32_t*>(s_n + K1_MAXCOLS);   // [GR]
+    uint32_t* first = cursor + GR;                                      // [GR]
+    const int chunk = blockIdx.x / nranges, r = blockIdx.x % nranges;
+    const int g0 = r * GR, glen = min(GR, ngenes - g0);
+    for (int g = threadIdx.x; g < glen; g += blockDim.x) {
+        const uint32_t at = (uint32_t)(row_ptr[g0 + g] + table[(size_t)chunk * ngenes + g0 + g]);
+        cursor[g] = at;
+        first[g] = at;
+    }
+    const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
+    const int ncols = c_hi - c_lo;
+    for (int j = threadIdx.x; j < ncols; j += blockDim.x) {
+        const int c = perm[c_lo + j];
+        uint32_t a = 0, b;
+        if (nranges > 1) {
+            a = split[(size_t)r * ncols_all + c_lo + j];
+            b = split[(size_t)(r + 1) * ncols_all + c_lo + j];
+        } else {
+            b = (uint32_t)(p[c + 1] - p[c]);
+        }
+        s_lo[j] = p[c] + a;
+        s_n[j] = (int)(b - a);
+    }
+    __syncthreads();
+
+    auto put = [&](int g, double v) {
+        const unsigned gl = (unsigned)(g - g0);
+        if (gl >= (unsigned)glen) return;  // only reachable with an invalid (unsorted) matrix, reported by pass A
+        const uint32_t at = cursor[gl];
+        cursor[gl] = at + 1;
+        double* sg = stage + (size_t)gl * 4;
+        sg[at & 3u] = v;
+        if ((at & 3u) == 3u) {
+            const uint32_t base = at - 3u, f = first[gl];
+            if (base >= f) {  // a whole 32-byte sector
+                double2* dst = reinterpret_cast<double2*>(vals + base);
+                dst[0] = make_double2(sg[0], sg[1]);
+                dst[1] = make_double2(sg[2], v);
+            } else {          // the sector started in an earlier chunk: write only our part
+                for (uint32_t s = f; s < at; ++s) vals[s] = sg[s & 3u];
                 vals[at] = v;
             }
         }
     };
+    auto apply = [&](SliceStage& st) {
+#pragma unroll
+        for (int q = 0; q < K1S_R; ++q) {
+            if (st.g[q] >= 0) put(st.g[q], st.v[q]);
+        }
+        for (int k = K1S_R * K1S_THREADS + (int)threadIdx.x; k < st.n; k += K1S_THREADS) put(idx[st.lo + k], x[st.lo + k]);
+    };
 
-    ColStage<true> s0, s1, s2;
+    SliceStage s0, s1, s2;
     s0.load(s_lo, s_n, 0, ncols, idx, x);
     s1.load(s_lo, s_n, 1, ncols, idx, x);
     s2.load(s_lo, s_n, 2, ncols, idx, x);
@@ -231,6 +312,14 @@ k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const
         if (j + 2 < ncols) apply(s2);
         __syncthreads();
         s2.load(s_lo, s_n, j + 5, ncols, idx, x);
+    }
+    // flush the incomplete last sector of every gene
+    for (int g = threadIdx.x; g < glen; g += blockDim.x) {
+        const uint32_t c = cursor[g], f = first[g];
+        if ((c & 3u) != 0u && c > f) {
+            const uint32_t from = max(f, c & ~3u);
+            for (uint32_t s = from; s < c; ++s) vals[s] = stage[(size_t)g * 4 + (s & 3u)];
+        }
     }
 }
 
@@ -255,13 +344,12 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
     int* bad = ctx->flags.as<int>();
     SB_CUDA(cudaMemsetAsync(bad, 0, 64, ctx->stream));
 
-    // Genes are handled in ranges whose cursors fit in shared memory (one range for <= ~50k genes).
+    // Counting pass: genes in ranges whose counters fit in shared memory (one range for <= ~50k genes).
     const size_t bounds_bytes = (size_t)K1_MAXCOLS * 12;
     const int max_glen = (int)((ctx->smem_optin - bounds_bytes - 1024) / 4);
     const int nranges = std::max(1, (int)ceil_div(ngenes, max_glen));
     const int glen_all = (int)ceil_div(ngenes, nranges);
     allow_smem(k1_count, (size_t)glen_all * 4 + bounds_bytes);
-    allow_smem(k1_scatter, (size_t)glen_all * 4 + bounds_bytes);
 
     if (L.nchunks > 0 && ngenes > 0) {
         for (int r = 0; r < nranges; ++r) {
@@ -276,11 +364,23 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
     }
     SB_LAUNCH(ctx, k1_scan_rows, 1, 1024, 0, ctx->row_total.as<uint32_t>(), ngenes, ctx->row_ptr.as<int64_t>());
     if (L.nchunks > 0 && ngenes > 0) {
-        for (int r = 0; r < nranges; ++r) {
-            const int g0 = r * glen_all, glen = std::min(glen_all, ngenes - g0);
-            SB_LAUNCH(ctx, k1_scatter, L.nchunks, K1_THREADS, (size_t)glen * 4 + bounds_bytes, mat->d_p, mat->d_i, mat->d_x, L.d_perm,
-                      L.d_chunk_start, ngenes, g0, glen, table, T.row_ptr, T.vals);
+        // Scatter pass: (chunk) x (range of K1S_GR genes) CTAs.
+        const int GR = K1S_GR;
+        const int sranges = (int)ceil_div(ngenes, GR);
+        const int ncols = (int)L.perm.size();
+        const uint32_t* split = nullptr;
+        if (sranges > 1) {
+            ctx->split.reserve((size_t)(sranges + 1) * ncols * 4);
+            SB_LAUNCH(ctx, k1_split, (unsigned)ceil_div(ncols, 256), 256, 0, mat->d_p, mat->d_i, L.d_perm, ncols, GR, sranges,
+                      ctx->split.as<uint32_t>());
+            split = ctx->split.as<uint32_t>();
         }
+        const size_t smem = (size_t)K1_MAXCOLS * 12 + (size_t)GR * 40;
+        allow_smem(k1_scatter, smem);
+        const int64_t grid = (int64_t)L.nchunks * sranges;
+        if (grid > 2147483647ll) throw Error("too many transpose tiles");
+        SB_LAUNCH(ctx, k1_scatter, (unsigned)grid, K1S_THREADS, smem, mat->d_p, mat->d_i, mat->d_x, L.d_perm, L.d_chunk_start,
+                  ngenes, GR, sranges, ncols, split, table, T.row_ptr, T.vals);
     }
     int h_bad = 0;
     SB_CUDA(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));

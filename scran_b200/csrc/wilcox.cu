@@ -3,23 +3,31 @@
 // Reference semantics: src/overlap_exprs.cpp:34-128 (class wilcoxer). There, every gene gathers
 // the cells of every group from a dense row, sorts each group and runs one two-pointer sweep per
 // pair: O(ncells) + O(nnz_gene * (G-1)) scalar steps per gene. Here the work is O(nnz) and the
-// zeros are handled in closed form:
+// zeros are handled in closed form.
 //
-//  k3_sort  one CTA per (gene, unit). The unit's stored non-zero values (all groups of one
-//           block) plus one "probe" element at 0 are sorted by value with their group label as
-//           payload (shared-memory radix sort, or the same sort streamed through L2 for units
-//           beyond the shared-memory capacity). Output: a 2-byte-per-entry label stream in value
-//           order with a "ties with previous" bit. With lfc != 0 the unit is sorted twice over:
-//           every value once as b ("R role") and once as a - lfc ("L role"), R before L in a tie.
-//  k3_walk  one CTA per (gene, unit): lane R keeps the running count c_R of label-R entries seen
-//           so far (cs_R = the count at the start of the current tie run) and adds it into
-//           row label(i) of a (G+1) x (G+1) table in shared memory while stepping through the
-//           stream. That yields B[L][R] = sum over a in L of #(b in R : b < a) for all ordered
-//           pairs at once; the probe row/column gives #(a > 0) and #(b < 0), from which the
-//           implicit zeros enter as  B[L][R] + B[L][probe] z_R + z_L B[probe][R]  (z = zero
-//           count). Then 2U = nL nR + Bfull[L][R] - Bfull[R][L] in int64, exact.
-//           (lfc != 0: the table accumulates cs_R + c_R at L-role entries and
+// A "unit" is one gene x one set of mutually compared combinations (for scoreMarkers: one gene
+// in one block level). Its stored non-zero values, plus one "probe" entry at 0, are put in value
+// order; what the count needs from that order is only the sequence of group labels with a
+// "ties with the previous entry" bit: the 2-byte label stream.
+//
+//  k3_plan  one CTA: cuts the (gene, unit) list into jobs: runs of consecutive small units that
+//           together fit the shared-memory sort, or one larger unit on its own.
+//  k3_sort  one CTA per job. Small units are sorted together in one shared-memory radix sort
+//           (key = value, then unit slot). A unit beyond the shared-memory capacity is first
+//           split by value into 256 ordered buckets (one stable pass through L2), then
+//           consecutive buckets are sorted in shared memory. With lfc != 0 every value enters
+//           twice: as b ("R role") and as a - lfc ("L role"), R before L inside a tie.
+//  k3_walk  lane R keeps the running count c_R of label-R entries seen so far (cs_R = the count
+//           at the start of the current tie run) and adds it into row label(i) of a
+//           (G+1) x (G+1) table in shared memory while stepping through the stream: that yields
+//           B[L][R] = sum over a in L of #(b in R : b < a) for all ordered pairs at once. The
+//           probe row/column gives #(a > 0) and #(b < 0), so the implicit zeros enter as
+//           Bfull[L][R] = B[L][R] + B[L][probe] z_R + z_L B[probe][R]  (z = zero count), and
+//           2U = nL nR + Bfull[L][R] - Bfull[R][L] in int64, exact. (lfc != 0: the table
+//           accumulates cs_R + c_R at L-role entries and
 //           2U = B[L][R] + z_R B[L][p] + z_L B[p][R] + z_L z_R B[p][p].)
+//           Small units are walked several at a time (one warp group each); large ones by all
+//           warps over position chunks with private tables.
 //  k3_ties  optional: sum over tie runs of t(t^2-1) per pair, accumulated in double in ascending
 //           value order like src/overlap_exprs.cpp:121-124.
 #include "kernels.h"
@@ -29,10 +37,12 @@ namespace sb {
 
 namespace {
 
-constexpr uint16_t LAB_MASK = 0x3fff;
-constexpr uint16_t ROLE_L = 0x4000;
-constexpr uint16_t TIE_BIT = 0x8000;
+constexpr uint32_t LAB_MASK = 0x3fff;
+constexpr uint32_t ROLE_L = 0x4000;
+constexpr uint32_t TIE_BIT = 0x8000;
 constexpr int MAX_LABELS = 16383;
+constexpr int MAXB = 512;      // units per job at most
+constexpr int MAXSEG = 4096;   // segment boundaries staged per job at most
 
 struct UnitTables {
     const int64_t* row_ptr;
@@ -43,111 +53,442 @@ struct UnitTables {
     int ngenes, U, mult;  // mult = 1 (lfc == 0) or 2
 };
 
-// Offset of (gene, unit) in the label stream / sort scratch, and its value range.
-__device__ inline void unit_range(const UnitTables& ut, int g, int u, int64_t& vbase, uint32_t& n, int64_t& soff) {
-    const int first = ut.unit_first[u], G = ut.unit_ncomb[u];
-    const uint32_t a = ut.seg_off[(size_t)first * ut.ngenes + g];
-    const uint32_t b = ut.seg_off[(size_t)(first + G) * ut.ngenes + g];
-    vbase = ut.row_ptr[g] + a;
-    n = b - a;
-    soff = (int64_t)ut.mult * (vbase + (int64_t)g * ut.U + u);
+struct UnitInfo {
+    int64_t vbase, soff;
+    uint32_t n, total;
+    int first, G, g, u;
+};
+
+__device__ inline UnitInfo unit_info(const UnitTables& ut, int64_t task) {
+    UnitInfo r;
+    r.g = (int)(task / ut.U);
+    r.u = (int)(task % ut.U);
+    r.first = ut.unit_first[r.u];
+    r.G = ut.unit_ncomb[r.u];
+    const uint32_t a = ut.seg_off[(size_t)r.first * ut.ngenes + r.g];
+    const uint32_t b = ut.seg_off[(size_t)(r.first + r.G) * ut.ngenes + r.g];
+    r.vbase = ut.row_ptr[r.g] + a;
+    r.n = b - a;
+    r.soff = (int64_t)ut.mult * (r.vbase + task);
+    r.total = (uint32_t)ut.mult * (r.n + 1);
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------
+// k3_plan
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k3_plan(UnitTables ut, uint32_t small_max, uint32_t window, int maxb,
+                                                 int32_t* jobs, int32_t* njobs) {
+    __shared__ int part[1024];
+    const int64_t ntasks = (int64_t)ut.ngenes * ut.U;
+    const int t = threadIdx.x;
+    const int64_t per = (ntasks + 1023) / 1024;
+    const int64_t lo = min(ntasks, t * per), hi = min(ntasks, lo + per);
+    auto is_start = [&](int64_t task, const UnitInfo& cur, const UnitInfo& prev) {
+        if (task == 0) return true;
+        if (cur.total > small_max || prev.total > small_max) return true;
+        if (cur.soff / window != prev.soff / window) return true;
+        return task / maxb != (task - 1) / maxb;
+    };
+    for (int phase = 0; phase < 2; ++phase) {
+        int cnt = 0;
+        UnitInfo prev = lo > 0 && lo < ntasks ? unit_info(ut, lo - 1) : UnitInfo();
+        int at = 0;
+        if (phase == 1) at = t == 0 ? 0 : part[t - 1];
+        for (int64_t task = lo; task < hi; ++task) {
+            const UnitInfo cur = unit_info(ut, task);
+            if (is_start(task, cur, prev)) {
+                if (phase == 1) jobs[at] = (int32_t)task;
+                ++at;
+                ++cnt;
+            }
+            prev = cur;
+        }
+        if (phase == 0) {
+            part[t] = cnt;
+            __syncthreads();
+            for (int d = 1; d < 1024; d <<= 1) {
+                const int v = t >= d ? part[t - d] : 0;
+                __syncthreads();
+                part[t] += v;
+                __syncthreads();
+            }
+        }
+    }
+    if (t == 1023) {
+        *njobs = part[1023];
+        jobs[part[1023]] = (int32_t)ntasks;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
 // k3_sort
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(SORT_THREADS)
-k3_sort(UnitTables ut, const double* __restrict__ vals, double shift, int cap, int maxG, uint16_t* stream,
-        uint32_t* unit_m, uint64_t* g_keys_a, uint64_t* g_keys_b, uint16_t* g_labs_a, uint16_t* g_labs_b,
-        unsigned long long* task_counter) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t* s_ka = reinterpret_cast<uint64_t*>(smem_raw);
-    uint64_t* s_kb = s_ka + cap;
-    uint16_t* s_la = reinterpret_cast<uint16_t*>(s_kb + cap);
-    uint16_t* s_lb = s_la + cap;
-    uint32_t* whist = reinterpret_cast<uint32_t*>(s_lb + cap);
-    uint32_t* segb = whist + SORT_HIST_WORDS;
-    uint32_t* misc = segb + (maxG + 2);  // [0] task, [1] dropped
+struct SortParams {
+    UnitTables ut;
+    const double* vals;
+    double shift;
+    int cap, maxG;
+    uint16_t* stream;
+    uint32_t* unit_m;
+    uint64_t *g_ka, *g_kb;   // global scratch, indexed like the stream (units beyond cap only)
+    uint32_t *g_pa, *g_pb;
+    const int32_t* jobs;
+    const int32_t* njobs;
+    unsigned long long* job_counter;
+};
 
-    const int64_t ntasks = (int64_t)ut.ngenes * ut.U;
+struct SortSmem {
+    uint64_t *ka, *kb;
+    uint32_t *pa, *pb;
+    uint32_t* whist;
+    uint32_t* seg;       // MAXSEG + MAXB + 8 staged segment boundaries
+    uint32_t* segptr;    // MAXB + 1
+    uint32_t* off;       // MAXB + 1: compact element offset of each unit in the job
+    uint32_t* drop;      // MAXB
+    uint32_t* n;         // MAXB
+    int64_t* vbase;      // MAXB
+    int64_t* soff;       // MAXB
+    uint32_t* boff;      // 258: bucket offsets of the value partition
+    uint32_t* misc;      // 16
+};
+
+constexpr size_t sort_fixed_bytes() {
+    return (size_t)SORT_HIST_WORDS * 4 + (size_t)(MAXSEG + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 2 +
+           (size_t)MAXB * 8 * 2 + 258 * 4 + 16 * 4 + 64;
+}
+
+__device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap) {
+    SortSmem s;
+    s.ka = reinterpret_cast<uint64_t*>(raw);
+    s.kb = s.ka + cap;
+    s.vbase = reinterpret_cast<int64_t*>(s.kb + cap);
+    s.soff = s.vbase + MAXB;
+    s.pa = reinterpret_cast<uint32_t*>(s.soff + MAXB);
+    s.pb = s.pa + cap;
+    s.whist = s.pb + cap;
+    s.seg = s.whist + SORT_HIST_WORDS;
+    s.segptr = s.seg + (MAXSEG + MAXB + 8);
+    s.off = s.segptr + (MAXB + 1);
+    s.drop = s.off + (MAXB + 1);
+    s.n = s.drop + MAXB;
+    s.boff = s.n + MAXB;
+    s.misc = s.boff + 258;
+    return s;
+}
+
+// Element e of a unit's list: (key, label | role). Dropped (stored zero) entries get key ~0.
+__device__ inline void unit_element(const double* __restrict__ vals, int64_t vbase, uint32_t n, const uint32_t* segb,
+                                    int G, double shift, uint32_t e, uint64_t& key, uint32_t& lab, bool& keep) {
+    const uint32_t per_role = n + 1;
+    const bool role = e >= per_role;
+    const uint32_t k = role ? e - per_role : e;
+    double v = 0.0;
+    lab = (uint32_t)G;
+    keep = true;
+    if (k < n) {
+        v = vals[vbase + k];
+        keep = v != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
+        int lo = 0, hi = G;  // label = last boundary <= k
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (segb[mid] <= k) lo = mid; else hi = mid;
+        }
+        lab = (uint32_t)lo;
+    }
+    if (role) {
+        v = v - shift;
+        lab |= ROLE_L;
+    }
+    key = keep ? key_of(v) : ~0ull;
+}
+
+__global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const SortSmem S = carve_sort_smem(smem_raw, P.cap);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int njobs = *P.njobs;
+    const UnitTables& ut = P.ut;
+
     while (true) {
         __syncthreads();
-        if (threadIdx.x == 0) {
-            const unsigned long long t = atomicAdd(task_counter, 1ull);
-            misc[0] = (uint32_t)(t & 0xffffffffu);
-            misc[2] = (uint32_t)(t >> 32);
-            misc[1] = 0;
+        if (tid == 0) S.misc[0] = (uint32_t)atomicAdd(P.job_counter, 1ull);
+        __syncthreads();
+        const int job = (int)S.misc[0];
+        if (job >= njobs) break;
+        const int64_t t0 = P.jobs[job], t1 = P.jobs[job + 1];
+        const int nb = (int)(t1 - t0);
+
+        // ---- per-unit tables -------------------------------------------------------------
+        if (tid < nb) {
+            const UnitInfo ui = unit_info(ut, t0 + tid);
+            S.vbase[tid] = ui.vbase;
+            S.soff[tid] = ui.soff;
+            S.n[tid] = ui.n;
+            S.drop[tid] = 0;
+            S.off[tid + 1] = ui.total;
+            S.segptr[tid + 1] = (uint32_t)ui.G + 1;
+        }
+        if (tid == 0) {
+            S.off[0] = 0;
+            S.segptr[0] = 0;
         }
         __syncthreads();
-        const int64_t task = (int64_t)(((uint64_t)misc[2] << 32) | misc[0]);
-        if (task >= ntasks) break;
-        const int g = (int)(task / ut.U), u = (int)(task % ut.U);
-        const int first = ut.unit_first[u], G = ut.unit_ncomb[u];
-        int64_t vbase, soff;
-        uint32_t n;
-        unit_range(ut, g, u, vbase, n, soff);
-        const uint32_t seg0 = ut.seg_off[(size_t)first * ut.ngenes + g];
-        for (int k = threadIdx.x; k <= G; k += blockDim.x) {
-            segb[k] = ut.seg_off[(size_t)(first + k) * ut.ngenes + g] - seg0;
+        if (warp == 0) {  // inclusive scans of off[1..nb] and segptr[1..nb] by one warp
+            uint32_t run_a = 0, run_b = 0;
+            for (int base = 0; base < nb; base += 32) {
+                const int i = base + lane;
+                uint32_t a = i < nb ? S.off[i + 1] : 0u, b = i < nb ? S.segptr[i + 1] : 0u;
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t ya = __shfl_up_sync(0xffffffffu, a, o), yb = __shfl_up_sync(0xffffffffu, b, o);
+                    if (lane >= o) {
+                        a += ya;
+                        b += yb;
+                    }
+                }
+                if (i < nb) {
+                    S.off[i + 1] = run_a + a;
+                    S.segptr[i + 1] = run_b + b;
+                }
+                run_a += __shfl_sync(0xffffffffu, a, 31);
+                run_b += __shfl_sync(0xffffffffu, b, 31);
+            }
+        }
+        __syncthreads();
+        const uint32_t total = S.off[nb];
+        const uint32_t nseg = S.segptr[nb];
+        for (uint32_t e = tid; e < nseg; e += blockDim.x) {  // stage the segment boundaries
+            int lo = 0, hi = nb;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (S.segptr[mid] <= e) lo = mid; else hi = mid;
+            }
+            const int64_t task = t0 + lo;
+            const int g = (int)(task / ut.U), u = (int)(task % ut.U);
+            const int first = ut.unit_first[u];
+            const uint32_t seg0 = ut.seg_off[(size_t)first * ut.ngenes + g];
+            S.seg[e] = ut.seg_off[(size_t)(first + (e - S.segptr[lo])) * ut.ngenes + g] - seg0;
         }
         __syncthreads();
 
-        const int64_t per_role = (int64_t)n + 1;
-        const int64_t total = per_role * ut.mult;
-        const bool in_smem = total <= cap;
-        uint64_t* ka = in_smem ? s_ka : g_keys_a + soff;
-        uint64_t* kb = in_smem ? s_kb : g_keys_b + soff;
-        uint16_t* la = in_smem ? s_la : g_labs_a + soff;
-        uint16_t* lb = in_smem ? s_lb : g_labs_b + soff;
-
-        // Build the element list: R role first, then (lfc != 0) the shifted L role.
-        uint32_t dropped = 0;
-        for (int64_t e = threadIdx.x; e < total; e += blockDim.x) {
-            const int role = e >= per_role;
-            const uint32_t k = (uint32_t)(e - (role ? per_role : 0));
-            double v = 0.0;
-            uint16_t lab = (uint16_t)G;
-            bool keep = true;
-            if (k < n) {
-                v = vals[vbase + k];
-                keep = v != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
-                int lo = 0, hi = G;  // label = last boundary <= k
+        if (total <= (uint32_t)P.cap) {
+            // ---- shared-memory path: all units of the job in one sort ---------------------
+            for (uint32_t e = tid; e < total; e += blockDim.x) {
+                int lo = 0, hi = nb;
                 while (hi - lo > 1) {
                     const int mid = (lo + hi) >> 1;
-                    if (segb[mid] <= k) lo = mid; else hi = mid;
+                    if (S.off[mid] <= e) lo = mid; else hi = mid;
                 }
-                lab = (uint16_t)lo;
+                uint64_t key;
+                uint32_t lab;
+                bool keep;
+                unit_element(P.vals, S.vbase[lo], S.n[lo], S.seg + S.segptr[lo], (int)(S.segptr[lo + 1] - S.segptr[lo]) - 1,
+                             P.shift, e - S.off[lo], key, lab, keep);
+                S.ka[e] = key;
+                S.pa[e] = ((uint32_t)lo << 16) | lab;
+                if (!keep) atomicAdd(&S.drop[lo], 1u);
             }
-            if (role) {
-                v = v - shift;
-                lab |= ROLE_L;
+            __syncthreads();
+            int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)total, S.whist);
+            if (nb > 1) {  // regroup by unit slot (stable): one pass per slot byte
+                uint64_t* k0 = cur ? S.kb : S.ka;
+                uint32_t* p0 = cur ? S.pb : S.pa;
+                uint64_t* k1 = cur ? S.ka : S.kb;
+                uint32_t* p1 = cur ? S.pa : S.pb;
+                const int c2 = block_radix_sort<uint32_t, true>(k0, p0, k1, p1, (int)total, 16, nb > 256 ? 32 : 24, S.whist);
+                cur = c2 ? (cur ^ 1) : cur;
             }
-            ka[e] = keep ? key_of(v) : ~0ull;
-            la[e] = lab;
-            dropped += keep ? 0u : 1u;
+            const uint64_t* rk = cur ? S.kb : S.ka;
+            const uint32_t* rp = cur ? S.pb : S.pa;
+            for (uint32_t j = tid; j < total; j += blockDim.x) {
+                const uint32_t pay = rp[j];
+                const uint32_t slot = pay >> 16;
+                const uint32_t pos = j - S.off[slot];
+                const uint32_t m = (S.off[slot + 1] - S.off[slot]) - S.drop[slot];
+                if (pos < m) {
+                    uint32_t e = pay & 0x7fffu;
+                    if (pos > 0 && rk[j] == rk[j - 1]) e |= TIE_BIT;
+                    P.stream[S.soff[slot] + pos] = (uint16_t)e;
+                }
+            }
+            if (tid < nb) P.unit_m[t0 + tid] = (S.off[tid + 1] - S.off[tid]) - S.drop[tid];
+            continue;
         }
-        if (dropped) atomicAdd(&misc[1], dropped);
-        __syncthreads();
 
-        const int cur = block_sort_keys<uint16_t>(ka, la, kb, lb, (int)total, whist);
-        const uint64_t* rk = cur ? kb : ka;
-        const uint16_t* rl = cur ? lb : la;
-        const uint32_t m = (uint32_t)total - misc[1];
-        for (uint32_t j = threadIdx.x; j < m; j += blockDim.x) {
-            uint16_t e = rl[j];
-            if (j > 0 && rk[j] == rk[j - 1]) e |= TIE_BIT;
-            stream[soff + j] = e;
+        // ---- one unit beyond the shared-memory capacity ------------------------------------
+        // (nb == 1 by construction.) Split by value into 256 ordered buckets with one stable pass
+        // into global scratch, then sort runs of consecutive buckets in shared memory.
+        const int64_t vbase = S.vbase[0], soff = S.soff[0];
+        const uint32_t n = S.n[0];
+        const int G = (int)nseg - 1;
+        uint64_t* ga = P.g_ka + soff;
+        uint32_t* gp = P.g_pa + soff;
+        uint64_t* gb = P.g_kb + soff;
+        uint32_t* gq = P.g_pb + soff;
+        // pass 0: key range
+        uint64_t kmin = ~0ull, kmax = 0ull;
+        uint32_t dropped = 0;
+        for (uint32_t e = tid; e < total; e += blockDim.x) {
+            uint64_t key;
+            uint32_t lab;
+            bool keep;
+            unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key, lab, keep);
+            if (keep) {
+                kmin = min(kmin, key);
+                kmax = max(kmax, key);
+            } else {
+                ++dropped;
+            }
         }
-        if (threadIdx.x == 0) unit_m[task] = m;
+        for (int o = 16; o > 0; o >>= 1) {
+            kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+            kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+            dropped += __shfl_xor_sync(0xffffffffu, dropped, o);
+        }
+        uint64_t* red = reinterpret_cast<uint64_t*>(S.whist);  // scratch for the block reduction
+        if (lane == 0) {
+            red[warp] = kmin;
+            red[32 + warp] = kmax;
+            red[64 + warp] = dropped;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            uint64_t a = red[lane], b = red[32 + lane], c = red[64 + lane];
+            for (int o = 16; o > 0; o >>= 1) {
+                a = min(a, __shfl_xor_sync(0xffffffffu, a, o));
+                b = max(b, __shfl_xor_sync(0xffffffffu, b, o));
+                c += __shfl_xor_sync(0xffffffffu, c, o);
+            }
+            if (lane == 0) {
+                red[96] = a;
+                red[97] = b;
+                red[98] = c;
+            }
+        }
+        __syncthreads();
+        kmin = red[96];
+        kmax = red[97];
+        const uint32_t m = total - (uint32_t)red[98];
+        __syncthreads();
+        const uint64_t span = kmax >= kmin ? kmax - kmin : 0ull;
+        const int sh = span ? max(0, 64 - __clzll((long long)span) - 8) : 0;
+
+        // pass 1: stable split by bucket = (key - kmin) >> sh (dropped entries: bucket 255)
+        {
+            const int per = (int)((((total + SORT_WARPS - 1) / SORT_WARPS) + 31) & ~31u);
+            const uint32_t s_lo = min(total, (uint32_t)warp * per), s_hi = min(total, s_lo + per);
+            uint32_t* mine = S.whist + warp * 256;
+            uint32_t* aux = S.whist + SORT_WARPS * 256;
+            for (int i = lane; i < 256; i += 32) mine[i] = 0;
+            __syncwarp();
+            for (uint32_t t = s_lo; t < s_hi; t += 32) {
+                const uint32_t e = t + lane;
+                const bool valid = e < s_hi;
+                const unsigned act = __ballot_sync(0xffffffffu, valid);
+                if (valid) {
+                    uint64_t key;
+                    uint32_t lab;
+                    bool keep;
+                    unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key, lab, keep);
+                    const unsigned d = keep ? (unsigned)((key - kmin) >> sh) : 255u;
+                    const unsigned peers = __match_any_sync(act, d);
+                    if (lane == __ffs(peers) - 1) mine[d] += __popc(peers);
+                }
+                __syncwarp();
+            }
+            __syncthreads();
+            if (tid < 256) {
+                uint32_t run = 0;
+                for (int w = 0; w < SORT_WARPS; ++w) {
+                    const uint32_t v = S.whist[w * 256 + tid];
+                    S.whist[w * 256 + tid] = run;
+                    run += v;
+                }
+                const uint32_t tot = run;
+                uint32_t inc = tot;
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += y;
+                }
+                if (lane == 31) aux[warp] = inc;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                uint32_t wbase = 0;
+                for (int w = 0; w < warp; ++w) wbase += aux[w];
+                const uint32_t dbase = wbase + inc - tot;
+                for (int w = 0; w < SORT_WARPS; ++w) S.whist[w * 256 + tid] += dbase;
+                S.boff[tid] = dbase;
+                if (tid == 255) S.boff[256] = dbase + tot;
+            }
+            __syncthreads();
+            for (uint32_t t = s_lo; t < s_hi; t += 32) {
+                const uint32_t e = t + lane;
+                const bool valid = e < s_hi;
+                const unsigned act = __ballot_sync(0xffffffffu, valid);
+                if (valid) {
+                    uint64_t key;
+                    uint32_t lab;
+                    bool keep;
+                    unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key, lab, keep);
+                    const unsigned d = keep ? (unsigned)((key - kmin) >> sh) : 255u;
+                    const unsigned peers = __match_any_sync(act, d);
+                    const uint32_t base = mine[d];
+                    const uint32_t at = base + __popc(peers & ((1u << lane) - 1u));
+                    ga[at] = key;
+                    gp[at] = lab;
+                    __syncwarp(act);
+                    if (lane == __ffs(peers) - 1) mine[d] = base + __popc(peers);
+                    __syncwarp(act);
+                }
+            }
+            __syncthreads();
+        }
+
+        // pass 2: runs of consecutive buckets that fit shared memory
+        int d0 = 0;
+        while (d0 < 256) {
+            const uint32_t start = S.boff[d0];
+            int d1 = d0 + 1;
+            while (d1 < 256 && S.boff[d1 + 1] - start <= (uint32_t)P.cap) ++d1;
+            const uint32_t cnt = S.boff[d1] - start;
+            d0 = d1;
+            if (cnt == 0) continue;
+            const uint64_t* rk;
+            const uint32_t* rp;
+            if (cnt <= (uint32_t)P.cap) {
+                for (uint32_t j = tid; j < cnt; j += blockDim.x) {
+                    S.ka[j] = ga[start + j];
+                    S.pa[j] = gp[start + j];
+                }
+                __syncthreads();
+                const int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)cnt, S.whist);
+                rk = cur ? S.kb : S.ka;
+                rp = cur ? S.pb : S.pa;
+            } else {  // a single bucket larger than shared memory (e.g. one heavily tied value)
+                const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist);
+                rk = cur ? gb + start : ga + start;
+                rp = cur ? gq + start : gp + start;
+            }
+            for (uint32_t j = tid; j < cnt; j += blockDim.x) {
+                const uint32_t pos = start + j;
+                if (pos < m) {
+                    uint32_t e = rp[j] & 0x7fffu;
+                    if (j > 0 && rk[j] == rk[j - 1]) e |= TIE_BIT;
+                    P.stream[soff + pos] = (uint16_t)e;
+                }
+            }
+            __syncthreads();
+        }
+        if (tid == 0) P.unit_m[t0] = m;
     }
 }
 
 // ------------------------------------------------------------------------------------------
 // k3_walk
 // ------------------------------------------------------------------------------------------
-constexpr int WALK_THREADS = 512;
+constexpr int WALK_THREADS = 1024;
 constexpr int WALK_WARPS = WALK_THREADS / 32;
 constexpr int WALK_MAX_GROUPS = 16;
+constexpr uint32_t WALK_BATCH_MAX_M = 3072;  // units up to this many stream entries are walked by one warp group
 
 struct WalkParams {
     UnitTables ut;
@@ -157,54 +498,150 @@ struct WalkParams {
     int64_t npairs;
     double* u_out;
     unsigned long long* bfull;  // per-CTA scratch: (maxG + 1)^2 entries each
-    unsigned long long* task_counter;
+    unsigned long long* job_counter;
+    const int32_t* jobs;
+    const int32_t* njobs;
     int maxG;
-    int tiles_per_batch;  // R tiles whose accumulators fit in shared memory at once
-    int groups;           // position chunks walked concurrently (private accumulator copies)
-    uint32_t m_lo, m_hi;  // this launch handles units with m_lo < m <= m_hi
+    int tiles_per_batch;  // solo mode: R tiles whose accumulators fit in shared memory at once
+    int groups;           // solo mode: position chunks walked concurrently (private tables)
+    int nslots;           // batch mode: warp groups (0 = batch mode unavailable: tables too large)
+    int slot_tiles;       // batch mode: warps per slot = ceil((maxG + 1) / 32)
+    int pass;             // 0: everything with m <= 65536 (uint32 tables); 1: only m > 65536 (uint64 tables)
 };
+
+// 2U from the count table (AccT entries, row stride `rpad`) for one pair.
+template <typename AccT, bool SHIFT>
+__device__ inline double pair_u(const AccT* B, size_t rpad, int l, int r, int pg, long long nL, long long nR,
+                                long long zL, long long zR) {
+    long long two;
+    if (SHIFT) {
+        two = (long long)B[(size_t)l * rpad + r] + zR * (long long)B[(size_t)l * rpad + pg] +
+              zL * (long long)B[(size_t)pg * rpad + r] + zL * zR * (long long)B[(size_t)pg * rpad + pg];
+    } else {
+        const long long a = (long long)B[(size_t)l * rpad + r] + (long long)B[(size_t)l * rpad + pg] * zR +
+                            zL * (long long)B[(size_t)pg * rpad + r];
+        const long long b = (long long)B[(size_t)r * rpad + l] + (long long)B[(size_t)r * rpad + pg] * zL +
+                            zR * (long long)B[(size_t)pg * rpad + l];
+        two = nL * nR + a - b;
+    }
+    if (nL == 0 || nR == 0) two = 0;
+    return 0.5 * (double)two;
+}
+
+__device__ inline void slot_barrier(int slot, int slot_tiles) {
+    if (slot_tiles == 1) {
+        __syncwarp();
+    } else {
+        asm volatile("bar.sync %0, %1;" ::"r"(slot + 1), "r"(slot_tiles * 32) : "memory");
+    }
+}
+
+// The inner loop shared by both modes: positions [i_lo, i_hi) of one unit's stream, lane = label R.
+template <typename AccT, bool SHIFT>
+__device__ inline void walk_range(const uint16_t* st, int i_lo, int i_hi, int R, bool live, AccT* col, size_t rpad,
+                                  uint32_t c, int lane) {
+    uint32_t cs = c;
+    for (int i0 = i_lo; i0 < i_hi; i0 += 32) {
+        const int mine = i0 + lane;
+        const uint32_t ent = mine < i_hi ? (uint32_t)st[mine] : 0u;
+        const int cnt = min(32, i_hi - i0);
+        for (int k = 0; k < cnt; ++k) {
+            const uint32_t e = __shfl_sync(0xffffffffu, ent, k);
+            const int lab = (int)(e & LAB_MASK);
+            if (!(e & TIE_BIT)) cs = c;
+            if (SHIFT) {
+                if (e & ROLE_L) {
+                    if (live) col[(size_t)lab * rpad] += (AccT)cs + (AccT)c;
+                } else {
+                    c += (lab == R) ? 1u : 0u;
+                }
+            } else {
+                if (live) col[(size_t)lab * rpad] += (AccT)cs;
+                c += (lab == R) ? 1u : 0u;
+            }
+        }
+    }
+}
 
 template <typename AccT, bool SHIFT>
 __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Gmax1 = P.maxG + 1;
-    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);        // [groups + 1][Gmax1]
-    uint32_t* nnzv = hist + (WALK_MAX_GROUPS + 1) * Gmax1;          // [Gmax1]
-    int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);             // [WALK_MAX_GROUPS + 1]
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [WALK_WARPS + 1][Gmax1]
+    uint32_t* nnzv = hist + (size_t)(WALK_WARPS + 1) * Gmax1;                // [Gmax1]
+    int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);                      // [WALK_MAX_GROUPS + 1]
     uint32_t* misc = reinterpret_cast<uint32_t*>(bounds + WALK_MAX_GROUPS + 1);  // [4]
     size_t off = (size_t)((unsigned char*)(misc + 4) - smem_raw);
     off = (off + 15) & ~size_t(15);
-    AccT* acc = reinterpret_cast<AccT*>(smem_raw + off);            // [groups][Gt][tiles_per_batch * 32]
+    AccT* acc = reinterpret_cast<AccT*>(smem_raw + off);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long* bfull = P.bfull + (size_t)blockIdx.x * Gmax1 * Gmax1;
-    const int64_t ntasks = (int64_t)P.ut.ngenes * P.ut.U;
+    const int njobs = *P.njobs;
+    const UnitTables& ut = P.ut;
 
     while (true) {
         __syncthreads();
-        if (tid == 0) {
-            const unsigned long long t = atomicAdd(P.task_counter, 1ull);
-            misc[0] = (uint32_t)(t & 0xffffffffu);
-            misc[1] = (uint32_t)(t >> 32);
-        }
+        if (tid == 0) misc[0] = (uint32_t)atomicAdd(P.job_counter, 1ull);
         __syncthreads();
-        const int64_t task = (int64_t)(((uint64_t)misc[1] << 32) | misc[0]);
-        if (task >= ntasks) break;
-        const uint32_t m = P.unit_m[task];
-        if (!(m > P.m_lo && m <= P.m_hi)) continue;
-        const int g = (int)(task / P.ut.U), u = (int)(task % P.ut.U);
-        const int first = P.ut.unit_first[u], G = P.ut.unit_ncomb[u];
-        const int Gt = G + 1;
-        int64_t vbase, soff;
-        uint32_t n;
-        unit_range(P.ut, g, u, vbase, n, soff);
-        const uint16_t* st = P.stream + soff;
+        const int job = (int)misc[0];
+        if (job >= njobs) break;
+        const int64_t t0 = P.jobs[job], t1 = P.jobs[job + 1];
+        const int nb = (int)(t1 - t0);
 
-        // Position chunks aligned to tie-run starts.
+        // ---- batch mode: several small units at a time, one warp group ("slot") each --------
+        bool batch = false;
+        if (sizeof(AccT) == 4 && P.nslots > 0) {
+            batch = nb > 1 || P.unit_m[t0] <= WALK_BATCH_MAX_M;
+        }
+        if (batch) {
+            if (P.pass != 0) continue;
+            const int stl = P.slot_tiles;
+            const int slot = warp / stl, wtile = warp % stl;
+            const size_t rpad = (size_t)stl * 32;
+            if (slot < P.nslots) {
+                uint32_t* sacc = reinterpret_cast<uint32_t*>(acc) + (size_t)slot * Gmax1 * rpad;
+                uint32_t* shist = hist + (size_t)slot * Gmax1;
+                const int sthreads = stl * 32, stid = wtile * 32 + lane;
+                for (int i = slot; i < nb; i += P.nslots) {
+                    const int64_t task = t0 + i;
+                    const UnitInfo ui = unit_info(ut, task);
+                    const int Gt = ui.G + 1;
+                    const uint32_t m = P.unit_m[task];
+                    const uint16_t* st = P.stream + ui.soff;
+                    for (int k = stid; k < Gt * (int)rpad; k += sthreads) sacc[k] = 0;
+                    for (int k = stid; k < Gt; k += sthreads) shist[k] = 0;
+                    slot_barrier(slot, stl);
+                    for (uint32_t k = stid; k < m; k += sthreads) {
+                        const uint32_t e = st[k];
+                        if (!(SHIFT && (e & ROLE_L))) atomicAdd(&shist[e & LAB_MASK], 1u);
+                    }
+                    const int R = wtile * 32 + lane;
+                    walk_range<uint32_t, SHIFT>(st, 0, (int)m, R, R < Gt, sacc + R, rpad, 0u, lane);
+                    slot_barrier(slot, stl);
+                    for (int pp = P.pair_ptr[ui.u] + stid; pp < P.pair_ptr[ui.u + 1]; pp += sthreads) {
+                        const int l = P.pair_l[pp], r = P.pair_r[pp];
+                        const long long nL = ut.ncells_dev[ui.first + l], nR = ut.ncells_dev[ui.first + r];
+                        const long long zL = nL - (long long)shist[l], zR = nR - (long long)shist[r];
+                        P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] =
+                            pair_u<uint32_t, SHIFT>(sacc, rpad, l, r, ui.G, nL, nR, zL, zR);
+                    }
+                    slot_barrier(slot, stl);
+                }
+            }
+            continue;
+        }
+
+        // ---- solo mode: one unit, all warps, position chunks with private tables ------------
+        const uint32_t m = P.unit_m[t0];
+        const bool wide = m > 65536u;
+        if ((P.pass == 0) == wide) continue;
+        const UnitInfo ui = unit_info(ut, t0);
+        const int G = ui.G, Gt = G + 1;
+        const uint16_t* st = P.stream + ui.soff;
         const int ntiles = (Gt + 31) / 32;
         const int tpb = min(P.tiles_per_batch, ntiles);
         int groups = max(1, min(P.groups, WALK_WARPS / tpb));
-        if (m < 2048u) groups = 1;
         if (tid <= groups) {
             int64_t b = tid == groups ? (int64_t)m : ((int64_t)m * tid) / groups;
             while (b < (int64_t)m && b > 0 && (st[b] & TIE_BIT)) ++b;
@@ -213,57 +650,38 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         for (int k = tid; k < (groups + 1) * Gmax1; k += blockDim.x) hist[k] = 0;
         __syncthreads();
         for (uint32_t i = tid; i < m; i += blockDim.x) {
-            const uint16_t e = st[i];
+            const uint32_t e = st[i];
             if (SHIFT && (e & ROLE_L)) continue;
             int cg = 0;
             while (cg + 1 < groups && (int)i >= bounds[cg + 1]) ++cg;
             atomicAdd(&hist[(cg + 1) * Gmax1 + (e & LAB_MASK)], 1u);
         }
         __syncthreads();
-        // hist[cg][R] becomes the count of label R before chunk cg; nnzv the total.
-        for (int R = tid; R < Gt; R += blockDim.x) {
+        for (int R = tid; R < Gt; R += blockDim.x) {  // hist[cg][R]: label-R entries before chunk cg
             uint32_t run = 0;
             for (int cg = 0; cg <= groups; ++cg) {
-                const uint32_t v = hist[cg * Gmax1 + R];
-                run += v;
+                run += hist[cg * Gmax1 + R];
                 hist[cg * Gmax1 + R] = run;
             }
             nnzv[R] = run;
         }
         __syncthreads();
-
         for (int tb = 0; tb < ntiles; tb += tpb) {
             const int bt = min(tpb, ntiles - tb);
-            const int rpad = bt * 32;
-            for (int k = tid; k < groups * Gt * rpad; k += blockDim.x) acc[k] = 0;
+            const size_t rpad = (size_t)bt * 32;
+            for (int k = tid; k < groups * Gt * (int)rpad; k += blockDim.x) acc[k] = 0;
             __syncthreads();
             if (warp < groups * bt) {
                 const int cg = warp / bt, tile = tb + warp % bt;
                 const int R = tile * 32 + lane;
                 const bool live = R < Gt;
-                AccT* row0 = acc + (size_t)cg * Gt * rpad + (R - tb * 32);
-                uint32_t c = live ? hist[cg * Gmax1 + R] : 0u;
-                uint32_t cs = c;
-                const int i_hi = bounds[cg + 1];
-                for (int i = bounds[cg]; i < i_hi; ++i) {
-                    const uint16_t e = st[i];
-                    const int lab = e & LAB_MASK;
-                    if (!(e & TIE_BIT)) cs = c;
-                    if (SHIFT) {
-                        if (e & ROLE_L) {
-                            if (live) row0[(size_t)lab * rpad] += (AccT)cs + (AccT)c;
-                        } else {
-                            c += (lab == R) ? 1u : 0u;
-                        }
-                    } else {
-                        if (live) row0[(size_t)lab * rpad] += (AccT)cs;
-                        c += (lab == R) ? 1u : 0u;
-                    }
-                }
+                walk_range<AccT, SHIFT>(st, bounds[cg], bounds[cg + 1], R, live,
+                                        acc + (size_t)cg * Gt * rpad + (R - tb * 32), rpad,
+                                        live ? hist[cg * Gmax1 + R] : 0u, lane);
             }
             __syncthreads();
-            for (int k = tid; k < Gt * rpad; k += blockDim.x) {
-                const int L = k / rpad, R = tb * 32 + k % rpad;
+            for (int k = tid; k < Gt * (int)rpad; k += blockDim.x) {
+                const int L = k / (int)rpad, R = tb * 32 + k % (int)rpad;
                 if (R < Gt) {
                     unsigned long long s = 0;
                     for (int cg = 0; cg < groups; ++cg) s += (unsigned long long)acc[(size_t)cg * Gt * rpad + k];
@@ -272,36 +690,22 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
             }
             __syncthreads();
         }
-
-        // Pairs of this unit.
-        const int pg = G;  // probe label
-        for (int pp = P.pair_ptr[u] + tid; pp < P.pair_ptr[u + 1]; pp += blockDim.x) {
+        for (int pp = P.pair_ptr[ui.u] + tid; pp < P.pair_ptr[ui.u + 1]; pp += blockDim.x) {
             const int l = P.pair_l[pp], r = P.pair_r[pp];
-            const long long nL = P.ut.ncells_dev[first + l], nR = P.ut.ncells_dev[first + r];
+            const long long nL = ut.ncells_dev[ui.first + l], nR = ut.ncells_dev[ui.first + r];
             const long long zL = nL - (long long)nnzv[l], zR = nR - (long long)nnzv[r];
-            long long two;
-            if (SHIFT) {
-                two = (long long)bfull[(size_t)l * Gt + r] + zR * (long long)bfull[(size_t)l * Gt + pg] +
-                      zL * (long long)bfull[(size_t)pg * Gt + r] + zL * zR * (long long)bfull[(size_t)pg * Gt + pg];
-            } else {
-                const long long a = (long long)bfull[(size_t)l * Gt + r] + (long long)bfull[(size_t)l * Gt + pg] * zR +
-                                    zL * (long long)bfull[(size_t)pg * Gt + r];
-                const long long b = (long long)bfull[(size_t)r * Gt + l] + (long long)bfull[(size_t)r * Gt + pg] * zL +
-                                    zR * (long long)bfull[(size_t)pg * Gt + l];
-                two = nL * nR + a - b;
-            }
-            if (nL == 0 || nR == 0) two = 0;
-            P.u_out[(size_t)g * P.npairs + P.pair_out[pp]] = 0.5 * (double)two;
+            P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] =
+                pair_u<unsigned long long, SHIFT>(bfull, (size_t)Gt, l, r, G, nL, nR, zL, zR);
         }
     }
 }
 
 // ------------------------------------------------------------------------------------------
-// k3_ties: tie term per pair. One CTA per (gene, unit); one thread per pair walks the tie runs.
+// k3_ties: tie term per pair. One CTA per (gene, unit); one thread per pair walks the stream.
 // A run contributes t(t^2-1) with t = (entries of the left label in L role) + (entries of the
 // right label in R role); the zeros of a group join the run at value 0 (R role) / -lfc (L role),
-// which is where the probe entries sit. Runs where t <= 1 add exactly 0 and are skipped, so the
-// double accumulation visits the same non-zero terms in the same order as the reference.
+// which is where the probe entries sit. Runs where t <= 1 add exactly 0, so the double
+// accumulation visits the same non-zero terms in the same order as the reference.
 // ------------------------------------------------------------------------------------------
 struct TieParams {
     UnitTables ut;
@@ -310,37 +714,23 @@ struct TieParams {
     const int32_t *pair_ptr, *pair_l, *pair_r, *pair_out;
     int64_t npairs;
     double* t_out;
-    uint32_t* run_scratch;  // per CTA: compacted tie-run table
-    uint32_t run_cap;       // entries per CTA
-    int maxG;
 };
 
-// Compacted representation per CTA: a list of "events" (run id, label|role, count) for every
-// (run, label, role) with a non-zero count, restricted to runs that can contribute (size >= 2 or
-// containing a probe). Built by one pass over the stream; then each pair thread scans the events.
 template <bool SHIFT>
 __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
     const int64_t task = blockIdx.x;
-    const int g = (int)(task / P.ut.U), u = (int)(task % P.ut.U);
-    const int first = P.ut.unit_first[u], G = P.ut.unit_ncomb[u];
-    int64_t vbase, soff;
-    uint32_t n;
-    unit_range(P.ut, g, u, vbase, n, soff);
-    const uint16_t* st = P.stream + soff;
+    const UnitInfo ui = unit_info(P.ut, task);
+    const int G = ui.G;
+    const uint16_t* st = P.stream + ui.soff;
     const uint32_t m = P.unit_m[task];
-    __shared__ uint32_t s_nnz[1];
-    // zeros per label need the stored non-zero count: count R-role entries per label on the fly
-    // (per pair thread, below) - cheap relative to the run scan because it is fused into it.
-    (void)s_nnz;
-    for (int pp = P.pair_ptr[u] + threadIdx.x; pp < P.pair_ptr[u + 1]; pp += blockDim.x) {
+    for (int pp = P.pair_ptr[ui.u] + threadIdx.x; pp < P.pair_ptr[ui.u + 1]; pp += blockDim.x) {
         const int l = P.pair_l[pp], r = P.pair_r[pp];
-        const long long nL = P.ut.ncells_dev[first + l], nR = P.ut.ncells_dev[first + r];
-        // First pass: stored non-zero counts of the two labels.
-        long long cl = 0, cr = 0;
+        const long long nL = P.ut.ncells_dev[ui.first + l], nR = P.ut.ncells_dev[ui.first + r];
+        long long cl = 0, cr = 0;  // stored non-zero entries of the two labels
         for (uint32_t i = 0; i < m; ++i) {
-            const uint16_t e = st[i];
+            const uint32_t e = st[i];
             if (SHIFT && (e & ROLE_L)) continue;
-            const int lab = e & LAB_MASK;
+            const int lab = (int)(e & LAB_MASK);
             cl += lab == l;
             cr += lab == r;
         }
@@ -359,8 +749,8 @@ __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
             }
             if (i == m) break;
             open = true;
-            const uint16_t e = st[i];
-            const int lab = e & LAB_MASK;
+            const uint32_t e = st[i];
+            const int lab = (int)(e & LAB_MASK);
             const bool roleL = SHIFT ? (e & ROLE_L) != 0 : false;
             if (lab == G) {  // probe: the zeros of the pair's groups sit here
                 if (SHIFT) {
@@ -376,7 +766,7 @@ __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
             }
         }
         if (nL == 0 || nR == 0) tie = 0.0;
-        P.t_out[(size_t)g * P.npairs + P.pair_out[pp]] = tie;
+        P.t_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] = tie;
     }
 }
 
@@ -385,9 +775,11 @@ __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
 void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, double lfc, double* d_u, double* d_t) {
     if (L.U == 0 || T.ngenes == 0 || L.npairs == 0) return;
     if (L.maxG > MAX_LABELS) throw Error("more than 16383 groups compared inside one block are not supported");
+    if (L.maxG + 1 > MAXSEG) throw Error("more than 4095 groups compared inside one block are not supported");
     const bool shift = lfc != 0.0;
     const int mult = shift ? 2 : 1;
     const int64_t ntasks = (int64_t)T.ngenes * L.U;
+    if (ntasks > 2000000000ll) throw Error("too many (gene, block) units");
 
     int64_t nnz_used = 0;
     SB_CUDA(cudaMemcpyAsync(&nnz_used, T.row_ptr + T.ngenes, 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -406,37 +798,55 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
 
     ctx->stream_lab.reserve((size_t)stream_len * 2 + 64);
     ctx->unit_m.reserve((size_t)ntasks * 4 + 64);
+    ctx->jobs.reserve((size_t)(ntasks + 2) * 4 + 64);
     ctx->flags.reserve(64);
     unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->flags.as<char>() + 16);
+    int32_t* njobs = reinterpret_cast<int32_t*>(ctx->flags.as<char>() + 32);
+    int32_t* jobs = ctx->jobs.as<int32_t>();
+
+    // ---- plan ----
+    const size_t fixed = sort_fixed_bytes();
+    int cap = (int)((ctx->smem_optin - fixed) / 24);
+    cap &= ~31;
+    const size_t sort_smem = (size_t)cap * 24 + fixed;
+    const uint32_t small_max = (uint32_t)cap / 2, window = (uint32_t)cap - small_max;
+    const int maxb = std::max(1, std::min(MAXB, MAXSEG / (L.maxG + 1)));
+    SB_LAUNCH(ctx, k3_plan, 1, 1024, 0, ut, small_max, window, maxb, jobs, njobs);
 
     // ---- sort ----
-    const size_t fixed = (size_t)SORT_HIST_WORDS * 4 + (size_t)(L.maxG + 2) * 4 + 64;
-    int cap = (int)((ctx->smem_optin - fixed) / 20);
-    cap &= ~31;
-    const size_t sort_smem = (size_t)cap * 20 + fixed;
-    // Units beyond the shared-memory capacity are sorted through global scratch.
     int64_t max_cells = 0;
     for (int u = 0; u < L.U; ++u) {
         int64_t s = 0;
         for (int k = 0; k < L.unit_ncomb[u]; ++k) s += L.ncells_dev[L.unit_first[u] + k];
         max_cells = std::max(max_cells, s);
     }
-    const bool may_spill = mult * (std::min<int64_t>(max_cells, nnz_used) + 1) > cap;
-    uint64_t *gka = nullptr, *gkb = nullptr;
-    uint16_t *gla = nullptr, *glb = nullptr;
-    if (may_spill) {
+    const int64_t max_m = mult * (std::min<int64_t>(max_cells, nnz_used) + 1);
+    if (max_m > 2000000000ll) throw Error("a (gene, block) unit with more than 2e9 entries is not supported");
+    SortParams sp;
+    sp.ut = ut;
+    sp.vals = T.vals;
+    sp.shift = lfc;
+    sp.cap = cap;
+    sp.maxG = L.maxG;
+    sp.stream = ctx->stream_lab.as<uint16_t>();
+    sp.unit_m = ctx->unit_m.as<uint32_t>();
+    sp.g_ka = sp.g_kb = nullptr;
+    sp.g_pa = sp.g_pb = nullptr;
+    if (max_m > cap) {  // some unit may not fit shared memory: scratch laid out like the stream
         ctx->sort_keys.reserve((size_t)stream_len * 16 + 64);
-        ctx->sort_labs.reserve((size_t)stream_len * 4 + 64);
-        gka = ctx->sort_keys.as<uint64_t>();
-        gkb = gka + stream_len;
-        gla = ctx->sort_labs.as<uint16_t>();
-        glb = gla + stream_len;
+        ctx->sort_labs.reserve((size_t)stream_len * 8 + 64);
+        sp.g_ka = ctx->sort_keys.as<uint64_t>();
+        sp.g_kb = sp.g_ka + stream_len;
+        sp.g_pa = ctx->sort_labs.as<uint32_t>();
+        sp.g_pb = sp.g_pa + stream_len;
     }
+    sp.jobs = jobs;
+    sp.njobs = njobs;
+    sp.job_counter = counter;
     allow_smem(k3_sort, sort_smem);
     SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
     const int sort_grid = (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count);
-    SB_LAUNCH(ctx, k3_sort, sort_grid, SORT_THREADS, sort_smem, ut, T.vals, lfc, cap, L.maxG, ctx->stream_lab.as<uint16_t>(),
-              ctx->unit_m.as<uint32_t>(), gka, gkb, gla, glb, counter);
+    SB_LAUNCH(ctx, k3_sort, sort_grid, SORT_THREADS, sort_smem, sp);
     phase_mark(ctx, PH_SORT);
 
     // ---- walk ----
@@ -450,43 +860,51 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     wp.pair_out = L.d_pair_out;
     wp.npairs = L.npairs;
     wp.u_out = d_u;
-    wp.task_counter = counter;
+    wp.job_counter = counter;
+    wp.jobs = jobs;
+    wp.njobs = njobs;
     wp.maxG = L.maxG;
     const int Gt = L.maxG + 1;
     const int ntiles = (Gt + 31) / 32;
-    const size_t walk_fixed = ((size_t)(WALK_MAX_GROUPS + 1) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32;
+    const size_t walk_fixed = ((size_t)(WALK_WARPS + 1) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32;
     const int walk_grid_max = ctx->sm_count * 2;
     ctx->plan_tmp.reserve((size_t)walk_grid_max * Gt * Gt * 8 + 64);
     wp.bfull = ctx->plan_tmp.as<unsigned long long>();
 
-    const int64_t max_m = mult * (std::min<int64_t>(max_cells, nnz_used) + 1);
     for (int pass = 0; pass < 2; ++pass) {
         const size_t acc_size = pass == 0 ? 4 : 8;
         if (pass == 1 && max_m <= 65536) break;
-        wp.m_lo = pass == 0 ? 0u : 65536u;
-        wp.m_hi = pass == 0 ? 65536u : 0xffffffffu;
-        // Aim for two CTAs per SM; use what is left for private accumulator copies.
-        const size_t budget = std::min<size_t>(ctx->smem_optin, (size_t)110 * 1024) - walk_fixed;
-        const size_t big_budget = ctx->smem_optin - walk_fixed;
+        wp.pass = pass;
         const size_t per_tile = (size_t)Gt * 32 * acc_size;
+        if (walk_fixed + per_tile > ctx->smem_optin) {
+            throw Error("too many groups inside one block for the shared-memory count table");
+        }
+        const size_t budget = ctx->smem_optin - walk_fixed;
+        // batch mode needs every label column of a unit resident: slot = ntiles warps + one uint32 table
+        wp.slot_tiles = ntiles;
+        wp.nslots = 0;
+        if (pass == 0 && per_tile * ntiles <= budget && ntiles <= WALK_WARPS) {
+            int ns = (int)std::min<size_t>(budget / (per_tile * ntiles), (size_t)(WALK_WARPS / ntiles));
+            if (ntiles > 1) ns = std::min(ns, 15);  // named barriers 1..15
+            wp.nslots = std::max(0, ns);
+        }
         int tpb, groups;
-        size_t smem;
         if (per_tile * ntiles <= budget) {
-            tpb = ntiles;
+            tpb = std::min(ntiles, WALK_WARPS);
             groups = (int)std::min<size_t>(budget / (per_tile * ntiles), (size_t)WALK_MAX_GROUPS);
             groups = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
-            smem = walk_fixed + per_tile * ntiles * groups;
         } else {
-            tpb = (int)std::max<size_t>(1, std::min<size_t>(big_budget / per_tile, (size_t)ntiles));
-            if (per_tile > big_budget) throw Error("too many groups inside one block for the shared-memory count table");
+            tpb = (int)std::max<size_t>(1, std::min<size_t>(budget / per_tile, (size_t)ntiles));
             tpb = std::min(tpb, WALK_WARPS);
             groups = 1;
-            smem = walk_fixed + per_tile * tpb;
         }
         wp.tiles_per_batch = tpb;
         wp.groups = groups;
+        size_t need = per_tile * tpb * groups;
+        if (wp.nslots > 0) need = std::max(need, per_tile * ntiles * wp.nslots);
+        const size_t smem = walk_fixed + need;
         SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
-        const int grid = (int)std::min<int64_t>(ntasks, walk_grid_max);
+        const int grid = (int)std::min<int64_t>(ntasks, smem * 2 <= ctx->smem_optin ? walk_grid_max : ctx->sm_count);
         if (pass == 0) {
             if (shift) {
                 allow_smem(k3_walk<uint32_t, true>, smem);
@@ -517,10 +935,6 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         tp.pair_out = L.d_pair_out;
         tp.npairs = L.npairs;
         tp.t_out = d_t;
-        tp.run_scratch = nullptr;
-        tp.run_cap = 0;
-        tp.maxG = L.maxG;
-        if (ntasks > 2147483647ll) throw Error("too many (gene, block) units for the tie-term kernel");
         if (shift) {
             SB_LAUNCH(ctx, k3_ties<true>, (unsigned)ntasks, 256, 0, tp);
         } else {
