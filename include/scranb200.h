@@ -161,6 +161,29 @@ int scranb200_fill_i32(scranb200_ctx* ctx, int32_t* d_ptr, int64_t n, int32_t va
  * the column strictly greater), NaN entries ignored; INT32_MAX if a row has none. */
 int scranb200_compute_min_rank(scranb200_ctx* ctx, const double* x, int64_t nrow, int64_t ncol, int32_t* out);
 
+/* ---- computeMinRank without device allocation ------------------------------------------------
+ * No counterpart in the reference: this exists for callers of this library that must not, or
+ * cannot, allocate device memory while it runs. Typical cases: the host application has given
+ * the whole GPU to its own memory pool, so a cudaMalloc from inside a library fails or competes
+ * with the pool; or the call sits on a latency-sensitive path where the device-wide stall of
+ * cudaMalloc / cudaFree is not acceptable. Same result as scranb200_compute_min_rank, but:
+ *   - d_x (nrow x ncol column-major, NaN = NA) and d_out (int32[nrow]) are DEVICE pointers that
+ *     the caller owns; nothing is copied to or from the host.
+ *   - all scratch lives in a fixed 16 MiB array inside the library image. Every GPU that loads
+ *     libscranb200.so holds those 16 MiB until the process exits. Limits: ncol <= 4096, and
+ *     nrow * 24 bytes must fit the array (about 696,000 rows) when a column is too long for the
+ *     shared-memory sort; beyond that the call fails with a message and computes nothing.
+ *   - the call issues no cudaMalloc / cudaFree and uses no allocating library routine. The first
+ *     call on a device looks up the array's device address (cudaGetSymbolAddress); make that
+ *     first call outside any stream capture.
+ *   - all calls on a device share the one array and it keeps the previous call's contents; the
+ *     call re-initialises what it reads. Two calls running on the same GPU at the same time
+ *     (from two contexts or threads) race on it: serialise them.
+ * The call returns after its work on the context's stream has finished; inputs written on
+ * another stream must be complete before it is made. */
+int scranb200_compute_min_rank_static(scranb200_ctx* ctx, const double* d_x, int64_t nrow, int64_t ncol,
+                                      int32_t* d_out);
+
 /* ---- synthetic input (bench.py), generated on the device -------------
  * Writes a CSC matrix of genes [g0, g1) x ncells log-counts into device memory owned by the
  * returned matrix. density < 0: natural Poisson density (config 1). */

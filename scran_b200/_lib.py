@@ -60,6 +60,7 @@ def _signatures():
         "scranb200_score_finish_dev": (C.c_int, [c_ctx, c_plan, i64, i64, _p, _p]),
         "scranb200_fill_i32": (C.c_int, [c_ctx, _p, i64, i32]),
         "scranb200_compute_min_rank": (C.c_int, [c_ctx, _p, i64, i64, _p]),
+        "scranb200_compute_min_rank_static": (C.c_int, [c_ctx, _p, i64, i64, _p]),
         "scranb200_synth_csc": (C.c_int, [c_ctx, i64, i64, i64, i64, _p, C.c_int, dbl, u64, PP]),
     }
 

@@ -327,3 +327,116 @@ void run_min_rank_matrix(scranb200_ctx* ctx, const double* d_x, int64_t nrow, in
 }
 
 }  // namespace sb
+
+// ------------------------------------------------------------------------------------------
+// scranb200_compute_min_rank_static: computeMinRank without any device allocation.
+//
+// The regular min-rank path takes its scratch (column descriptors and, for columns longer than
+// the shared-memory sort, the ping-pong sort buffers) from growable cudaMalloc'ed buffers of the
+// context. Two kinds of caller cannot live with that: a host application that has handed the
+// whole device to its own memory pool, so that a cudaMalloc issued from inside this library
+// fails or fights the pool; and a caller on a latency-sensitive path, where cudaMalloc/cudaFree
+// stall the device. For them this variant keeps its scratch in the fixed array below, which is
+// part of the library image: every GPU that loads libscranb200.so carries these 16 MiB until the
+// process exits, whether or not the entry point is ever called.
+// ------------------------------------------------------------------------------------------
+namespace sb {
+namespace {
+
+constexpr size_t STATIC_SCRATCH_BYTES = (size_t)16 << 20;
+constexpr int STATIC_MAX_COLS = 4096;                       // descriptor table: 4 int32 per column
+constexpr size_t STATIC_DESC_BYTES = (size_t)STATIC_MAX_COLS * 4 * 4;
+
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+// Device address of g_static_scratch per device ordinal. In host code the symbol itself is only a
+// handle; the address a kernel can use comes from cudaGetSymbolAddress, asked for once per device
+// while that device is current.
+constexpr int STATIC_MAX_DEVICES = 64;
+unsigned char* g_static_ptr[STATIC_MAX_DEVICES] = {nullptr};
+
+unsigned char* static_scratch_for(scranb200_ctx* ctx) {
+    if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) throw Error("device ordinal too large for the static scratch table");
+    if (!g_static_ptr[ctx->device]) {
+        void* p = nullptr;
+        SB_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));  // ctx_guard has made ctx->device current
+        g_static_ptr[ctx->device] = reinterpret_cast<unsigned char*>(p);
+    }
+    return g_static_ptr[ctx->device];
+}
+
+// Every column is ranked as it is and contributes to table 0. Written by the device into the
+// static array (device code may name the array directly).
+__global__ void static_fill_descriptors(int ncols) {
+    int32_t* d = reinterpret_cast<int32_t*>(g_static_scratch);
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < ncols) {
+        d[c] = c;                  // col_src
+        d[ncols + c] = 0;          // tab_direct
+        d[2 * ncols + c] = -1;     // tab_flipped
+        d[3 * ncols + c] = 0;      // is_auc
+    }
+}
+
+}  // namespace
+}  // namespace sb
+
+extern "C" int scranb200_compute_min_rank_static(scranb200_ctx* ctx, const double* d_x, int64_t nrow, int64_t ncol,
+                                                  int32_t* d_out) {
+    using namespace sb;
+    try {
+        ctx_guard(ctx);
+        if (nrow < 0 || ncol < 0) throw Error("negative matrix dimension");
+        if (ncol > STATIC_MAX_COLS) throw Error("compute_min_rank_static: more than 4096 columns exceed the static scratch");
+        if (nrow > 2147483647ll / 2) throw Error("too many rows to rank");
+        if (nrow == 0) return 0;
+        unsigned char* base = static_scratch_for(ctx);
+
+        RankParams rp;
+        rp.x = d_x;
+        rp.ld = nrow;
+        rp.ngenes = (int)nrow;
+        rp.ncols = (int)ncol;
+        const size_t fixed = (size_t)SORT_HIST_WORDS * 4 + 64;
+        int cap = (int)((ctx->smem_optin - fixed) / 24);
+        cap &= ~31;
+        rp.cap = cap;
+        rp.col_src = reinterpret_cast<const int32_t*>(base);
+        rp.tab_direct = rp.col_src + ncol;
+        rp.tab_flipped = rp.tab_direct + ncol;
+        rp.is_auc = rp.tab_flipped + ncol;
+        rp.minrank = d_out;
+        rp.g_ka = rp.g_kb = nullptr;
+        rp.g_pa = rp.g_pb = nullptr;
+        int grid = (int)std::min<int64_t>(ncol, ctx->sm_count);
+        if (nrow > cap) {  // columns are sorted through the static array: 24 bytes per row and CTA
+            const size_t per_cta = (size_t)nrow * 24;
+            const size_t avail = STATIC_SCRATCH_BYTES - STATIC_DESC_BYTES;
+            if (per_cta > avail) {
+                throw Error("compute_min_rank_static: matrix too tall for the 16 MiB static scratch (limit about 696,000 rows); "
+                            "use scranb200_compute_min_rank");
+            }
+            grid = (int)std::min<size_t>((size_t)grid, avail / per_cta);
+            unsigned char* s = base + STATIC_DESC_BYTES;
+            rp.g_ka = reinterpret_cast<uint64_t*>(s);
+            rp.g_kb = rp.g_ka + (size_t)grid * nrow;
+            rp.g_pa = reinterpret_cast<uint32_t*>(rp.g_kb + (size_t)grid * nrow);
+            rp.g_pb = rp.g_pa + (size_t)grid * nrow;
+        }
+        // The array still holds whatever the previous call left: the descriptors are rewritten
+        // here, the sort buffers are fully written before they are read, and the output starts
+        // from "no rank yet".
+        SB_LAUNCH(ctx, k5_fill_i32, (unsigned)ceil_div(nrow, 256), 256, 0, d_out, nrow, INT32_MAX);
+        if (ncol > 0) {
+            SB_LAUNCH(ctx, static_fill_descriptors, (unsigned)ceil_div(ncol, 256), 256, 0, (int)ncol);
+            const size_t smem = (size_t)cap * 24 + fixed;
+            allow_smem(k5_rank, smem);
+            SB_LAUNCH(ctx, k5_rank, grid, SORT_THREADS, smem, rp);
+        }
+        SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    } catch (const std::exception& e) {
+        sb::set_last_error(e.what());
+        return 1;
+    }
+    return 0;
+}
