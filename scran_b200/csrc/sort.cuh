@@ -15,18 +15,39 @@ namespace sb {
 
 constexpr int SORT_THREADS = 1024;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
+#ifndef SORT_UNROLL
+#define SORT_UNROLL 1
+#endif
 constexpr int SORT_HIST_WORDS = SORT_WARPS * 256 + 64;  // + aux words
 
 // whist: SORT_HIST_WORDS uint32 of shared memory. Returns 0 if the result is in (ka, pa), 1 if
 // in (kb, pb). Must be called by all SORT_THREADS threads with identical arguments.
+// Lanes with equal 8-bit digits, from eight ballots. `valid` lanes only; others get themselves.
+__device__ __forceinline__ unsigned match_digit(unsigned d, bool valid, int lane) {
+#ifdef SORT_USE_MATCH
+    return __match_any_sync(0xffffffffu, valid ? d : 256u + (unsigned)lane);
+#else
+    unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    return valid ? peers : (1u << lane);
+#endif
+}
+
 template <typename P, bool FROM_PAYLOAD = false>
 __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, int bit_lo, int bit_hi,
                                 uint32_t* whist) {
+    constexpr int U = SORT_UNROLL;  // 32-element groups in flight per warp: their loads and matches overlap
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint32_t* aux = whist + SORT_WARPS * 256;  // [0..7] warp sums, [32] skip flag
     const int per = (((n + SORT_WARPS - 1) / SORT_WARPS) + 31) & ~31;
     const int s_lo = min(n, warp * per), s_hi = min(n, s_lo + per);
     uint32_t* mine = whist + warp * 256;
+    const unsigned lt = (1u << lane) - 1u;
     int cur = 0;
     for (int bit = bit_lo; bit < bit_hi; bit += 8) {
         uint64_t* sk = cur ? kb : ka;
@@ -36,16 +57,23 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
         for (int i = lane; i < 256; i += 32) mine[i] = 0;
         if (tid == 0) aux[32] = 0;
         __syncwarp();
-        for (int t = s_lo; t < s_hi; t += 32) {
-            const int i = t + lane;
-            const bool valid = i < s_hi;
-            const unsigned act = __ballot_sync(0xffffffffu, valid);
-            if (valid) {
-                const unsigned d = FROM_PAYLOAD ? ((unsigned)(sp[i] >> bit) & 255u) : ((unsigned)(sk[i] >> bit) & 255u);
-                const unsigned peers = __match_any_sync(act, d);
-                if (lane == __ffs(peers) - 1) mine[d] += __popc(peers);
+        // ---- per-warp digit histogram of the warp's slice -----------------------------------
+        for (int t = s_lo; t < s_hi; t += 32 * U) {
+            unsigned d[U], peers[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = t + 32 * u + lane;
+                // lanes past the end get a digit nobody else has, so that they match only themselves
+                d[u] = 256u + (unsigned)lane;
+                if (i < s_hi) d[u] = FROM_PAYLOAD ? ((unsigned)(sp[i] >> bit) & 255u) : ((unsigned)(sk[i] >> bit) & 255u);
             }
-            __syncwarp();
+#pragma unroll
+            for (int u = 0; u < U; ++u) peers[u] = match_digit(d[u], d[u] < 256u, lane);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (d[u] < 256u && (peers[u] & lt) == 0u) mine[d[u]] += __popc(peers[u]);
+                __syncwarp();
+            }
         }
         __syncthreads();
         if (tid < 256) {
@@ -72,22 +100,39 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
         __syncthreads();
         const bool skip = aux[32] != 0;
         if (!skip) {
-            for (int t = s_lo; t < s_hi; t += 32) {
-                const int i = t + lane;
-                const bool valid = i < s_hi;
-                const unsigned act = __ballot_sync(0xffffffffu, valid);
-                if (valid) {
-                    const uint64_t k = sk[i];
-                    const P pl = sp[i];
-                    const unsigned d = FROM_PAYLOAD ? ((unsigned)(pl >> bit) & 255u) : ((unsigned)(k >> bit) & 255u);
-                    const unsigned peers = __match_any_sync(act, d);
-                    const uint32_t base = mine[d];
-                    const uint32_t at = base + __popc(peers & ((1u << lane) - 1u));
-                    dk[at] = k;
-                    dp[at] = pl;
-                    __syncwarp(act);
-                    if (lane == __ffs(peers) - 1) mine[d] = base + __popc(peers);
-                    __syncwarp(act);
+            // ---- stable reorder: rank inside the 32 by lane order, base from the warp's counters ---
+            for (int t = s_lo; t < s_hi; t += 32 * U) {
+                uint64_t k[U];
+                P pl[U];
+                unsigned d[U], peers[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = t + 32 * u + lane;
+                    d[u] = 256u + (unsigned)lane;
+                    if (i < s_hi) {
+                        k[u] = sk[i];
+                        pl[u] = sp[i];
+                        d[u] = FROM_PAYLOAD ? ((unsigned)(pl[u] >> bit) & 255u) : ((unsigned)(k[u] >> bit) & 255u);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) peers[u] = match_digit(d[u], d[u] < 256u, lane);
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const bool live = d[u] < 256u;
+                    const bool leader = (peers[u] & lt) == 0u;
+                    uint32_t base = 0;
+                    if (live && leader) {  // the first lane of every digit group advances the counter
+                        base = mine[d[u]];
+                        mine[d[u]] = base + __popc(peers[u]);
+                    }
+                    base = __shfl_sync(0xffffffffu, base, __ffs(peers[u]) - 1);
+                    if (live) {
+                        const uint32_t at = base + __popc(peers[u] & lt);
+                        dk[at] = k[u];
+                        dp[at] = pl[u];
+                    }
+                    __syncwarp();
                 }
             }
             cur ^= 1;
@@ -137,13 +182,21 @@ __device__ void fixup_low_bits(uint64_t* k, P* p, int n, uint32_t* overflow) {
     }
 }
 
-// Full 64-bit stable sort: high word first with the low-bit fix-up, falling back to all eight
-// digits when the keys share long runs of equal high words. Returns the buffer index (0 / 1).
+// Full 64-bit stable sort: high word first with the low-bit fix-up, falling back to all digits
+// when the keys share long runs of equal high words. `top_bit`: the caller's bound on the highest
+// key bit that differs between any two keys (64 = unknown); digits above it are not visited.
+// Returns the buffer index (0 / 1).
 template <typename P>
-__device__ int block_sort_keys(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, uint32_t* whist) {
+__device__ int block_sort_keys(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, uint32_t* whist, int top_bit = 64) {
     uint32_t* overflow = whist + SORT_WARPS * 256 + 33;
+    const int bit_hi = min(64, (top_bit + 7) & ~7);
+    if (bit_hi <= 32) {  // the keys agree on the whole high word: plain passes over the low digits
+        const int c = block_radix_sort<P>(ka, pa, kb, pb, n, 0, bit_hi, whist);
+        __syncthreads();
+        return c;
+    }
     if (threadIdx.x == 0) *overflow = 0;
-    int cur = block_radix_sort<P>(ka, pa, kb, pb, n, 32, 64, whist);
+    int cur = block_radix_sort<P>(ka, pa, kb, pb, n, 32, bit_hi, whist);
     uint64_t* k = cur ? kb : ka;
     P* p = cur ? pb : pa;
     fixup_low_bits<P>(k, p, n, overflow);
@@ -152,7 +205,7 @@ __device__ int block_sort_keys(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, 
         // (k, p) is the current input; the other pair is scratch.
         uint64_t* ok = cur ? ka : kb;
         P* op = cur ? pa : pb;
-        const int c2 = block_radix_sort<P>(k, p, ok, op, n, 0, 64, whist);
+        const int c2 = block_radix_sort<P>(k, p, ok, op, n, 0, bit_hi, whist);
         cur = c2 ? (cur ^ 1) : cur;
     }
     __syncthreads();

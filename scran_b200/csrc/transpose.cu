@@ -206,11 +206,13 @@ k1_split(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
 
 constexpr int K1S_THREADS = 256;
 constexpr int K1S_GR = 2048;  // genes per scatter CTA: cursor + start + 4 staged values = 40 B per gene
-constexpr int K1S_R = 2;      // entries per thread per column slice held in registers
 
+// Register stage of one column slice: R entries per thread (R * 256 entries in all; longer
+// slices finish through direct loads). D of these rotate, so D column slices are in flight.
+template <int R>
 struct SliceStage {
-    int32_t g[K1S_R];
-    double v[K1S_R];
+    int32_t g[R];
+    double v[R];
     int64_t lo;
     int n;
     __device__ __forceinline__ void load(const int64_t* s_lo, const int* s_n, int j, int ncols,
@@ -222,7 +224,7 @@ struct SliceStage {
             n = s_n[j];
         }
 #pragma unroll
-        for (int r = 0; r < K1S_R; ++r) {
+        for (int r = 0; r < R; ++r) {
             const int k = r * K1S_THREADS + (int)threadIdx.x;
             g[r] = -1;
             if (k < n) {
@@ -237,6 +239,7 @@ struct SliceStage {
 // keeps the write cursor and the last up-to-4 values in shared memory, and writes a 32-byte
 // sector to HBM only when the sector is complete (or at the end of the chunk), so that the
 // gene-major array is written in whole sectors instead of one scattered 8-byte store per entry.
+template <int R, int D>
 __global__ void __launch_bounds__(K1S_THREADS)
 k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
            const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int GR, int nranges,
@@ -290,28 +293,24 @@ k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const
             }
         }
     };
-    auto apply = [&](SliceStage& st) {
+    auto apply = [&](SliceStage<R>& st) {
 #pragma unroll
-        for (int q = 0; q < K1S_R; ++q) {
+        for (int q = 0; q < R; ++q) {
             if (st.g[q] >= 0) put(st.g[q], st.v[q]);
         }
-        for (int k = K1S_R * K1S_THREADS + (int)threadIdx.x; k < st.n; k += K1S_THREADS) put(idx[st.lo + k], x[st.lo + k]);
+        for (int k = R * K1S_THREADS + (int)threadIdx.x; k < st.n; k += K1S_THREADS) put(idx[st.lo + k], x[st.lo + k]);
     };
 
-    SliceStage s0, s1, s2;
-    s0.load(s_lo, s_n, 0, ncols, idx, x);
-    s1.load(s_lo, s_n, 1, ncols, idx, x);
-    s2.load(s_lo, s_n, 2, ncols, idx, x);
-    for (int j = 0; j < ncols; j += 3) {
-        apply(s0);
-        __syncthreads();
-        s0.load(s_lo, s_n, j + 3, ncols, idx, x);
-        if (j + 1 < ncols) apply(s1);
-        __syncthreads();
-        s1.load(s_lo, s_n, j + 4, ncols, idx, x);
-        if (j + 2 < ncols) apply(s2);
-        __syncthreads();
-        s2.load(s_lo, s_n, j + 5, ncols, idx, x);
+    SliceStage<R> ring[D];
+#pragma unroll
+    for (int q = 0; q < D; ++q) ring[q].load(s_lo, s_n, q, ncols, idx, x);
+    for (int j = 0; j < ncols; j += D) {
+#pragma unroll
+        for (int q = 0; q < D; ++q) {
+            if (j + q < ncols) apply(ring[q]);
+            __syncthreads();
+            ring[q].load(s_lo, s_n, j + q + D, ncols, idx, x);
+        }
     }
     // flush the incomplete last sector of every gene
     for (int g = threadIdx.x; g < glen; g += blockDim.x) {
@@ -376,11 +375,20 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
             split = ctx->split.as<uint32_t>();
         }
         const size_t smem = (size_t)K1_MAXCOLS * 12 + (size_t)GR * 40;
-        allow_smem(k1_scatter, smem);
         const int64_t grid = (int64_t)L.nchunks * sranges;
         if (grid > 2147483647ll) throw Error("too many transpose tiles");
-        SB_LAUNCH(ctx, k1_scatter, (unsigned)grid, K1S_THREADS, smem, mat->d_p, mat->d_i, mat->d_x, L.d_perm, L.d_chunk_start,
-                  ngenes, GR, sranges, ncols, split, table, T.row_ptr, T.vals);
+        // entries of one column that fall into one gene range, on average
+        const double slice = (double)mat->nnz / std::max(1, (int)mat->ncol) / sranges;
+#define SB_SCATTER(RR, DD)                                                                                          \
+    do {                                                                                                            \
+        allow_smem(k1_scatter<RR, DD>, smem);                                                                       \
+        SB_LAUNCH(ctx, (k1_scatter<RR, DD>), (unsigned)grid, K1S_THREADS, smem, mat->d_p, mat->d_i, mat->d_x, L.d_perm, \
+                  L.d_chunk_start, ngenes, GR, sranges, ncols, split, table, T.row_ptr, T.vals);                    \
+    } while (0)
+        if (slice <= 200.0) SB_SCATTER(1, 8);
+        else if (slice <= 450.0) SB_SCATTER(2, 4);
+        else SB_SCATTER(4, 2);
+#undef SB_SCATTER
     }
     int h_bad = 0;
     SB_CUDA(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));

@@ -203,6 +203,22 @@ __device__ inline void unit_element(const double* __restrict__ vals, int64_t vba
     key = keep ? key_of(v) : ~0ull;
 }
 
+// Key of element e without its label (enough for the range and the bucket histogram).
+__device__ inline void unit_key(const double* __restrict__ vals, int64_t vbase, uint32_t n, double shift, uint32_t e,
+                                uint64_t& key, bool& keep) {
+    const uint32_t per_role = n + 1;
+    const bool role = e >= per_role;
+    const uint32_t k = role ? e - per_role : e;
+    double v = 0.0;
+    keep = true;
+    if (k < n) {
+        v = vals[vbase + k];
+        keep = v != 0.0;
+    }
+    if (role) v = v - shift;
+    key = keep ? key_of(v) : ~0ull;
+}
+
 __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const SortSmem S = carve_sort_smem(smem_raw, P.cap);
@@ -330,9 +346,8 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         uint32_t dropped = 0;
         for (uint32_t e = tid; e < total; e += blockDim.x) {
             uint64_t key;
-            uint32_t lab;
             bool keep;
-            unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key, lab, keep);
+            unit_key(P.vals, vbase, n, P.shift, e, key, keep);
             if (keep) {
                 kmin = min(kmin, key);
                 kmax = max(kmax, key);
@@ -353,7 +368,8 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         }
         __syncthreads();
         if (warp == 0) {
-            uint64_t a = red[lane], b = red[32 + lane], c = red[64 + lane];
+            uint64_t a = lane < SORT_WARPS ? red[lane] : ~0ull, b = lane < SORT_WARPS ? red[32 + lane] : 0ull,
+                     c = lane < SORT_WARPS ? red[64 + lane] : 0ull;
             for (int o = 16; o > 0; o >>= 1) {
                 a = min(a, __shfl_xor_sync(0xffffffffu, a, o));
                 b = max(b, __shfl_xor_sync(0xffffffffu, b, o));
@@ -387,9 +403,8 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 const unsigned act = __ballot_sync(0xffffffffu, valid);
                 if (valid) {
                     uint64_t key;
-                    uint32_t lab;
                     bool keep;
-                    unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key, lab, keep);
+                    unit_key(P.vals, vbase, n, P.shift, e, key, keep);
                     const unsigned d = keep ? (unsigned)((key - kmin) >> sh) : 255u;
                     const unsigned peers = __match_any_sync(act, d);
                     if (lane == __ffs(peers) - 1) mine[d] += __popc(peers);
@@ -446,10 +461,25 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         // pass 2: runs of consecutive buckets that fit shared memory
         int d0 = 0;
         while (d0 < 256) {
+            __syncthreads();
+            if (tid == 0) {  // extend the run of buckets while it fits
+                const uint32_t st0 = S.boff[d0];
+                int d = d0 + 1;
+                while (d < 256 && S.boff[d + 1] - st0 <= (uint32_t)P.cap) ++d;
+                S.misc[1] = (uint32_t)d;
+            }
+            __syncthreads();
             const uint32_t start = S.boff[d0];
-            int d1 = d0 + 1;
-            while (d1 < 256 && S.boff[d1 + 1] - start <= (uint32_t)P.cap) ++d1;
+            const int d1 = (int)S.misc[1];
             const uint32_t cnt = S.boff[d1] - start;
+            // keys of buckets [d0, d1) lie in [kmin + (d0 << sh), kmin + (d1 << sh)): bits above the
+            // highest differing bit of the two ends are common to all of them (dropped entries, which
+            // only the last bucket holds, are excluded from this shortcut)
+            int top_bit = 64;
+            if (d1 < 256 && sh < 56) {
+                const uint64_t lo_k = kmin + ((uint64_t)d0 << sh), hi_k = kmin + ((uint64_t)d1 << sh) - 1ull;
+                if (hi_k >= lo_k) top_bit = 64 - __clzll((long long)(lo_k ^ hi_k));
+            }
             d0 = d1;
             if (cnt == 0) continue;
             const uint64_t* rk;
@@ -460,11 +490,11 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                     S.pa[j] = gp[start + j];
                 }
                 __syncthreads();
-                const int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)cnt, S.whist);
+                const int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)cnt, S.whist, top_bit);
                 rk = cur ? S.kb : S.ka;
                 rp = cur ? S.pb : S.pa;
             } else {  // a single bucket larger than shared memory (e.g. one heavily tied value)
-                const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist);
+                const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist, top_bit);
                 rk = cur ? gb + start : ga + start;
                 rp = cur ? gq + start : gp + start;
             }
@@ -536,35 +566,60 @@ __device__ inline void slot_barrier(int slot, int slot_tiles) {
     }
 }
 
-// The inner loop shared by both modes: positions [i_lo, i_hi) of one unit's stream, lane = label R.
-template <typename AccT, bool SHIFT>
-__device__ inline void walk_range(const uint16_t* st, int i_lo, int i_hi, int R, bool live, AccT* col, size_t rpad,
-                                  uint32_t c, int lane) {
-    uint32_t cs = c;
+// The inner loop shared by both modes: positions [i_lo, i_hi) of one unit's stream. One warp covers
+// a "wide tile" of W = 32 * J labels: lane l owns labels R0 + 32 j (j < J), i.e. J running counts
+// in registers and J read-modify-writes per entry that share the entry's decode. The table has
+// whole wide tiles of columns, so lanes past the last label update padding that nobody reads.
+template <typename AccT, bool SHIFT, int J>
+__device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_hi, int R0, AccT* col, size_t rpad,
+                                           const uint32_t* c0, int Gt, int lane) {
+    uint32_t c[J], cs[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int R = R0 + 32 * j;
+        c[j] = (c0 != nullptr && R < Gt) ? c0[R] : 0u;
+        cs[j] = c[j];
+    }
+    auto step = [&](uint32_t e) {
+        const int lab = (int)(e & LAB_MASK);
+        AccT* row = col + (size_t)lab * rpad;
+        const int hit = lab - R0;  // == 32 j for the one (lane, j) that owns this label
+        if (!(e & TIE_BIT)) {
+#pragma unroll
+            for (int j = 0; j < J; ++j) cs[j] = c[j];
+        }
+        if (SHIFT) {
+            if (e & ROLE_L) {
+#pragma unroll
+                for (int j = 0; j < J; ++j) row[32 * j] += (AccT)cs[j] + (AccT)c[j];
+            } else {
+#pragma unroll
+                for (int j = 0; j < J; ++j) c[j] += (hit == 32 * j) ? 1u : 0u;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < J; ++j) {
+                row[32 * j] += (AccT)cs[j];
+                c[j] += (hit == 32 * j) ? 1u : 0u;
+            }
+        }
+    };
     for (int i0 = i_lo; i0 < i_hi; i0 += 32) {
         const int mine = i0 + lane;
         const uint32_t ent = mine < i_hi ? (uint32_t)st[mine] : 0u;
-        const int cnt = min(32, i_hi - i0);
-        for (int k = 0; k < cnt; ++k) {
-            const uint32_t e = __shfl_sync(0xffffffffu, ent, k);
-            const int lab = (int)(e & LAB_MASK);
-            if (!(e & TIE_BIT)) cs = c;
-            if (SHIFT) {
-                if (e & ROLE_L) {
-                    if (live) col[(size_t)lab * rpad] += (AccT)cs + (AccT)c;
-                } else {
-                    c += (lab == R) ? 1u : 0u;
-                }
-            } else {
-                if (live) col[(size_t)lab * rpad] += (AccT)cs;
-                c += (lab == R) ? 1u : 0u;
-            }
+        if (i_hi - i0 >= 32) {
+#pragma unroll 8
+            for (int k = 0; k < 32; ++k) step(__shfl_sync(0xffffffffu, ent, k));
+        } else {
+            const int cnt = i_hi - i0;
+            for (int k = 0; k < cnt; ++k) step(__shfl_sync(0xffffffffu, ent, k));
         }
     }
 }
 
-template <typename AccT, bool SHIFT>
+template <typename AccT, bool SHIFT, int J>
 __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
+    constexpr int W = 32 * J;  // labels per warp
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Gmax1 = P.maxG + 1;
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [WALK_WARPS + 1][Gmax1]
@@ -598,7 +653,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
             if (P.pass != 0) continue;
             const int stl = P.slot_tiles;
             const int slot = warp / stl, wtile = warp % stl;
-            const size_t rpad = (size_t)stl * 32;
+            const size_t rpad = (size_t)stl * W;
             if (slot < P.nslots) {
                 uint32_t* sacc = reinterpret_cast<uint32_t*>(acc) + (size_t)slot * Gmax1 * rpad;
                 uint32_t* shist = hist + (size_t)slot * Gmax1;
@@ -616,8 +671,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
                         const uint32_t e = st[k];
                         if (!(SHIFT && (e & ROLE_L))) atomicAdd(&shist[e & LAB_MASK], 1u);
                     }
-                    const int R = wtile * 32 + lane;
-                    walk_range<uint32_t, SHIFT>(st, 0, (int)m, R, R < Gt, sacc + R, rpad, 0u, lane);
+                    const int R0 = wtile * W + lane;
+                    walk_range<uint32_t, SHIFT, J>(st, 0, (int)m, R0, sacc + R0, rpad, nullptr, Gt, lane);
                     slot_barrier(slot, stl);
                     for (int pp = P.pair_ptr[ui.u] + stid; pp < P.pair_ptr[ui.u + 1]; pp += sthreads) {
                         const int l = P.pair_l[pp], r = P.pair_r[pp];
@@ -639,7 +694,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         const UnitInfo ui = unit_info(ut, t0);
         const int G = ui.G, Gt = G + 1;
         const uint16_t* st = P.stream + ui.soff;
-        const int ntiles = (Gt + 31) / 32;
+        const int ntiles = (Gt + W - 1) / W;  // wide tiles
         const int tpb = min(P.tiles_per_batch, ntiles);
         int groups = max(1, min(P.groups, WALK_WARPS / tpb));
         if (tid <= groups) {
@@ -668,20 +723,18 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         __syncthreads();
         for (int tb = 0; tb < ntiles; tb += tpb) {
             const int bt = min(tpb, ntiles - tb);
-            const size_t rpad = (size_t)bt * 32;
+            const size_t rpad = (size_t)bt * W;
             for (int k = tid; k < groups * Gt * (int)rpad; k += blockDim.x) acc[k] = 0;
             __syncthreads();
             if (warp < groups * bt) {
                 const int cg = warp / bt, tile = tb + warp % bt;
-                const int R = tile * 32 + lane;
-                const bool live = R < Gt;
-                walk_range<AccT, SHIFT>(st, bounds[cg], bounds[cg + 1], R, live,
-                                        acc + (size_t)cg * Gt * rpad + (R - tb * 32), rpad,
-                                        live ? hist[cg * Gmax1 + R] : 0u, lane);
+                const int R0 = tile * W + lane;
+                walk_range<AccT, SHIFT, J>(st, bounds[cg], bounds[cg + 1], R0,
+                                           acc + (size_t)cg * Gt * rpad + (R0 - tb * W), rpad, hist + cg * Gmax1, Gt, lane);
             }
             __syncthreads();
             for (int k = tid; k < Gt * (int)rpad; k += blockDim.x) {
-                const int L = k / (int)rpad, R = tb * 32 + k % (int)rpad;
+                const int L = k / (int)rpad, R = tb * W + k % (int)rpad;
                 if (R < Gt) {
                     unsigned long long s = 0;
                     for (int cg = 0; cg < groups; ++cg) s += (unsigned long long)acc[(size_t)cg * Gt * rpad + k];
@@ -865,7 +918,11 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     wp.njobs = njobs;
     wp.maxG = L.maxG;
     const int Gt = L.maxG + 1;
-    const int ntiles = (Gt + 31) / 32;
+    // Labels per warp: 32 * J with J in {1, 2, 4, 8}; beyond 256 labels several warps share a unit.
+    const int narrow_tiles = (Gt + 31) / 32;
+    const int J = narrow_tiles <= 1 ? 1 : narrow_tiles <= 2 ? 2 : narrow_tiles <= 4 ? 4 : 8;
+    const int W = 32 * J;
+    const int ntiles = (Gt + W - 1) / W;  // wide tiles = warps per unit
     const size_t walk_fixed = ((size_t)(WALK_WARPS + 1) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32;
     const int walk_grid_max = ctx->sm_count * 2;
     ctx->plan_tmp.reserve((size_t)walk_grid_max * Gt * Gt * 8 + 64);
@@ -875,11 +932,17 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         const size_t acc_size = pass == 0 ? 4 : 8;
         if (pass == 1 && max_m <= 65536) break;
         wp.pass = pass;
-        const size_t per_tile = (size_t)Gt * 32 * acc_size;
-        if (walk_fixed + per_tile > ctx->smem_optin) {
+        const size_t per_tile = (size_t)Gt * W * acc_size;
+        const size_t narrow = (size_t)Gt * 32 * acc_size;
+        if (walk_fixed + narrow > ctx->smem_optin) {
             throw Error("too many groups inside one block for the shared-memory count table");
         }
         const size_t budget = ctx->smem_optin - walk_fixed;
+        if (per_tile > budget) {
+            // not even one wide tile fits (hundreds of groups with 64-bit counts): this case would need
+            // narrower warps; it is outside every configuration of BASELINE.json
+            throw Error("too many groups inside one block for the shared-memory count table");
+        }
         // batch mode needs every label column of a unit resident: slot = ntiles warps + one uint32 table
         wp.slot_tiles = ntiles;
         wp.nslots = 0;
@@ -905,23 +968,25 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         const size_t smem = walk_fixed + need;
         SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
         const int grid = (int)std::min<int64_t>(ntasks, smem * 2 <= ctx->smem_optin ? walk_grid_max : ctx->sm_count);
+#define SB_WALK(ACC, SH, JJ)                                              \
+    do {                                                                  \
+        allow_smem(k3_walk<ACC, SH, JJ>, smem);                           \
+        SB_LAUNCH(ctx, (k3_walk<ACC, SH, JJ>), grid, WALK_THREADS, smem, wp); \
+    } while (0)
+#define SB_WALK_J(ACC, SH)                  \
+    do {                                    \
+        if (J == 1) SB_WALK(ACC, SH, 1);    \
+        else if (J == 2) SB_WALK(ACC, SH, 2); \
+        else if (J == 4) SB_WALK(ACC, SH, 4); \
+        else SB_WALK(ACC, SH, 8);           \
+    } while (0)
         if (pass == 0) {
-            if (shift) {
-                allow_smem(k3_walk<uint32_t, true>, smem);
-                SB_LAUNCH(ctx, (k3_walk<uint32_t, true>), grid, WALK_THREADS, smem, wp);
-            } else {
-                allow_smem(k3_walk<uint32_t, false>, smem);
-                SB_LAUNCH(ctx, (k3_walk<uint32_t, false>), grid, WALK_THREADS, smem, wp);
-            }
+            if (shift) SB_WALK_J(uint32_t, true); else SB_WALK_J(uint32_t, false);
         } else {
-            if (shift) {
-                allow_smem(k3_walk<unsigned long long, true>, smem);
-                SB_LAUNCH(ctx, (k3_walk<unsigned long long, true>), grid, WALK_THREADS, smem, wp);
-            } else {
-                allow_smem(k3_walk<unsigned long long, false>, smem);
-                SB_LAUNCH(ctx, (k3_walk<unsigned long long, false>), grid, WALK_THREADS, smem, wp);
-            }
+            if (shift) SB_WALK_J(unsigned long long, true); else SB_WALK_J(unsigned long long, false);
         }
+#undef SB_WALK_J
+#undef SB_WALK
     }
 
     if (d_t) {
