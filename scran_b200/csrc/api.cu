@@ -143,11 +143,17 @@ void run_pairs(scranb200_ctx* ctx, const scranb200_mat* mat, PairLayout& L, DevB
     run_transpose(ctx, mat, L, T);
     phase_mark(ctx, PH_TRANSPOSE);
     const size_t cells = (size_t)std::max<int64_t>(1, mat->nrow) * std::max(1, L.C);
-    if (want_stats) {
-        ctx->mean.reserve(cells * 8);
-        ctx->var.reserve(cells * 8);
-        ctx->ndet.reserve(cells * 8);
-        run_stats(ctx, T, L, ctx->mean.as<double>(), ctx->var.as<double>(), ctx->ndet.as<double>());
+    if (want_stats || want_u) {  // the sort takes each segment's value range from this pass
+        double *pm = nullptr, *pv = nullptr, *pd = nullptr;
+        if (want_stats) {
+            ctx->mean.reserve(cells * 8);
+            ctx->var.reserve(cells * 8);
+            ctx->ndet.reserve(cells * 8);
+            pm = ctx->mean.as<double>();
+            pv = ctx->var.as<double>();
+            pd = ctx->ndet.as<double>();
+        }
+        run_stats(ctx, T, L, pm, pv, pd);
         phase_mark(ctx, PH_STATS);
     }
     if (want_u) {
@@ -229,7 +235,7 @@ void scranb200_ctx_destroy(scranb200_ctx* ctx) {
                               &ctx->unit_m, &ctx->sort_keys, &ctx->sort_labs, &ctx->flags, &ctx->mean, &ctx->var,
                               &ctx->ndet, &ctx->u_pairs, &ctx->t_pairs, &ctx->layout_i32, &ctx->layout_f64, &ctx->eff,
                               &ctx->out, &ctx->minrank, &ctx->rank_keys, &ctx->rank_idx, &ctx->plan_tmp, &ctx->io_a,
-                              &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit, &ctx->jobs, &ctx->split};
+                              &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit, &ctx->jobs, &ctx->split, &ctx->vmin, &ctx->vmax};
         for (sb::DevBuf* b : bufs) b->release();
         for (int k = 0; k < 16; ++k) {
             if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);

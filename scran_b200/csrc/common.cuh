@@ -72,7 +72,7 @@ struct scranb200_ctx {
     // scratch, named by role (sizes at config 3 in DESIGN.md)
     sb::DevBuf table, seg_off, row_total, row_ptr, vals, stream_lab, unit_m, sort_keys, sort_labs, flags;
     sb::DevBuf mean, var, ndet, u_pairs, t_pairs, layout_i32, layout_f64;
-    sb::DevBuf eff, out, minrank, rank_keys, rank_idx, plan_tmp, io_a, io_b, io_c, grp_avg, logit, jobs, split;
+    sb::DevBuf eff, out, minrank, rank_keys, rank_idx, plan_tmp, io_a, io_b, io_c, grp_avg, logit, jobs, split, vmin, vmax;
 };
 
 struct scranb200_mat {

@@ -13,15 +13,78 @@
 
 namespace sb {
 
+#ifdef SORT_PROBE
+__device__ long long g_probe[8];
+#endif
+
 constexpr int SORT_THREADS = 1024;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 #ifndef SORT_UNROLL
 #define SORT_UNROLL 1
 #endif
-constexpr int SORT_HIST_WORDS = SORT_WARPS * 256 + 64;  // + aux words
+constexpr int SORT_HIST_WORDS = SORT_WARPS * 256 + 64 + 1024;  // + aux words + scan exchange area
 
 // whist: SORT_HIST_WORDS uint32 of shared memory. Returns 0 if the result is in (ka, pa), 1 if
 // in (kb, pb). Must be called by all SORT_THREADS threads with identical arguments.
+// Turns the per-warp digit histograms whist[warp][digit] into the position where each warp's
+// first entry of each digit goes: exclusive scan in (digit, warp) order, by all 1024 threads
+// (eight entries each). aux: >= 40 words after the histograms; aux[32] is set when a single
+// digit holds all n entries. dbase (nullable, 257 words): where each digit starts (+ total).
+// Ends with a barrier. The kernels that use it run 1024 threads = 32 warps.
+__device__ __forceinline__ void scan_digit_histograms(uint32_t* whist, uint32_t* aux, int n, uint32_t* dbase,
+                                                      uint32_t offset) {
+    static_assert(SORT_THREADS == 1024, "the scan maps 8 (digit, warp) cells to each of 1024 threads");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // thread = (digit d, group of eight warps wg): consecutive lanes read consecutive digits (no bank conflicts)
+    const int d = tid & 255, wg = tid >> 8;
+    uint32_t* xch = aux + 64;  // [4][256] sums of the warp groups, then the digit bases in xch[0][*]
+    uint32_t v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = whist[(wg * 8 + q) * 256 + d];
+    uint32_t run = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const uint32_t t = v[q];
+        v[q] = run;
+        run += t;
+    }
+    xch[wg * 256 + d] = run;
+    __syncthreads();
+    uint32_t tot = 0, inc = 0;
+    if (tid < 256) {  // one thread per digit: total, then an exclusive scan over the 256 digits
+        tot = xch[d] + xch[256 + d] + xch[512 + d] + xch[768 + d];
+        inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += y;
+        }
+        if (lane == 31) aux[warp] = inc;
+        if (tot == (uint32_t)n) aux[32] = 1;
+    }
+    __syncthreads();
+    if (tid < 256) {
+        uint32_t wbase = 0;
+        for (int w = 0; w < warp; ++w) wbase += aux[w];
+        const uint32_t base = offset + wbase + inc - tot;
+        if (dbase) {
+            dbase[d] = base;
+            if (d == 255) dbase[256] = base + tot;
+        }
+        // bases of the four warp groups of this digit
+        const uint32_t s0 = xch[d], s1 = xch[256 + d], s2 = xch[512 + d];
+        xch[d] = base;
+        xch[256 + d] = base + s0;
+        xch[512 + d] = base + s0 + s1;
+        xch[768 + d] = base + s0 + s1 + s2;
+    }
+    __syncthreads();
+    const uint32_t base = xch[wg * 256 + d];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) whist[(wg * 8 + q) * 256 + d] = base + v[q];
+    __syncthreads();
+}
+
 // Lanes with equal 8-bit digits, from eight ballots. `valid` lanes only; others get themselves.
 __device__ __forceinline__ unsigned match_digit(unsigned d, bool valid, int lane) {
 #ifdef SORT_USE_MATCH
@@ -40,7 +103,7 @@ __device__ __forceinline__ unsigned match_digit(unsigned d, bool valid, int lane
 
 template <typename P, bool FROM_PAYLOAD = false>
 __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, int bit_lo, int bit_hi,
-                                uint32_t* whist) {
+                                uint32_t* whist, uint64_t sub = 0, uint32_t* dbase = nullptr) {
     constexpr int U = SORT_UNROLL;  // 32-element groups in flight per warp: their loads and matches overlap
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint32_t* aux = whist + SORT_WARPS * 256;  // [0..7] warp sums, [32] skip flag
@@ -54,6 +117,9 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
         P* sp = cur ? pb : pa;
         uint64_t* dk = cur ? ka : kb;
         P* dp = cur ? pa : pb;
+#ifdef SORT_PROBE
+        long long pt0 = clock64();
+#endif
         for (int i = lane; i < 256; i += 32) mine[i] = 0;
         if (tid == 0) aux[32] = 0;
         __syncwarp();
@@ -65,8 +131,9 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
                 const int i = t + 32 * u + lane;
                 // lanes past the end get a digit nobody else has, so that they match only themselves
                 d[u] = 256u + (unsigned)lane;
-                if (i < s_hi) d[u] = FROM_PAYLOAD ? ((unsigned)(sp[i] >> bit) & 255u) : ((unsigned)(sk[i] >> bit) & 255u);
+                if (i < s_hi) d[u] = FROM_PAYLOAD ? ((unsigned)(sp[i] >> bit) & 255u) : ((unsigned)((sk[i] - sub) >> bit) & 255u);
             }
+#ifdef SORT_HIST_BALLOT
 #pragma unroll
             for (int u = 0; u < U; ++u) peers[u] = match_digit(d[u], d[u] < 256u, lane);
 #pragma unroll
@@ -74,30 +141,27 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
                 if (d[u] < 256u && (peers[u] & lt) == 0u) mine[d[u]] += __popc(peers[u]);
                 __syncwarp();
             }
-        }
-        __syncthreads();
-        if (tid < 256) {
-            uint32_t run = 0;
-            for (int w = 0; w < SORT_WARPS; ++w) {
-                const uint32_t v = whist[w * 256 + tid];
-                whist[w * 256 + tid] = run;
-                run += v;
+#else
+            // counting needs no order: shared-memory atomics on the warp's own counters
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (d[u] < 256u) atomicAdd(&mine[d[u]], 1u);
             }
-            const uint32_t tot = run;
-            uint32_t inc = tot;
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += y;
-            }
-            if (lane == 31) aux[warp] = inc;
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            uint32_t wbase = 0;
-            for (int w = 0; w < warp; ++w) wbase += aux[w];
-            const uint32_t dbase = wbase + inc - tot;
-            for (int w = 0; w < SORT_WARPS; ++w) whist[w * 256 + tid] += dbase;
-            if (tot == (uint32_t)n) aux[32] = 1;
+            (void)peers;
+#endif
         }
+        __syncwarp();
+#ifdef SORT_PROBE
+        long long pt1 = clock64();
         __syncthreads();
+        long long pt1b = clock64();
+#else
+        __syncthreads();
+#endif
+        scan_digit_histograms(whist, aux, dbase ? -1 : n, dbase, 0u);  // with dbase the pass is never skipped
+#ifdef SORT_PROBE
+        long long pt2 = clock64();
+#endif
         const bool skip = aux[32] != 0;
         if (!skip) {
             // ---- stable reorder: rank inside the 32 by lane order, base from the warp's counters ---
@@ -112,7 +176,7 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
                     if (i < s_hi) {
                         k[u] = sk[i];
                         pl[u] = sp[i];
-                        d[u] = FROM_PAYLOAD ? ((unsigned)(pl[u] >> bit) & 255u) : ((unsigned)(k[u] >> bit) & 255u);
+                        d[u] = FROM_PAYLOAD ? ((unsigned)(pl[u] >> bit) & 255u) : ((unsigned)((k[u] - sub) >> bit) & 255u);
                     }
                 }
 #pragma unroll
@@ -137,7 +201,13 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
             }
             cur ^= 1;
         }
+#ifdef SORT_PROBE
+        long long pt3 = clock64();
+#endif
         __syncthreads();
+#ifdef SORT_PROBE
+        if (tid == 0) { g_probe[0] += pt1 - pt0; g_probe[1] += pt1b - pt1; g_probe[2] += pt2 - pt1b; g_probe[3] += pt3 - pt2; g_probe[4] += clock64() - pt3; g_probe[5] += 1; }
+#endif
     }
     return cur;
 }
@@ -147,18 +217,19 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
 // run is fine as long as all its keys are equal (heavy ties); if one holds different keys,
 // *overflow is raised and the caller falls back to sorting all eight digits.
 template <typename P>
-__device__ void fixup_low_bits(uint64_t* k, P* p, int n, uint32_t* overflow) {
+__device__ void fixup_low_bits(uint64_t* k, P* p, int n, uint32_t* overflow, uint64_t sub = 0, int rs = 32) {
+    // a "run" = entries with equal (key - sub) >> rs, i.e. equal in the digits already sorted
     for (int j = threadIdx.x; j < n; j += blockDim.x) {
         const uint64_t kj = k[j];
-        const uint32_t h = (uint32_t)(kj >> 32);
-        if (j > 0 && (uint32_t)(k[j - 1] >> 32) == h) {
+        const uint64_t h = (kj - sub) >> rs;
+        if (j > 0 && ((k[j - 1] - sub) >> rs) == h) {
             // inside a run: entries 32 or more past the run start report unsorted neighbours
-            if (j >= 32 && (uint32_t)(k[j - 32] >> 32) == h && k[j - 1] != kj) *overflow = 1;
+            if (j >= 32 && ((k[j - 32] - sub) >> rs) == h && k[j - 1] != kj) *overflow = 1;
             continue;
         }
         int e = j + 1;
         bool differ = false;
-        while (e < n && e - j <= 32 && (uint32_t)(k[e] >> 32) == h) {
+        while (e < n && e - j <= 32 && ((k[e] - sub) >> rs) == h) {
             differ |= k[e] != kj;
             ++e;
         }
@@ -187,25 +258,28 @@ __device__ void fixup_low_bits(uint64_t* k, P* p, int n, uint32_t* overflow) {
 // key bit that differs between any two keys (64 = unknown); digits above it are not visited.
 // Returns the buffer index (0 / 1).
 template <typename P>
-__device__ int block_sort_keys(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, uint32_t* whist, int top_bit = 64) {
+__device__ int block_sort_keys(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n, uint32_t* whist, int top_bit = 64,
+                               uint64_t sub = 0) {
+    // Orders by (key - sub); `top_bit` bounds the highest bit of (key - sub) that still has to be
+    // sorted (bits above it are equal, or already in order and left alone by the stable passes).
     uint32_t* overflow = whist + SORT_WARPS * 256 + 33;
     const int bit_hi = min(64, (top_bit + 7) & ~7);
-    if (bit_hi <= 32) {  // the keys agree on the whole high word: plain passes over the low digits
-        const int c = block_radix_sort<P>(ka, pa, kb, pb, n, 0, bit_hi, whist);
+    if (bit_hi <= 32) {  // nothing to do above the low word: plain passes over the low digits
+        const int c = block_radix_sort<P>(ka, pa, kb, pb, n, 0, bit_hi, whist, sub);
         __syncthreads();
         return c;
     }
     if (threadIdx.x == 0) *overflow = 0;
-    int cur = block_radix_sort<P>(ka, pa, kb, pb, n, 32, bit_hi, whist);
+    int cur = block_radix_sort<P>(ka, pa, kb, pb, n, 32, bit_hi, whist, sub);
     uint64_t* k = cur ? kb : ka;
     P* p = cur ? pb : pa;
-    fixup_low_bits<P>(k, p, n, overflow);
+    fixup_low_bits<P>(k, p, n, overflow, sub, 32);
     __syncthreads();
     if (*overflow) {
         // (k, p) is the current input; the other pair is scratch.
         uint64_t* ok = cur ? ka : kb;
         P* op = cur ? pa : pb;
-        const int c2 = block_radix_sort<P>(k, p, ok, op, n, 0, bit_hi, whist);
+        const int c2 = block_radix_sort<P>(k, p, ok, op, n, 0, bit_hi, whist, sub);
         cur = c2 ? (cur ^ 1) : cur;
     }
     __syncthreads();

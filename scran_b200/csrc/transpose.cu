@@ -62,7 +62,9 @@ __device__ inline int stage_bounds(const int64_t* __restrict__ p, const int32_t*
     return ncols;
 }
 
-// Pass A: table[chunk][gene] = stored entries of `gene` in the chunk's columns.
+// Pass A: table[chunk][gene] = stored entries of `gene` in the chunk's columns. Counting does not
+// care about order, so the warps of a CTA take columns independently (32 columns in flight per
+// CTA) and bump the shared-memory counters with atomics; no barrier between columns.
 __global__ void __launch_bounds__(K1_THREADS)
 k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const int32_t* __restrict__ perm,
          const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen, uint32_t* __restrict__ table,
@@ -77,51 +79,36 @@ k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
     const int ncols = stage_bounds(p, perm, c_lo, c_hi, s_lo, s_n);
     __syncthreads();
     int flag = 0;
-    const int lane = threadIdx.x & 31;
-
-    auto apply = [&](ColStage<false>& st) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    for (int j = warp; j < ncols; j += nwarps) {
+        const int64_t lo = s_lo[j];
+        const int n = s_n[j];
+        for (int k0 = 0; k0 < n; k0 += 128) {  // four loads in flight per lane
+            int g[4];
 #pragma unroll
-        for (int r = 0; r < K1_R; ++r) {
-            const int g = st.g[r];
-            // strictly increasing rows inside a column: compare with the left neighbour
-            int prev = __shfl_up_sync(0xffffffffu, g, 1);
-            const int k = r * K1_THREADS + (int)threadIdx.x;
-            if (k < st.n) {
-                if (lane == 0) prev = k > 0 ? idx[st.lo + k - 1] : -1;
-                if (g < 0 || g >= ngenes || prev >= g) {
-                    flag = 1;
-                } else {
-                    const unsigned gl = (unsigned)(g - g0);
-                    if (gl < (unsigned)glen) cnt[gl] += 1;
+            for (int q = 0; q < 4; ++q) {
+                const int k = k0 + 32 * q + lane;
+                g[q] = k < n ? idx[lo + k] : -2;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int k = k0 + 32 * q + lane;
+                // strictly increasing rows inside a column: compare with the left neighbour
+                int prev = __shfl_up_sync(0xffffffffu, g[q], 1);
+                const int before = q > 0 ? __shfl_sync(0xffffffffu, g[q - 1], 31) : -1;  // all lanes take part
+                if (lane == 0) prev = q > 0 ? before : ((k0 > 0 && k < n) ? idx[lo + k - 1] : -1);
+                if (k < n) {
+                    if (g[q] < 0 || g[q] >= ngenes || prev >= g[q]) {
+                        flag = 1;
+                    } else {
+                        const unsigned gl = (unsigned)(g[q] - g0);
+                        if (gl < (unsigned)glen) atomicAdd(&cnt[gl], 1u);
+                    }
                 }
             }
         }
-        for (int k = K1_R * K1_THREADS + (int)threadIdx.x; k < st.n; k += K1_THREADS) {  // very long columns
-            const int g = idx[st.lo + k];
-            if (g < 0 || g >= ngenes || idx[st.lo + k - 1] >= g) {
-                flag = 1;
-            } else {
-                const unsigned gl = (unsigned)(g - g0);
-                if (gl < (unsigned)glen) cnt[gl] += 1;
-            }
-        }
-    };
-
-    ColStage<false> s0, s1, s2;
-    s0.load(s_lo, s_n, 0, ncols, idx, nullptr);
-    s1.load(s_lo, s_n, 1, ncols, idx, nullptr);
-    s2.load(s_lo, s_n, 2, ncols, idx, nullptr);
-    for (int j = 0; j < ncols; j += 3) {
-        apply(s0);
-        __syncthreads();
-        s0.load(s_lo, s_n, j + 3, ncols, idx, nullptr);
-        if (j + 1 < ncols) apply(s1);
-        __syncthreads();
-        s1.load(s_lo, s_n, j + 4, ncols, idx, nullptr);
-        if (j + 2 < ncols) apply(s2);
-        __syncthreads();
-        s2.load(s_lo, s_n, j + 5, ncols, idx, nullptr);
     }
+    __syncthreads();
     if (flag) *bad = 1;
     for (int g = threadIdx.x; g < glen; g += blockDim.x) table[(size_t)chunk * ngenes + g0 + g] = cnt[g];
 }

@@ -35,6 +35,15 @@
 
 namespace sb {
 
+#ifdef SB_PHASE_PROBE
+__device__ unsigned long long g_phase[16];
+#define PHASE_T(v) const long long v = clock64()
+#define PHASE_ADD(k, a, b) do { if (threadIdx.x == 0) atomicAdd(&g_phase[k], (unsigned long long)((b) - (a))); } while (0)
+#else
+#define PHASE_T(v)
+#define PHASE_ADD(k, a, b)
+#endif
+
 namespace {
 
 constexpr uint32_t LAB_MASK = 0x3fff;
@@ -121,12 +130,43 @@ __global__ void __launch_bounds__(1024) k3_plan(UnitTables ut, uint32_t small_ma
     }
 }
 
+// Job order for the persistent kernels: the large single-unit jobs first, so that the long ones
+// do not end up in the tail of the launch (longest-processing-time-first, two classes).
+__global__ void __launch_bounds__(1024) k3_order(UnitTables ut, const int32_t* jobs, const int32_t* njobs_ptr,
+                                                  uint32_t big_total, int32_t* order) {
+    __shared__ int part[1024];
+    const int njobs = *njobs_ptr;
+    const int t = threadIdx.x;
+    const int per = (njobs + 1023) / 1024;
+    const int lo = min(njobs, t * per), hi = min(njobs, lo + per);
+    auto is_big = [&](int j) {
+        return jobs[j + 1] - jobs[j] == 1 && unit_info(ut, jobs[j]).total > big_total;
+    };
+    int cnt = 0;
+    for (int j = lo; j < hi; ++j) cnt += is_big(j) ? 1 : 0;
+    part[t] = cnt;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        const int v = t >= d ? part[t - d] : 0;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    const int nbig = part[1023];
+    int big_at = part[t] - cnt;          // big jobs before my range
+    int small_at = nbig + (lo - big_at); // other jobs before my range, placed after all big ones
+    for (int j = lo; j < hi; ++j) {
+        if (is_big(j)) order[big_at++] = j; else order[small_at++] = j;
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // k3_sort
 // ------------------------------------------------------------------------------------------
 struct SortParams {
     UnitTables ut;
     const double* vals;
+    const double *vmin, *vmax;  // per (device combination, gene) value range from K2
     double shift;
     int cap, maxG;
     uint16_t* stream;
@@ -135,6 +175,7 @@ struct SortParams {
     uint32_t *g_pa, *g_pb;
     const int32_t* jobs;
     const int32_t* njobs;
+    const int32_t* order;
     unsigned long long* job_counter;
 };
 
@@ -150,12 +191,14 @@ struct SortSmem {
     int64_t* vbase;      // MAXB
     int64_t* soff;       // MAXB
     uint32_t* boff;      // 258: bucket offsets of the value partition
+    uint32_t* gcur;      // 256: write cursor of every bucket in global scratch
+    uint32_t* tb;        // 260: bucket starts inside the current tile
     uint32_t* misc;      // 16
 };
 
 constexpr size_t sort_fixed_bytes() {
     return (size_t)SORT_HIST_WORDS * 4 + (size_t)(MAXSEG + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 2 +
-           (size_t)MAXB * 8 * 2 + 258 * 4 + 16 * 4 + 64;
+           (size_t)MAXB * 8 * 2 + 258 * 4 + 256 * 4 + 260 * 4 + 16 * 4 + 64;
 }
 
 __device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap) {
@@ -173,7 +216,9 @@ __device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap) {
     s.drop = s.off + (MAXB + 1);
     s.n = s.drop + MAXB;
     s.boff = s.n + MAXB;
-    s.misc = s.boff + 258;
+    s.gcur = s.boff + 258;
+    s.tb = s.gcur + 256;
+    s.misc = s.tb + 260;
     return s;
 }
 
@@ -230,11 +275,12 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         __syncthreads();
         if (tid == 0) S.misc[0] = (uint32_t)atomicAdd(P.job_counter, 1ull);
         __syncthreads();
-        const int job = (int)S.misc[0];
-        if (job >= njobs) break;
+        if ((int)S.misc[0] >= njobs) break;
+        const int job = P.order[S.misc[0]];
         const int64_t t0 = P.jobs[job], t1 = P.jobs[job + 1];
         const int nb = (int)(t1 - t0);
 
+        PHASE_T(p_t0);
         // ---- per-unit tables -------------------------------------------------------------
         if (tid < nb) {
             const UnitInfo ui = unit_info(ut, t0 + tid);
@@ -288,6 +334,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         __syncthreads();
 
         if (total <= (uint32_t)P.cap) {
+            PHASE_T(p_b0);
             // ---- shared-memory path: all units of the job in one sort ---------------------
             for (uint32_t e = tid; e < total; e += blockDim.x) {
                 int lo = 0, hi = nb;
@@ -305,7 +352,9 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 if (!keep) atomicAdd(&S.drop[lo], 1u);
             }
             __syncthreads();
+            PHASE_T(p_b1);
             int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)total, S.whist);
+            PHASE_T(p_b2);
             if (nb > 1) {  // regroup by unit slot (stable): one pass per slot byte
                 uint64_t* k0 = cur ? S.kb : S.ka;
                 uint32_t* p0 = cur ? S.pb : S.pa;
@@ -314,6 +363,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 const int c2 = block_radix_sort<uint32_t, true>(k0, p0, k1, p1, (int)total, 16, nb > 256 ? 32 : 24, S.whist);
                 cur = c2 ? (cur ^ 1) : cur;
             }
+            PHASE_T(p_b3);
             const uint64_t* rk = cur ? S.kb : S.ka;
             const uint32_t* rp = cur ? S.pb : S.pa;
             for (uint32_t j = tid; j < total; j += blockDim.x) {
@@ -327,6 +377,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                     P.stream[S.soff[slot] + pos] = (uint16_t)e;
                 }
             }
+            PHASE_T(p_b4); PHASE_ADD(0, p_t0, p_b0); PHASE_ADD(1, p_b0, p_b1); PHASE_ADD(2, p_b1, p_b2); PHASE_ADD(3, p_b2, p_b3); PHASE_ADD(4, p_b3, p_b4);
             if (tid < nb) P.unit_m[t0 + tid] = (S.off[tid + 1] - S.off[tid]) - S.drop[tid];
             continue;
         }
@@ -341,123 +392,135 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         uint32_t* gp = P.g_pa + soff;
         uint64_t* gb = P.g_kb + soff;
         uint32_t* gq = P.g_pb + soff;
-        // pass 0: key range
+        PHASE_T(p_g0); PHASE_ADD(0, p_t0, p_g0);
+        // pass 0: key range, from the per-segment value ranges K2 left behind (no pass over the values)
+        if (tid == 0) S.misc[3] = 0;  // dropped (stored zero) entries, counted in pass 1
         uint64_t kmin = ~0ull, kmax = 0ull;
-        uint32_t dropped = 0;
-        for (uint32_t e = tid; e < total; e += blockDim.x) {
-            uint64_t key;
-            bool keep;
-            unit_key(P.vals, vbase, n, P.shift, e, key, keep);
-            if (keep) {
-                kmin = min(kmin, key);
-                kmax = max(kmax, key);
-            } else {
-                ++dropped;
-            }
-        }
-        for (int o = 16; o > 0; o >>= 1) {
-            kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
-            kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
-            dropped += __shfl_xor_sync(0xffffffffu, dropped, o);
-        }
-        uint64_t* red = reinterpret_cast<uint64_t*>(S.whist);  // scratch for the block reduction
-        if (lane == 0) {
-            red[warp] = kmin;
-            red[32 + warp] = kmax;
-            red[64 + warp] = dropped;
-        }
-        __syncthreads();
         if (warp == 0) {
-            uint64_t a = lane < SORT_WARPS ? red[lane] : ~0ull, b = lane < SORT_WARPS ? red[32 + lane] : 0ull,
-                     c = lane < SORT_WARPS ? red[64 + lane] : 0ull;
+            auto take = [&](double v) {
+                const uint64_t k = key_of(v);
+                kmin = min(kmin, k);
+                kmax = max(kmax, k);
+            };
+            if (lane == 0) {  // the probe entries
+                take(0.0);
+                if (ut.mult == 2) take(0.0 - P.shift);
+            }
+            const int first = ut.unit_first[(int)(t0 % ut.U)], gene = (int)(t0 / ut.U);
+            for (int k = lane; k < G; k += 32) {
+                const double lo_v = P.vmin[(size_t)(first + k) * ut.ngenes + gene];
+                const double hi_v = P.vmax[(size_t)(first + k) * ut.ngenes + gene];
+                if (lo_v <= hi_v) {  // the segment has non-zero values
+                    take(lo_v);
+                    take(hi_v);
+                    if (ut.mult == 2) {
+                        take(lo_v - P.shift);
+                        take(hi_v - P.shift);
+                    }
+                }
+            }
             for (int o = 16; o > 0; o >>= 1) {
-                a = min(a, __shfl_xor_sync(0xffffffffu, a, o));
-                b = max(b, __shfl_xor_sync(0xffffffffu, b, o));
-                c += __shfl_xor_sync(0xffffffffu, c, o);
+                kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+                kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
             }
             if (lane == 0) {
-                red[96] = a;
-                red[97] = b;
-                red[98] = c;
+                uint64_t* red = reinterpret_cast<uint64_t*>(S.whist);
+                red[0] = kmin;
+                red[1] = kmax;
             }
         }
         __syncthreads();
-        kmin = red[96];
-        kmax = red[97];
-        const uint32_t m = total - (uint32_t)red[98];
+        kmin = reinterpret_cast<uint64_t*>(S.whist)[0];
+        kmax = reinterpret_cast<uint64_t*>(S.whist)[1];
         __syncthreads();
         const uint64_t span = kmax >= kmin ? kmax - kmin : 0ull;
         const int sh = span ? max(0, 64 - __clzll((long long)span) - 8) : 0;
 
-        // pass 1: stable split by bucket = (key - kmin) >> sh (dropped entries: bucket 255)
+        PHASE_T(p_g1); PHASE_ADD(5, p_g0, p_g1);
+        // pass 1: stable split by bucket = (key - kmin) >> sh (dropped entries: bucket 255) into global
+        // scratch. First the unit-wide bucket counts, then tile by tile: a tile is put in bucket
+        // order in shared memory (one stable radix pass) and each bucket's run of the tile is appended
+        // to the bucket's region, so that global memory sees runs of consecutive entries instead
+        // of one scattered 12-byte write per entry.
         {
-            const int per = (int)((((total + SORT_WARPS - 1) / SORT_WARPS) + 31) & ~31u);
-            const uint32_t s_lo = min(total, (uint32_t)warp * per), s_hi = min(total, s_lo + per);
-            uint32_t* mine = S.whist + warp * 256;
-            uint32_t* aux = S.whist + SORT_WARPS * 256;
-            for (int i = lane; i < 256; i += 32) mine[i] = 0;
-            __syncwarp();
-            for (uint32_t t = s_lo; t < s_hi; t += 32) {
-                const uint32_t e = t + lane;
-                const bool valid = e < s_hi;
-                const unsigned act = __ballot_sync(0xffffffffu, valid);
-                if (valid) {
-                    uint64_t key;
-                    bool keep;
-                    unit_key(P.vals, vbase, n, P.shift, e, key, keep);
-                    const unsigned d = keep ? (unsigned)((key - kmin) >> sh) : 255u;
-                    const unsigned peers = __match_any_sync(act, d);
-                    if (lane == __ffs(peers) - 1) mine[d] += __popc(peers);
-                }
-                __syncwarp();
-            }
+            for (int i = tid; i < 256; i += blockDim.x) S.gcur[i] = 0;
             __syncthreads();
-            if (tid < 256) {
-                uint32_t run = 0;
-                for (int w = 0; w < SORT_WARPS; ++w) {
-                    const uint32_t v = S.whist[w * 256 + tid];
-                    S.whist[w * 256 + tid] = run;
-                    run += v;
+            uint32_t ndrop = 0;
+            for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {  // four loads in flight per thread
+                uint64_t key[4];
+                bool keep[4], valid[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t e = t + q * blockDim.x;
+                    valid[q] = e < total;
+                    key[q] = 0;
+                    keep[q] = false;
+                    if (valid[q]) unit_key(P.vals, vbase, n, P.shift, e, key[q], keep[q]);
                 }
-                const uint32_t tot = run;
-                uint32_t inc = tot;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (valid[q]) {
+                        atomicAdd(&S.gcur[keep[q] ? (unsigned)((key[q] - kmin) >> sh) : 255u], 1u);
+                        ndrop += keep[q] ? 0u : 1u;
+                    }
+                }
+            }
+            for (int o = 16; o > 0; o >>= 1) ndrop += __shfl_xor_sync(0xffffffffu, ndrop, o);
+            if (lane == 0 && ndrop) atomicAdd(&S.misc[3], ndrop);
+            __syncthreads();
+            if (warp == 0) {  // exclusive scan of the 256 bucket counts: eight per lane
+                uint32_t c[8], run = 0;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    c[q] = S.gcur[lane * 8 + q];
+                    run += c[q];
+                }
+                uint32_t inc = run;
+#pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
                     if (lane >= o) inc += y;
                 }
-                if (lane == 31) aux[warp] = inc;
-                asm volatile("bar.sync 1, 256;" ::: "memory");
-                uint32_t wbase = 0;
-                for (int w = 0; w < warp; ++w) wbase += aux[w];
-                const uint32_t dbase = wbase + inc - tot;
-                for (int w = 0; w < SORT_WARPS; ++w) S.whist[w * 256 + tid] += dbase;
-                S.boff[tid] = dbase;
-                if (tid == 255) S.boff[256] = dbase + tot;
+                uint32_t at = inc - run;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    S.boff[lane * 8 + q] = at;
+                    S.gcur[lane * 8 + q] = at;
+                    at += c[q];
+                }
+                if (lane == 31) S.boff[256] = at;
             }
             __syncthreads();
-            for (uint32_t t = s_lo; t < s_hi; t += 32) {
-                const uint32_t e = t + lane;
-                const bool valid = e < s_hi;
-                const unsigned act = __ballot_sync(0xffffffffu, valid);
-                if (valid) {
+            for (uint32_t tile = 0; tile < total; tile += (uint32_t)P.cap) {
+                const uint32_t tn = min((uint32_t)P.cap, total - tile);
+                for (uint32_t j = tid; j < tn; j += blockDim.x) {
                     uint64_t key;
                     uint32_t lab;
                     bool keep;
-                    unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key, lab, keep);
+                    unit_element(P.vals, vbase, n, S.seg, G, P.shift, tile + j, key, lab, keep);
                     const unsigned d = keep ? (unsigned)((key - kmin) >> sh) : 255u;
-                    const unsigned peers = __match_any_sync(act, d);
-                    const uint32_t base = mine[d];
-                    const uint32_t at = base + __popc(peers & ((1u << lane) - 1u));
-                    ga[at] = key;
-                    gp[at] = lab;
-                    __syncwarp(act);
-                    if (lane == __ffs(peers) - 1) mine[d] = base + __popc(peers);
-                    __syncwarp(act);
+                    S.ka[j] = key;
+                    S.pa[j] = lab | (d << 16);
                 }
+                __syncthreads();
+                const int cur = block_radix_sort<uint32_t, true>(S.ka, S.pa, S.kb, S.pb, (int)tn, 16, 24, S.whist, 0ull, S.tb);
+                const uint64_t* rk = cur ? S.kb : S.ka;
+                const uint32_t* rp = cur ? S.pb : S.pa;
+                for (uint32_t j = tid; j < tn; j += blockDim.x) {
+                    const uint32_t pay = rp[j];
+                    const unsigned d = pay >> 16;
+                    const uint32_t dst = S.gcur[d] + (j - S.tb[d]);
+                    ga[dst] = rk[j];
+                    gp[dst] = pay & 0xffffu;
+                }
+                __syncthreads();
+                if (tid < 256) S.gcur[tid] += S.tb[tid + 1] - S.tb[tid];
+                __syncthreads();
             }
-            __syncthreads();
         }
+        const uint32_t m = total - S.misc[3];
 
+        PHASE_T(p_g2); PHASE_ADD(6, p_g1, p_g2);
         // pass 2: runs of consecutive buckets that fit shared memory
         int d0 = 0;
         while (d0 < 256) {
@@ -475,7 +538,11 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
             // keys of buckets [d0, d1) lie in [kmin + (d0 << sh), kmin + (d1 << sh)): bits above the
             // highest differing bit of the two ends are common to all of them (dropped entries, which
             // only the last bucket holds, are excluded from this shortcut)
+            // keys of buckets [d0, d1) lie in [kmin + (d0 << sh), kmin + (d1 << sh)): bits above the
+            // highest differing bit of the two ends are common to all of them (dropped entries, which
+            // only the last bucket holds, are excluded from this shortcut)
             int top_bit = 64;
+            const uint64_t sub = 0;
             if (d1 < 256 && sh < 56) {
                 const uint64_t lo_k = kmin + ((uint64_t)d0 << sh), hi_k = kmin + ((uint64_t)d1 << sh) - 1ull;
                 if (hi_k >= lo_k) top_bit = 64 - __clzll((long long)(lo_k ^ hi_k));
@@ -485,19 +552,23 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
             const uint64_t* rk;
             const uint32_t* rp;
             if (cnt <= (uint32_t)P.cap) {
+                PHASE_T(p_l0);
                 for (uint32_t j = tid; j < cnt; j += blockDim.x) {
                     S.ka[j] = ga[start + j];
                     S.pa[j] = gp[start + j];
                 }
                 __syncthreads();
-                const int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)cnt, S.whist, top_bit);
+                PHASE_T(p_l1); PHASE_ADD(7, p_l0, p_l1);
+                const int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)cnt, S.whist, top_bit, sub);
+                PHASE_T(p_l2); PHASE_ADD(8, p_l1, p_l2);
                 rk = cur ? S.kb : S.ka;
                 rp = cur ? S.pb : S.pa;
             } else {  // a single bucket larger than shared memory (e.g. one heavily tied value)
-                const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist, top_bit);
+                const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist, top_bit, sub);
                 rk = cur ? gb + start : ga + start;
                 rp = cur ? gq + start : gp + start;
             }
+            PHASE_T(p_e0);
             for (uint32_t j = tid; j < cnt; j += blockDim.x) {
                 const uint32_t pos = start + j;
                 if (pos < m) {
@@ -507,6 +578,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 }
             }
             __syncthreads();
+            PHASE_T(p_e1); PHASE_ADD(9, p_e0, p_e1);
         }
         if (tid == 0) P.unit_m[t0] = m;
     }
@@ -531,6 +603,7 @@ struct WalkParams {
     unsigned long long* job_counter;
     const int32_t* jobs;
     const int32_t* njobs;
+    const int32_t* order;
     int maxG;
     int tiles_per_batch;  // solo mode: R tiles whose accumulators fit in shared memory at once
     int groups;           // solo mode: position chunks walked concurrently (private tables)
@@ -639,8 +712,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         __syncthreads();
         if (tid == 0) misc[0] = (uint32_t)atomicAdd(P.job_counter, 1ull);
         __syncthreads();
-        const int job = (int)misc[0];
-        if (job >= njobs) break;
+        if ((int)misc[0] >= njobs) break;
+        const int job = P.order[misc[0]];
         const int64_t t0 = P.jobs[job], t1 = P.jobs[job + 1];
         const int nb = (int)(t1 - t0);
 
@@ -825,6 +898,19 @@ __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
 
 }  // namespace
 
+#ifdef SB_PHASE_PROBE
+void phase_probe_dump() {
+    unsigned long long h[16];
+    cudaMemcpyFromSymbol(h, g_phase, sizeof(h));
+    const char* names[10] = {"tables", "batch build", "batch sort", "batch slot pass", "batch emit", "big pass0 minmax", "big partition", "big group load", "big group sort", "big group emit"};
+    unsigned long long tot = 0;
+    for (int k = 0; k < 10; ++k) tot += h[k];
+    for (int k = 0; k < 10; ++k) fprintf(stderr, "  %-18s %6.2f%%\n", names[k], 100.0 * h[k] / (double)tot);
+    unsigned long long z[16] = {0};
+    cudaMemcpyToSymbol(g_phase, z, sizeof(z));
+}
+#endif
+
 void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, double lfc, double* d_u, double* d_t) {
     if (L.U == 0 || T.ngenes == 0 || L.npairs == 0) return;
     if (L.maxG > MAX_LABELS) throw Error("more than 16383 groups compared inside one block are not supported");
@@ -851,11 +937,12 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
 
     ctx->stream_lab.reserve((size_t)stream_len * 2 + 64);
     ctx->unit_m.reserve((size_t)ntasks * 4 + 64);
-    ctx->jobs.reserve((size_t)(ntasks + 2) * 4 + 64);
+    ctx->jobs.reserve((size_t)(ntasks + 2) * 8 + 64);
     ctx->flags.reserve(64);
     unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->flags.as<char>() + 16);
     int32_t* njobs = reinterpret_cast<int32_t*>(ctx->flags.as<char>() + 32);
     int32_t* jobs = ctx->jobs.as<int32_t>();
+    int32_t* order = jobs + (ntasks + 2);
 
     // ---- plan ----
     const size_t fixed = sort_fixed_bytes();
@@ -865,6 +952,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     const uint32_t small_max = (uint32_t)cap / 2, window = (uint32_t)cap - small_max;
     const int maxb = std::max(1, std::min(MAXB, MAXSEG / (L.maxG + 1)));
     SB_LAUNCH(ctx, k3_plan, 1, 1024, 0, ut, small_max, window, maxb, jobs, njobs);
+    SB_LAUNCH(ctx, k3_order, 1, 1024, 0, ut, jobs, njobs, 16384u, order);
 
     // ---- sort ----
     int64_t max_cells = 0;
@@ -878,6 +966,9 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     SortParams sp;
     sp.ut = ut;
     sp.vals = T.vals;
+    sp.vmin = T.vmin;
+    sp.vmax = T.vmax;
+    if (!T.vmin || !T.vmax) throw Error("internal: the value ranges of the segments are missing");
     sp.shift = lfc;
     sp.cap = cap;
     sp.maxG = L.maxG;
@@ -895,12 +986,17 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     }
     sp.jobs = jobs;
     sp.njobs = njobs;
+    sp.order = order;
     sp.job_counter = counter;
     allow_smem(k3_sort, sort_smem);
     SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
     const int sort_grid = (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count);
     SB_LAUNCH(ctx, k3_sort, sort_grid, SORT_THREADS, sort_smem, sp);
     phase_mark(ctx, PH_SORT);
+#ifdef SB_PHASE_PROBE
+    cudaStreamSynchronize(ctx->stream);
+    phase_probe_dump();
+#endif
 
     // ---- walk ----
     WalkParams wp;
@@ -916,6 +1012,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     wp.job_counter = counter;
     wp.jobs = jobs;
     wp.njobs = njobs;
+    wp.order = order;
     wp.maxG = L.maxG;
     const int Gt = L.maxG + 1;
     // Labels per warp: 32 * J with J in {1, 2, 4, 8}; beyond 256 labels several warps share a unit.
