@@ -191,6 +191,7 @@ struct SortSmem {
     int64_t* vbase;      // MAXB
     int64_t* soff;       // MAXB
     uint32_t* boff;      // 258: bucket offsets of the value partition
+    unsigned long long *bmin, *bmax;  // 256 each: smallest / largest key of every bucket
     uint32_t* gcur;      // 256: write cursor of every bucket in global scratch
     uint32_t* tb;        // 260: bucket starts inside the current tile
     uint32_t* misc;      // 16
@@ -198,7 +199,7 @@ struct SortSmem {
 
 constexpr size_t sort_fixed_bytes() {
     return (size_t)SORT_HIST_WORDS * 4 + (size_t)(MAXSEG + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 2 +
-           (size_t)MAXB * 8 * 2 + 258 * 4 + 256 * 4 + 260 * 4 + 16 * 4 + 64;
+           (size_t)MAXB * 8 * 2 + 512 * 8 + 258 * 4 + 256 * 4 + 260 * 4 + 16 * 4 + 64;
 }
 
 __device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap) {
@@ -207,7 +208,9 @@ __device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap) {
     s.kb = s.ka + cap;
     s.vbase = reinterpret_cast<int64_t*>(s.kb + cap);
     s.soff = s.vbase + MAXB;
-    s.pa = reinterpret_cast<uint32_t*>(s.soff + MAXB);
+    s.bmin = reinterpret_cast<unsigned long long*>(s.soff + MAXB);
+    s.bmax = s.bmin + 256;
+    s.pa = reinterpret_cast<uint32_t*>(s.bmax + 256);
     s.pb = s.pa + cap;
     s.whist = s.pb + cap;
     s.seg = s.whist + SORT_HIST_WORDS;
@@ -262,6 +265,16 @@ __device__ inline void unit_key(const double* __restrict__ vals, int64_t vbase, 
     }
     if (role) v = v - shift;
     key = keep ? key_of(v) : ~0ull;
+}
+
+// Value bucket of a key: 256 buckets of equal width in VALUE space over [fmin, fmax] (equal width
+// in key space would follow the exponent and put a whole binade range into one bucket). Monotone
+// in the value, so the buckets are ordered; values outside the range (the probes) clamp to the
+// ends; dropped entries go to the last bucket, where their all-ones key sorts them last.
+__device__ __forceinline__ unsigned value_bucket(uint64_t key, bool keep, double fmin, double scale) {
+    if (!keep) return 255u;
+    const double x = (value_of(key) - fmin) * scale;
+    return x >= 255.0 ? 255u : (x > 0.0 ? (unsigned)x : 0u);
 }
 
 __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
@@ -393,57 +406,53 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         uint64_t* gb = P.g_kb + soff;
         uint32_t* gq = P.g_pb + soff;
         PHASE_T(p_g0); PHASE_ADD(0, p_t0, p_g0);
-        // pass 0: key range, from the per-segment value ranges K2 left behind (no pass over the values)
+        // pass 0: value range of the unit (both roles, probes excluded), from the per-segment ranges
+        // that K2 left behind: no pass over the values
         if (tid == 0) S.misc[3] = 0;  // dropped (stored zero) entries, counted in pass 1
-        uint64_t kmin = ~0ull, kmax = 0ull;
+        double fmin = __longlong_as_double(0x7ff0000000000000ll), fmax = -fmin;
         if (warp == 0) {
-            auto take = [&](double v) {
-                const uint64_t k = key_of(v);
-                kmin = min(kmin, k);
-                kmax = max(kmax, k);
-            };
-            if (lane == 0) {  // the probe entries
-                take(0.0);
-                if (ut.mult == 2) take(0.0 - P.shift);
-            }
             const int first = ut.unit_first[(int)(t0 % ut.U)], gene = (int)(t0 / ut.U);
             for (int k = lane; k < G; k += 32) {
                 const double lo_v = P.vmin[(size_t)(first + k) * ut.ngenes + gene];
                 const double hi_v = P.vmax[(size_t)(first + k) * ut.ngenes + gene];
                 if (lo_v <= hi_v) {  // the segment has non-zero values
-                    take(lo_v);
-                    take(hi_v);
+                    fmin = fmin < lo_v ? fmin : lo_v;
+                    fmax = fmax > hi_v ? fmax : hi_v;
                     if (ut.mult == 2) {
-                        take(lo_v - P.shift);
-                        take(hi_v - P.shift);
+                        fmin = fmin < lo_v - P.shift ? fmin : lo_v - P.shift;
+                        fmax = fmax > hi_v - P.shift ? fmax : hi_v - P.shift;
                     }
                 }
             }
             for (int o = 16; o > 0; o >>= 1) {
-                kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
-                kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+                const double a = __shfl_xor_sync(0xffffffffu, fmin, o), b = __shfl_xor_sync(0xffffffffu, fmax, o);
+                fmin = fmin < a ? fmin : a;
+                fmax = fmax > b ? fmax : b;
             }
             if (lane == 0) {
-                uint64_t* red = reinterpret_cast<uint64_t*>(S.whist);
-                red[0] = kmin;
-                red[1] = kmax;
+                double* red = reinterpret_cast<double*>(S.whist);
+                red[0] = fmin;
+                red[1] = fmax;
             }
         }
         __syncthreads();
-        kmin = reinterpret_cast<uint64_t*>(S.whist)[0];
-        kmax = reinterpret_cast<uint64_t*>(S.whist)[1];
+        fmin = reinterpret_cast<double*>(S.whist)[0];
+        fmax = reinterpret_cast<double*>(S.whist)[1];
         __syncthreads();
-        const uint64_t span = kmax >= kmin ? kmax - kmin : 0ull;
-        const int sh = span ? max(0, 64 - __clzll((long long)span) - 8) : 0;
+        const double scale = fmax > fmin ? 256.0 / (fmax - fmin) : 0.0;
 
         PHASE_T(p_g1); PHASE_ADD(5, p_g0, p_g1);
-        // pass 1: stable split by bucket = (key - kmin) >> sh (dropped entries: bucket 255) into global
+        // pass 1: stable split by value bucket (dropped entries: bucket 255) into global
         // scratch. First the unit-wide bucket counts, then tile by tile: a tile is put in bucket
         // order in shared memory (one stable radix pass) and each bucket's run of the tile is appended
         // to the bucket's region, so that global memory sees runs of consecutive entries instead
         // of one scattered 12-byte write per entry.
         {
-            for (int i = tid; i < 256; i += blockDim.x) S.gcur[i] = 0;
+            for (int i = tid; i < 256; i += blockDim.x) {
+                S.gcur[i] = 0;
+                S.bmin[i] = ~0ull;
+                S.bmax[i] = 0ull;
+            }
             __syncthreads();
             uint32_t ndrop = 0;
             for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {  // four loads in flight per thread
@@ -460,7 +469,12 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     if (valid[q]) {
-                        atomicAdd(&S.gcur[keep[q] ? (unsigned)((key[q] - kmin) >> sh) : 255u], 1u);
+                        const unsigned d = value_bucket(key[q], keep[q], fmin, scale);
+                        atomicAdd(&S.gcur[d], 1u);
+                        if (keep[q]) {  // key range of every bucket, for the digit skipping of the sorts
+                            atomicMin(&S.bmin[d], (unsigned long long)key[q]);
+                            atomicMax(&S.bmax[d], (unsigned long long)key[q]);
+                        }
                         ndrop += keep[q] ? 0u : 1u;
                     }
                 }
@@ -491,6 +505,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 if (lane == 31) S.boff[256] = at;
             }
             __syncthreads();
+            PHASE_T(p_h1); PHASE_ADD(10, p_g1, p_h1);
             for (uint32_t tile = 0; tile < total; tile += (uint32_t)P.cap) {
                 const uint32_t tn = min((uint32_t)P.cap, total - tile);
                 for (uint32_t j = tid; j < tn; j += blockDim.x) {
@@ -498,7 +513,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                     uint32_t lab;
                     bool keep;
                     unit_element(P.vals, vbase, n, S.seg, G, P.shift, tile + j, key, lab, keep);
-                    const unsigned d = keep ? (unsigned)((key - kmin) >> sh) : 255u;
+                    const unsigned d = value_bucket(key, keep, fmin, scale);
                     S.ka[j] = key;
                     S.pa[j] = lab | (d << 16);
                 }
@@ -520,33 +535,34 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         }
         const uint32_t m = total - S.misc[3];
 
-        PHASE_T(p_g2); PHASE_ADD(6, p_g1, p_g2);
+        PHASE_T(p_g2); PHASE_ADD(6, p_g1, p_g2);  // includes slot 10
         // pass 2: runs of consecutive buckets that fit shared memory
         int d0 = 0;
         while (d0 < 256) {
             __syncthreads();
-            if (tid == 0) {  // extend the run of buckets while it fits
+            if (tid == 0) {  // extend the run of buckets while it fits; note the key range of the run
                 const uint32_t st0 = S.boff[d0];
                 int d = d0 + 1;
                 while (d < 256 && S.boff[d + 1] - st0 <= (uint32_t)P.cap) ++d;
                 S.misc[1] = (uint32_t)d;
+                unsigned long long lo_k = ~0ull, hi_k = 0ull;
+                for (int q = d0; q < d; ++q) {
+                    lo_k = S.bmin[q] < lo_k ? S.bmin[q] : lo_k;
+                    hi_k = S.bmax[q] > hi_k ? S.bmax[q] : hi_k;
+                }
+                // bits above the highest bit in which the smallest and the largest key of the run
+                // differ are common to all its keys (the dropped entries of the last bucket, whose
+                // key is not a value, switch this shortcut off)
+                int tb = 64;
+                if (hi_k >= lo_k && !(d == 256 && S.misc[3] > 0)) tb = lo_k == hi_k ? 0 : 64 - __clzll((long long)(lo_k ^ hi_k));
+                S.misc[4] = (uint32_t)tb;
             }
             __syncthreads();
             const uint32_t start = S.boff[d0];
             const int d1 = (int)S.misc[1];
             const uint32_t cnt = S.boff[d1] - start;
-            // keys of buckets [d0, d1) lie in [kmin + (d0 << sh), kmin + (d1 << sh)): bits above the
-            // highest differing bit of the two ends are common to all of them (dropped entries, which
-            // only the last bucket holds, are excluded from this shortcut)
-            // keys of buckets [d0, d1) lie in [kmin + (d0 << sh), kmin + (d1 << sh)): bits above the
-            // highest differing bit of the two ends are common to all of them (dropped entries, which
-            // only the last bucket holds, are excluded from this shortcut)
-            int top_bit = 64;
+            const int top_bit = (int)S.misc[4];
             const uint64_t sub = 0;
-            if (d1 < 256 && sh < 56) {
-                const uint64_t lo_k = kmin + ((uint64_t)d0 << sh), hi_k = kmin + ((uint64_t)d1 << sh) - 1ull;
-                if (hi_k >= lo_k) top_bit = 64 - __clzll((long long)(lo_k ^ hi_k));
-            }
             d0 = d1;
             if (cnt == 0) continue;
             const uint64_t* rk;
@@ -902,10 +918,10 @@ __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
 void phase_probe_dump() {
     unsigned long long h[16];
     cudaMemcpyFromSymbol(h, g_phase, sizeof(h));
-    const char* names[10] = {"tables", "batch build", "batch sort", "batch slot pass", "batch emit", "big pass0 minmax", "big partition", "big group load", "big group sort", "big group emit"};
+    const char* names[11] = {"tables", "batch build", "batch sort", "batch slot pass", "batch emit", "big pass0 minmax", "big partition (all)", "big group load", "big group sort", "big group emit", "  of which unit hist"};
     unsigned long long tot = 0;
     for (int k = 0; k < 10; ++k) tot += h[k];
-    for (int k = 0; k < 10; ++k) fprintf(stderr, "  %-18s %6.2f%%\n", names[k], 100.0 * h[k] / (double)tot);
+    for (int k = 0; k < 11; ++k) fprintf(stderr, "  %-22s %6.2f%%  %8.3f Mcycles per CTA\n", names[k], 100.0 * h[k] / (double)tot, h[k] / 148.0 / 1e6);
     unsigned long long z[16] = {0};
     cudaMemcpyToSymbol(g_phase, z, sizeof(z));
 }
