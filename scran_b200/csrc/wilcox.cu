@@ -856,57 +856,109 @@ struct TieParams {
     const int32_t *pair_ptr, *pair_l, *pair_r, *pair_out;
     int64_t npairs;
     double* t_out;
+    int maxG;
 };
+
+constexpr int TIE_EVENTS = 8192;  // compacted stream entries kept in shared memory per unit
+
+// Adds one stream entry to the running tie count of pair (l, r) of a unit with probe label G.
+template <bool SHIFT>
+__device__ __forceinline__ void tie_entry(uint32_t e, int l, int r, int G, long long zL, long long zR, long long& t) {
+    const int lab = (int)(e & LAB_MASK);
+    const bool roleL = SHIFT ? (e & ROLE_L) != 0 : false;
+    if (lab == G) {  // probe: the zeros of the pair's groups sit here
+        if (SHIFT) {
+            t += roleL ? zL : zR;
+        } else {
+            t += zL + zR;
+        }
+    } else if (SHIFT) {
+        if (roleL && lab == l) t += 1;
+        if (!roleL && lab == r) t += 1;
+    } else {
+        if (lab == l || lab == r) t += 1;
+    }
+}
 
 template <bool SHIFT>
 __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
+    extern __shared__ __align__(16) unsigned char tie_smem[];
+    uint32_t* hist = reinterpret_cast<uint32_t*>(tie_smem);                 // [maxG + 2] stored non-zero entries per label
+    uint32_t* wsum = hist + (P.maxG + 2);                                   // [8] + [1] count + [1] overflow
+    uint16_t* events = reinterpret_cast<uint16_t*>(wsum + 12);              // [TIE_EVENTS]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t task = blockIdx.x;
     const UnitInfo ui = unit_info(P.ut, task);
     const int G = ui.G;
     const uint16_t* st = P.stream + ui.soff;
     const uint32_t m = P.unit_m[task];
-    for (int pp = P.pair_ptr[ui.u] + threadIdx.x; pp < P.pair_ptr[ui.u + 1]; pp += blockDim.x) {
+    for (int k = tid; k <= G; k += blockDim.x) hist[k] = 0;
+    if (tid == 0) {
+        wsum[8] = 0;
+        wsum[9] = 0;
+    }
+    __syncthreads();
+    // Only entries of runs with two or more entries, and the probes (where the zeros sit), can add
+    // to any pair's tie term. They are compacted, in order, into shared memory; bit 15 of a
+    // compacted entry marks the first entry of its run.
+    for (uint32_t base = 0; base < m; base += blockDim.x) {
+        const uint32_t i = base + tid;
+        uint32_t e = 0;
+        bool rel = false;
+        if (i < m) {
+            e = st[i];
+            const bool tied_next = i + 1 < m && (st[i + 1] & TIE_BIT);
+            rel = (e & TIE_BIT) || tied_next || (int)(e & LAB_MASK) == G;
+            if (!(SHIFT && (e & ROLE_L))) atomicAdd(&hist[e & LAB_MASK], 1u);
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, rel);
+        if (lane == 0) wsum[warp] = __popc(bal);
+        __syncthreads();
+        uint32_t off = wsum[8];
+        for (int w = 0; w < warp; ++w) off += wsum[w];
+        if (rel) {
+            const uint32_t at = off + __popc(bal & ((1u << lane) - 1u));
+            // a compacted entry starts a run unless it ties with its predecessor, which is then relevant too
+            if (at < TIE_EVENTS) events[at] = (uint16_t)((e & 0x7fffu) | ((e & TIE_BIT) ? 0u : 0x8000u));
+        }
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t tot = wsum[8];
+            for (int w = 0; w < 8; ++w) tot += wsum[w];
+            wsum[8] = tot;
+            if (tot > TIE_EVENTS) wsum[9] = 1;
+        }
+        __syncthreads();
+    }
+    const uint32_t nev = wsum[8];
+    const bool overflow = wsum[9] != 0;
+    for (int pp = P.pair_ptr[ui.u] + tid; pp < P.pair_ptr[ui.u + 1]; pp += blockDim.x) {
         const int l = P.pair_l[pp], r = P.pair_r[pp];
         const long long nL = P.ut.ncells_dev[ui.first + l], nR = P.ut.ncells_dev[ui.first + r];
-        long long cl = 0, cr = 0;  // stored non-zero entries of the two labels
-        for (uint32_t i = 0; i < m; ++i) {
-            const uint32_t e = st[i];
-            if (SHIFT && (e & ROLE_L)) continue;
-            const int lab = (int)(e & LAB_MASK);
-            cl += lab == l;
-            cr += lab == r;
-        }
-        const long long zL = nL - cl, zR = nR - cr;
+        const long long zL = nL - (long long)hist[l], zR = nR - (long long)hist[r];
         double tie = 0.0;
         long long t = 0;
-        bool open = false;
-        for (uint32_t i = 0; i <= m; ++i) {
-            const bool boundary = i == m || !(st[i] & TIE_BIT);
-            if (boundary && open) {
-                if (t > 0) {
-                    const double nt = (double)t;
-                    tie += nt * (nt * nt - 1.0);
-                }
-                t = 0;
+        auto close_run = [&]() {
+            if (t > 0) {
+                const double nt = (double)t;
+                tie += nt * (nt * nt - 1.0);
             }
-            if (i == m) break;
-            open = true;
-            const uint32_t e = st[i];
-            const int lab = (int)(e & LAB_MASK);
-            const bool roleL = SHIFT ? (e & ROLE_L) != 0 : false;
-            if (lab == G) {  // probe: the zeros of the pair's groups sit here
-                if (SHIFT) {
-                    t += roleL ? zL : zR;
-                } else {
-                    t += zL + zR;
-                }
-            } else if (SHIFT) {
-                if (roleL && lab == l) t += 1;
-                if (!roleL && lab == r) t += 1;
-            } else {
-                if (lab == l || lab == r) t += 1;
+            t = 0;
+        };
+        if (!overflow) {
+            for (uint32_t k = 0; k < nev; ++k) {
+                const uint32_t e = events[k];
+                if (e & 0x8000u) close_run();
+                tie_entry<SHIFT>(e, l, r, G, zL, zR, t);
+            }
+        } else {  // too many tied entries for shared memory: walk the stream itself
+            for (uint32_t i = 0; i < m; ++i) {
+                const uint32_t e = st[i];
+                if (!(e & TIE_BIT)) close_run();
+                tie_entry<SHIFT>(e, l, r, G, zL, zR, t);
             }
         }
+        close_run();
         if (nL == 0 || nR == 0) tie = 0.0;
         P.t_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] = tie;
     }
@@ -1113,10 +1165,14 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         tp.pair_out = L.d_pair_out;
         tp.npairs = L.npairs;
         tp.t_out = d_t;
+        tp.maxG = L.maxG;
+        const size_t tie_smem = (size_t)(L.maxG + 2 + 12) * 4 + (size_t)TIE_EVENTS * 2;
         if (shift) {
-            SB_LAUNCH(ctx, k3_ties<true>, (unsigned)ntasks, 256, 0, tp);
+            allow_smem(k3_ties<true>, tie_smem);
+            SB_LAUNCH(ctx, k3_ties<true>, (unsigned)ntasks, 256, tie_smem, tp);
         } else {
-            SB_LAUNCH(ctx, k3_ties<false>, (unsigned)ntasks, 256, 0, tp);
+            allow_smem(k3_ties<false>, tie_smem);
+            SB_LAUNCH(ctx, k3_ties<false>, (unsigned)ntasks, 256, tie_smem, tp);
         }
     }
     phase_mark(ctx, PH_COUNT);
