@@ -669,10 +669,18 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         c[j] = (c0 != nullptr && R < Gt) ? c0[R] : 0u;
         cs[j] = c[j];
     }
+    // byte addressing of the table: one multiply-add per entry
+    unsigned char* colb = reinterpret_cast<unsigned char*>(col);
+    const uint32_t rowbytes = (uint32_t)(rpad * sizeof(AccT));
+    int Rj[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) Rj[j] = R0 + 32 * j;
+    auto bump = [&](uint32_t& cnt, int lab, int R) {  // cnt += (lab == R): compare + predicated add
+        asm("{\n\t.reg .pred p;\n\tsetp.eq.s32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(cnt) : "r"(lab), "r"(R));
+    };
     auto step = [&](uint32_t e) {
         const int lab = (int)(e & LAB_MASK);
-        AccT* row = col + (size_t)lab * rpad;
-        const int hit = lab - R0;  // == 32 j for the one (lane, j) that owns this label
+        AccT* row = reinterpret_cast<AccT*>(colb + (uint32_t)lab * rowbytes);
         if (!(e & TIE_BIT)) {
 #pragma unroll
             for (int j = 0; j < J; ++j) cs[j] = c[j];
@@ -683,22 +691,41 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
                 for (int j = 0; j < J; ++j) row[32 * j] += (AccT)cs[j] + (AccT)c[j];
             } else {
 #pragma unroll
-                for (int j = 0; j < J; ++j) c[j] += (hit == 32 * j) ? 1u : 0u;
+                for (int j = 0; j < J; ++j) bump(c[j], lab, Rj[j]);
             }
         } else {
 #pragma unroll
             for (int j = 0; j < J; ++j) {
                 row[32 * j] += (AccT)cs[j];
-                c[j] += (hit == 32 * j) ? 1u : 0u;
+                bump(c[j], lab, Rj[j]);
             }
+        }
+    };
+    // No entry of the 32 ties with its predecessor (the usual case for continuous data): every entry
+    // starts its own run, so the count at the run start is the running count itself.
+    auto step_untied = [&](uint32_t e) {
+        const int lab = (int)(e & LAB_MASK);
+        AccT* row = reinterpret_cast<AccT*>(colb + (uint32_t)lab * rowbytes);
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            row[32 * j] += (AccT)c[j];
+            bump(c[j], lab, Rj[j]);
         }
     };
     for (int i0 = i_lo; i0 < i_hi; i0 += 32) {
         const int mine = i0 + lane;
         const uint32_t ent = mine < i_hi ? (uint32_t)st[mine] : 0u;
         if (i_hi - i0 >= 32) {
+            if (!SHIFT && !__any_sync(0xffffffffu, (ent & TIE_BIT) != 0u)) {
 #pragma unroll 8
-            for (int k = 0; k < 32; ++k) step(__shfl_sync(0xffffffffu, ent, k));
+                for (int k = 0; k < 31; ++k) step_untied(__shfl_sync(0xffffffffu, ent, k));
+#pragma unroll
+                for (int j = 0; j < J; ++j) cs[j] = c[j];  // the last entry's run starts here; the next block may tie with it
+                step_untied(__shfl_sync(0xffffffffu, ent, 31));
+            } else {
+#pragma unroll 8
+                for (int k = 0; k < 32; ++k) step(__shfl_sync(0xffffffffu, ent, k));
+            }
         } else {
             const int cnt = i_hi - i0;
             for (int k = 0; k < cnt; ++k) step(__shfl_sync(0xffffffffu, ent, k));
