@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(1024) k3_plan(UnitTables ut, uint32_t small_ma
 // Job order for the persistent kernels: the large single-unit jobs first, so that the long ones
 // do not end up in the tail of the launch (longest-processing-time-first, two classes).
 __global__ void __launch_bounds__(1024) k3_order(UnitTables ut, const int32_t* jobs, const int32_t* njobs_ptr,
-                                                  uint32_t big_total, int32_t* order) {
+                                                  uint32_t big_total, int32_t* order, int32_t* nbig_out) {
     __shared__ int part[1024];
     const int njobs = *njobs_ptr;
     const int t = threadIdx.x;
@@ -153,6 +153,7 @@ __global__ void __launch_bounds__(1024) k3_order(UnitTables ut, const int32_t* j
         __syncthreads();
     }
     const int nbig = part[1023];
+    if (t == 0) *nbig_out = nbig;
     int big_at = part[t] - cnt;          // big jobs before my range
     int small_at = nbig + (lo - big_at); // other jobs before my range, placed after all big ones
     for (int j = lo; j < hi; ++j) {
@@ -626,6 +627,9 @@ struct WalkParams {
     int nslots;           // batch mode: warp groups (0 = batch mode unavailable: tables too large)
     int slot_tiles;       // batch mode: warps per slot = ceil((maxG + 1) / 32)
     int pass;             // 0: everything with m <= 65536 (uint32 tables); 1: only m > 65536 (uint64 tables)
+    const int32_t* nbig;  // number of large single-unit jobs at the head of `order`
+    uint32_t big_total;   // a unit with more entries than this is "large": walked by a whole CTA
+    int by_task;          // large-unit kernel: walk EVERY unit (used when the per-warp mode has no room for its tables)
 };
 
 // 2U from the count table (AccT entries, row stride `rpad`) for one pair.
@@ -733,6 +737,65 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
     }
 }
 
+// Units of up to `big_total` entries: every warp group ("slot": the warps that cover one unit's
+// labels, one warp for up to 256 labels) takes units on its own from a global counter, with its own
+// count table. There is no CTA-wide barrier: the slots of a CTA never wait for each other.
+template <bool SHIFT, int J>
+__global__ void __launch_bounds__(WALK_THREADS) k3_walk_small(WalkParams P) {
+    constexpr int W = 32 * J;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int Gmax1 = P.maxG + 1;
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                  // [WALK_WARPS][Gmax1]
+    unsigned long long* slot_task = reinterpret_cast<unsigned long long*>(hist + (size_t)WALK_WARPS * Gmax1 + (Gmax1 & 1));
+    uint32_t* acc = reinterpret_cast<uint32_t*>(slot_task + WALK_WARPS);    // [nslots][Gmax1][stl * W]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const UnitTables& ut = P.ut;
+    const int stl = P.slot_tiles;
+    const int slot = warp / stl, wtile = warp % stl;
+    if (slot >= P.nslots) return;
+    const size_t rpad = (size_t)stl * W;
+    uint32_t* sacc = acc + (size_t)slot * Gmax1 * rpad;
+    uint32_t* shist = hist + (size_t)slot * Gmax1;
+    const int sthreads = stl * 32, stid = wtile * 32 + lane;
+    const int64_t ntasks = (int64_t)ut.ngenes * ut.U;
+    while (true) {
+        unsigned long long t = 0;
+        if (stl == 1) {
+            if (lane == 0) t = atomicAdd(P.job_counter, 1ull);
+            t = __shfl_sync(0xffffffffu, t, 0);
+        } else {
+            if (stid == 0) slot_task[slot] = atomicAdd(P.job_counter, 1ull);
+            slot_barrier(slot, stl);
+            t = slot_task[slot];
+            slot_barrier(slot, stl);
+        }
+        if ((int64_t)t >= ntasks) break;
+        const int64_t task = (int64_t)t;
+        const UnitInfo ui = unit_info(ut, task);
+        if (ui.total > P.big_total) continue;  // walked by k3_walk
+        const int Gt = ui.G + 1;
+        const uint32_t m = P.unit_m[task];
+        const uint16_t* st = P.stream + ui.soff;
+        for (int k = stid; k < Gt * (int)rpad; k += sthreads) sacc[k] = 0;
+        for (int k = stid; k < Gt; k += sthreads) shist[k] = 0;
+        slot_barrier(slot, stl);
+        for (uint32_t k = stid; k < m; k += sthreads) {
+            const uint32_t e = st[k];
+            if (!(SHIFT && (e & ROLE_L))) atomicAdd(&shist[e & LAB_MASK], 1u);
+        }
+        const int R0 = wtile * W + lane;
+        walk_range<uint32_t, SHIFT, J>(st, 0, (int)m, R0, sacc + R0, rpad, nullptr, Gt, lane);
+        slot_barrier(slot, stl);
+        for (int pp = P.pair_ptr[ui.u] + stid; pp < P.pair_ptr[ui.u + 1]; pp += sthreads) {
+            const int l = P.pair_l[pp], r = P.pair_r[pp];
+            const long long nL = ut.ncells_dev[ui.first + l], nR = ut.ncells_dev[ui.first + r];
+            const long long zL = nL - (long long)shist[l], zR = nR - (long long)shist[r];
+            P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] = pair_u<uint32_t, SHIFT>(sacc, rpad, l, r, ui.G, nL, nR, zL, zR);
+        }
+        slot_barrier(slot, stl);
+    }
+}
+
 template <typename AccT, bool SHIFT, int J>
 __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
     constexpr int W = 32 * J;  // labels per warp
@@ -748,62 +811,22 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long* bfull = P.bfull + (size_t)blockIdx.x * Gmax1 * Gmax1;
-    const int njobs = *P.njobs;
+    const int nbig = *P.nbig;
     const UnitTables& ut = P.ut;
 
     while (true) {
         __syncthreads();
         if (tid == 0) misc[0] = (uint32_t)atomicAdd(P.job_counter, 1ull);
         __syncthreads();
-        if ((int)misc[0] >= njobs) break;
-        const int job = P.order[misc[0]];
-        const int64_t t0 = P.jobs[job], t1 = P.jobs[job + 1];
-        const int nb = (int)(t1 - t0);
-
-        // ---- batch mode: several small units at a time, one warp group ("slot") each --------
-        bool batch = false;
-        if (sizeof(AccT) == 4 && P.nslots > 0) {
-            batch = nb > 1 || P.unit_m[t0] <= WALK_BATCH_MAX_M;
+        int64_t t0;
+        if (P.by_task) {
+            if ((int64_t)misc[0] >= (int64_t)ut.ngenes * ut.U) break;
+            t0 = (int64_t)misc[0];
+        } else {
+            if ((int)misc[0] >= nbig) break;
+            t0 = P.jobs[P.order[misc[0]]];
         }
-        if (batch) {
-            if (P.pass != 0) continue;
-            const int stl = P.slot_tiles;
-            const int slot = warp / stl, wtile = warp % stl;
-            const size_t rpad = (size_t)stl * W;
-            if (slot < P.nslots) {
-                uint32_t* sacc = reinterpret_cast<uint32_t*>(acc) + (size_t)slot * Gmax1 * rpad;
-                uint32_t* shist = hist + (size_t)slot * Gmax1;
-                const int sthreads = stl * 32, stid = wtile * 32 + lane;
-                for (int i = slot; i < nb; i += P.nslots) {
-                    const int64_t task = t0 + i;
-                    const UnitInfo ui = unit_info(ut, task);
-                    const int Gt = ui.G + 1;
-                    const uint32_t m = P.unit_m[task];
-                    const uint16_t* st = P.stream + ui.soff;
-                    for (int k = stid; k < Gt * (int)rpad; k += sthreads) sacc[k] = 0;
-                    for (int k = stid; k < Gt; k += sthreads) shist[k] = 0;
-                    slot_barrier(slot, stl);
-                    for (uint32_t k = stid; k < m; k += sthreads) {
-                        const uint32_t e = st[k];
-                        if (!(SHIFT && (e & ROLE_L))) atomicAdd(&shist[e & LAB_MASK], 1u);
-                    }
-                    const int R0 = wtile * W + lane;
-                    walk_range<uint32_t, SHIFT, J>(st, 0, (int)m, R0, sacc + R0, rpad, nullptr, Gt, lane);
-                    slot_barrier(slot, stl);
-                    for (int pp = P.pair_ptr[ui.u] + stid; pp < P.pair_ptr[ui.u + 1]; pp += sthreads) {
-                        const int l = P.pair_l[pp], r = P.pair_r[pp];
-                        const long long nL = ut.ncells_dev[ui.first + l], nR = ut.ncells_dev[ui.first + r];
-                        const long long zL = nL - (long long)shist[l], zR = nR - (long long)shist[r];
-                        P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] =
-                            pair_u<uint32_t, SHIFT>(sacc, rpad, l, r, ui.G, nL, nR, zL, zR);
-                    }
-                    slot_barrier(slot, stl);
-                }
-            }
-            continue;
-        }
-
-        // ---- solo mode: one unit, all warps, position chunks with private tables ------------
+        // ---- one large unit, all warps: position chunks with private tables -----------------
         const uint32_t m = P.unit_m[t0];
         const bool wide = m > 65536u;
         if ((P.pass == 0) == wide) continue;
@@ -1036,6 +1059,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     ctx->flags.reserve(64);
     unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->flags.as<char>() + 16);
     int32_t* njobs = reinterpret_cast<int32_t*>(ctx->flags.as<char>() + 32);
+    int32_t* nbig = reinterpret_cast<int32_t*>(ctx->flags.as<char>() + 40);
     int32_t* jobs = ctx->jobs.as<int32_t>();
     int32_t* order = jobs + (ntasks + 2);
 
@@ -1047,7 +1071,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     const uint32_t small_max = (uint32_t)cap / 2, window = (uint32_t)cap - small_max;
     const int maxb = std::max(1, std::min(MAXB, MAXSEG / (L.maxG + 1)));
     SB_LAUNCH(ctx, k3_plan, 1, 1024, 0, ut, small_max, window, maxb, jobs, njobs);
-    SB_LAUNCH(ctx, k3_order, 1, 1024, 0, ut, jobs, njobs, 16384u, order);
+    SB_LAUNCH(ctx, k3_order, 1, 1024, 0, ut, jobs, njobs, 16384u, order, nbig);
 
     // ---- sort ----
     int64_t max_cells = 0;
@@ -1120,28 +1144,58 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     ctx->plan_tmp.reserve((size_t)walk_grid_max * Gt * Gt * 8 + 64);
     wp.bfull = ctx->plan_tmp.as<unsigned long long>();
 
-    for (int pass = 0; pass < 2; ++pass) {
+    const uint32_t big_total = 16384u;  // same threshold as k3_order's "large job"
+    wp.big_total = big_total;
+    wp.nbig = nbig;
+    wp.by_task = 0;
+
+    // ---- units of up to big_total entries: one warp group per unit, no CTA-wide barriers ----
+    {
+        const size_t table = (size_t)Gt * W * 4 * ntiles;  // one unit's uint32 count table
+        const size_t fixed_small = ((size_t)WALK_WARPS * Gt + (Gt & 1)) * 4 + WALK_WARPS * 8 + 32;
+        int ns = 0;
+        if (fixed_small + table <= ctx->smem_optin && ntiles <= WALK_WARPS) {
+            ns = (int)std::min<size_t>((ctx->smem_optin - fixed_small) / table, (size_t)(WALK_WARPS / ntiles));
+            if (ntiles > 1) ns = std::min(ns, 15);  // named barriers 1..15
+        }
+        wp.slot_tiles = ntiles;
+        wp.nslots = ns;
+        if (ns > 0) {
+            const size_t smem = fixed_small + table * ns;
+            SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
+            const int grid = ctx->sm_count * (smem * 2 <= ctx->smem_optin ? 2 : 1);
+#define SB_WALKS(SH, JJ)                                                        \
+    do {                                                                        \
+        allow_smem(k3_walk_small<SH, JJ>, smem);                                \
+        SB_LAUNCH(ctx, (k3_walk_small<SH, JJ>), grid, WALK_THREADS, smem, wp);  \
+    } while (0)
+#define SB_WALKS_J(SH)                  \
+    do {                                \
+        if (J == 1) SB_WALKS(SH, 1);    \
+        else if (J == 2) SB_WALKS(SH, 2); \
+        else if (J == 4) SB_WALKS(SH, 4); \
+        else SB_WALKS(SH, 8);           \
+    } while (0)
+            if (shift) SB_WALKS_J(true); else SB_WALKS_J(false);
+#undef SB_WALKS_J
+#undef SB_WALKS
+        } else {
+            wp.by_task = 1;  // no room for per-warp tables: the large-unit kernel walks every unit
+        }
+    }
+
+    // ---- large units: one CTA per unit (32-bit counts up to 65536 entries, 64-bit beyond) ----
+    const bool any_large = wp.by_task || max_m > (int64_t)big_total;
+    for (int pass = 0; pass < 2 && any_large; ++pass) {
         const size_t acc_size = pass == 0 ? 4 : 8;
         if (pass == 1 && max_m <= 65536) break;
         wp.pass = pass;
         const size_t per_tile = (size_t)Gt * W * acc_size;
-        const size_t narrow = (size_t)Gt * 32 * acc_size;
-        if (walk_fixed + narrow > ctx->smem_optin) {
-            throw Error("too many groups inside one block for the shared-memory count table");
-        }
         const size_t budget = ctx->smem_optin - walk_fixed;
-        if (per_tile > budget) {
-            // not even one wide tile fits (hundreds of groups with 64-bit counts): this case would need
-            // narrower warps; it is outside every configuration of BASELINE.json
+        if (walk_fixed > ctx->smem_optin || per_tile > budget) {
+            // not even one wide tile fits (hundreds of groups with 64-bit counts); outside every
+            // configuration of BASELINE.json
             throw Error("too many groups inside one block for the shared-memory count table");
-        }
-        // batch mode needs every label column of a unit resident: slot = ntiles warps + one uint32 table
-        wp.slot_tiles = ntiles;
-        wp.nslots = 0;
-        if (pass == 0 && per_tile * ntiles <= budget && ntiles <= WALK_WARPS) {
-            int ns = (int)std::min<size_t>(budget / (per_tile * ntiles), (size_t)(WALK_WARPS / ntiles));
-            if (ntiles > 1) ns = std::min(ns, 15);  // named barriers 1..15
-            wp.nslots = std::max(0, ns);
         }
         int tpb, groups;
         if (per_tile * ntiles <= budget) {
@@ -1155,9 +1209,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         }
         wp.tiles_per_batch = tpb;
         wp.groups = groups;
-        size_t need = per_tile * tpb * groups;
-        if (wp.nslots > 0) need = std::max(need, per_tile * ntiles * wp.nslots);
-        const size_t smem = walk_fixed + need;
+        const size_t smem = walk_fixed + per_tile * tpb * groups;
         SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
         const int grid = (int)std::min<int64_t>(ntasks, smem * 2 <= ctx->smem_optin ? walk_grid_max : ctx->sm_count);
 #define SB_WALK(ACC, SH, JJ)                                              \
