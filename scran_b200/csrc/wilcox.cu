@@ -130,34 +130,63 @@ __global__ void __launch_bounds__(1024) k3_plan(UnitTables ut, uint32_t small_ma
     }
 }
 
-// Job order for the persistent kernels: the large single-unit jobs first, so that the long ones
-// do not end up in the tail of the launch (longest-processing-time-first, two classes).
+// Job order for the persistent kernels: the large single-unit jobs first and among them the larger
+// size classes first (powers of two above `big_total`), so that the long jobs do not end up in the
+// tail of the launch (longest-processing-time-first over ORDER_CLASSES + 1 classes).
+constexpr int ORDER_CLASSES = 6;
 __global__ void __launch_bounds__(1024) k3_order(UnitTables ut, const int32_t* jobs, const int32_t* njobs_ptr,
                                                   uint32_t big_total, int32_t* order, int32_t* nbig_out) {
-    __shared__ int part[1024];
+    __shared__ int part[ORDER_CLASSES + 1][1024];
+    __shared__ int class_base[ORDER_CLASSES + 2];
     const int njobs = *njobs_ptr;
     const int t = threadIdx.x;
     const int per = (njobs + 1023) / 1024;
     const int lo = min(njobs, t * per), hi = min(njobs, lo + per);
-    auto is_big = [&](int j) {
-        return jobs[j + 1] - jobs[j] == 1 && unit_info(ut, jobs[j]).total > big_total;
+    auto class_of = [&](int j) {  // 0 = largest ... ORDER_CLASSES - 1 = just above big_total; ORDER_CLASSES = the rest
+        if (jobs[j + 1] - jobs[j] != 1) return ORDER_CLASSES;
+        const uint32_t total = unit_info(ut, jobs[j]).total;
+        if (total <= big_total) return ORDER_CLASSES;
+        const int above = 31 - __clz(total / big_total);  // floor(log2(total / big_total)) >= 0
+        return ORDER_CLASSES - 1 - min(above, ORDER_CLASSES - 1);
     };
-    int cnt = 0;
-    for (int j = lo; j < hi; ++j) cnt += is_big(j) ? 1 : 0;
-    part[t] = cnt;
+    int cnt[ORDER_CLASSES + 1];
+#pragma unroll
+    for (int c = 0; c <= ORDER_CLASSES; ++c) cnt[c] = 0;
+    for (int j = lo; j < hi; ++j) {
+        const int cl = class_of(j);
+#pragma unroll
+        for (int c = 0; c <= ORDER_CLASSES; ++c) cnt[c] += cl == c ? 1 : 0;
+    }
+#pragma unroll
+    for (int c = 0; c <= ORDER_CLASSES; ++c) part[c][t] = cnt[c];
     __syncthreads();
     for (int d = 1; d < 1024; d <<= 1) {
-        const int v = t >= d ? part[t - d] : 0;
+        int v[ORDER_CLASSES + 1];
+#pragma unroll
+        for (int c = 0; c <= ORDER_CLASSES; ++c) v[c] = t >= d ? part[c][t - d] : 0;
         __syncthreads();
-        part[t] += v;
+#pragma unroll
+        for (int c = 0; c <= ORDER_CLASSES; ++c) part[c][t] += v[c];
         __syncthreads();
     }
-    const int nbig = part[1023];
-    if (t == 0) *nbig_out = nbig;
-    int big_at = part[t] - cnt;          // big jobs before my range
-    int small_at = nbig + (lo - big_at); // other jobs before my range, placed after all big ones
+    if (t == 0) {
+        int run = 0;
+        for (int c = 0; c <= ORDER_CLASSES; ++c) {
+            class_base[c] = run;
+            run += part[c][1023];
+        }
+        class_base[ORDER_CLASSES + 1] = run;
+        *nbig_out = class_base[ORDER_CLASSES];
+    }
+    __syncthreads();
+    int at[ORDER_CLASSES + 1];
+#pragma unroll
+    for (int c = 0; c <= ORDER_CLASSES; ++c) at[c] = class_base[c] + part[c][t] - cnt[c];
     for (int j = lo; j < hi; ++j) {
-        if (is_big(j)) order[big_at++] = j; else order[small_at++] = j;
+        const int cl = class_of(j);
+#pragma unroll
+        for (int c = 0; c <= ORDER_CLASSES; ++c)
+            if (cl == c) order[at[c]++] = j;
     }
 }
 
@@ -607,7 +636,6 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 constexpr int WALK_THREADS = 1024;
 constexpr int WALK_WARPS = WALK_THREADS / 32;
 constexpr int WALK_MAX_GROUPS = 16;
-constexpr uint32_t WALK_BATCH_MAX_M = 3072;  // units up to this many stream entries are walked by one warp group
 
 struct WalkParams {
     UnitTables ut;
@@ -659,20 +687,19 @@ __device__ inline void slot_barrier(int slot, int slot_tiles) {
     }
 }
 
-// The inner loop shared by both modes: positions [i_lo, i_hi) of one unit's stream. One warp covers
+// The inner loop shared by both kernels: positions [i_lo, i_hi) of one unit's stream. One warp covers
 // a "wide tile" of W = 32 * J labels: lane l owns labels R0 + 32 j (j < J), i.e. J running counts
 // in registers and J read-modify-writes per entry that share the entry's decode. The table has
 // whole wide tiles of columns, so lanes past the last label update padding that nobody reads.
+// The running counts start at zero: what the entries BEFORE i_lo contribute is linear in the
+// counts this function returns (cnt_r: entries per label in the counted role; cnt_l: entries per
+// label in the adding role, which is the same thing unless SHIFT) and is added by the caller.
 template <typename AccT, bool SHIFT, int J>
 __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_hi, int R0, AccT* col, size_t rpad,
-                                           const uint32_t* c0, int Gt, int lane) {
-    uint32_t c[J], cs[J];
+                                           uint32_t* cnt_r, uint32_t* cnt_l, int Gt, int lane) {
+    uint32_t c[J], cs[J], cl[J];
 #pragma unroll
-    for (int j = 0; j < J; ++j) {
-        const int R = R0 + 32 * j;
-        c[j] = (c0 != nullptr && R < Gt) ? c0[R] : 0u;
-        cs[j] = c[j];
-    }
+    for (int j = 0; j < J; ++j) c[j] = cs[j] = cl[j] = 0u;
     // byte addressing of the table: one multiply-add per entry
     unsigned char* colb = reinterpret_cast<unsigned char*>(col);
     const uint32_t rowbytes = (uint32_t)(rpad * sizeof(AccT));
@@ -692,7 +719,10 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         if (SHIFT) {
             if (e & ROLE_L) {
 #pragma unroll
-                for (int j = 0; j < J; ++j) row[32 * j] += (AccT)cs[j] + (AccT)c[j];
+                for (int j = 0; j < J; ++j) {
+                    row[32 * j] += (AccT)cs[j] + (AccT)c[j];
+                    bump(cl[j], lab, Rj[j]);
+                }
             } else {
 #pragma unroll
                 for (int j = 0; j < J; ++j) bump(c[j], lab, Rj[j]);
@@ -706,14 +736,53 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         }
     };
     // No entry of the 32 ties with its predecessor (the usual case for continuous data): every entry
-    // starts its own run, so the count at the run start is the running count itself.
-    auto step_untied = [&](uint32_t e) {
-        const int lab = (int)(e & LAB_MASK);
-        AccT* row = reinterpret_cast<AccT*>(colb + (uint32_t)lab * rowbytes);
+    // starts its own run, so the count at the run start is the running count itself, and without a
+    // role bit the entry IS its label.
+    auto step_untied = [&](uint32_t lab) {
+        AccT* row = reinterpret_cast<AccT*>(colb + lab * rowbytes);
 #pragma unroll
         for (int j = 0; j < J; ++j) {
             row[32 * j] += (AccT)c[j];
-            bump(c[j], lab, Rj[j]);
+            bump(c[j], (int)lab, Rj[j]);
+        }
+    };
+    // Four untied entries at once. A table update is load / add / store through shared memory and
+    // the next one may hit the same row, so taken one by one they form a chain of shared-memory
+    // round trips. The labels are warp-uniform: when the four differ (checked without divergence)
+    // their rows are disjoint, all loads go out first and the adds and stores follow.
+    // (QN entries at once: four while the loaded table words fit in 16 registers, else two, else one.)
+    constexpr int QN = J * sizeof(AccT) <= 16 ? 4 : J * sizeof(AccT) <= 32 ? 2 : 1;
+    auto multi_untied = [&](const uint32_t (&l)[QN]) {
+        bool dup = false;
+#pragma unroll
+        for (int a = 0; a < QN; ++a)
+#pragma unroll
+            for (int b = a + 1; b < QN; ++b) dup |= l[a] == l[b];
+        if (QN == 1 || dup) {
+#pragma unroll
+            for (int a = 0; a < QN; ++a) step_untied(l[a]);
+            return;
+        }
+        if constexpr (QN > 1) {
+        AccT* r[QN];
+        AccT v[QN][J];
+#pragma unroll
+        for (int a = 0; a < QN; ++a) r[a] = reinterpret_cast<AccT*>(colb + l[a] * rowbytes);
+#pragma unroll
+        for (int a = 0; a < QN; ++a)
+#pragma unroll
+            for (int j = 0; j < J; ++j) v[a][j] = r[a][32 * j];
+#pragma unroll
+        for (int a = 0; a < QN; ++a)
+#pragma unroll
+            for (int j = 0; j < J; ++j) {
+                v[a][j] += (AccT)c[j];
+                bump(c[j], (int)l[a], Rj[j]);
+            }
+#pragma unroll
+        for (int a = 0; a < QN; ++a)
+#pragma unroll
+            for (int j = 0; j < J; ++j) r[a][32 * j] = v[a][j];
         }
     };
     for (int i0 = i_lo; i0 < i_hi; i0 += 32) {
@@ -721,8 +790,16 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         const uint32_t ent = mine < i_hi ? (uint32_t)st[mine] : 0u;
         if (i_hi - i0 >= 32) {
             if (!SHIFT && !__any_sync(0xffffffffu, (ent & TIE_BIT) != 0u)) {
-#pragma unroll 8
-                for (int k = 0; k < 31; ++k) step_untied(__shfl_sync(0xffffffffu, ent, k));
+#pragma unroll
+                for (int k = 0; k < 28; k += QN) {
+                    uint32_t l[QN];
+#pragma unroll
+                    for (int a = 0; a < QN; ++a) l[a] = __shfl_sync(0xffffffffu, ent, k + a);
+                    multi_untied(l);
+                }
+                step_untied(__shfl_sync(0xffffffffu, ent, 28));
+                step_untied(__shfl_sync(0xffffffffu, ent, 29));
+                step_untied(__shfl_sync(0xffffffffu, ent, 30));
 #pragma unroll
                 for (int j = 0; j < J; ++j) cs[j] = c[j];  // the last entry's run starts here; the next block may tie with it
                 step_untied(__shfl_sync(0xffffffffu, ent, 31));
@@ -733,6 +810,13 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         } else {
             const int cnt = i_hi - i0;
             for (int k = 0; k < cnt; ++k) step(__shfl_sync(0xffffffffu, ent, k));
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        if (Rj[j] < Gt) {
+            cnt_r[Rj[j]] = c[j];
+            if (SHIFT && cnt_l != nullptr) cnt_l[Rj[j]] = cl[j];
         }
     }
 }
@@ -777,14 +861,10 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk_small(WalkParams P) {
         const uint32_t m = P.unit_m[task];
         const uint16_t* st = P.stream + ui.soff;
         for (int k = stid; k < Gt * (int)rpad; k += sthreads) sacc[k] = 0;
-        for (int k = stid; k < Gt; k += sthreads) shist[k] = 0;
         slot_barrier(slot, stl);
-        for (uint32_t k = stid; k < m; k += sthreads) {
-            const uint32_t e = st[k];
-            if (!(SHIFT && (e & ROLE_L))) atomicAdd(&shist[e & LAB_MASK], 1u);
-        }
         const int R0 = wtile * W + lane;
-        walk_range<uint32_t, SHIFT, J>(st, 0, (int)m, R0, sacc + R0, rpad, nullptr, Gt, lane);
+        // shist: stored entries per label (counted role), left behind by the walk
+        walk_range<uint32_t, SHIFT, J>(st, 0, (int)m, R0, sacc + R0, rpad, shist, nullptr, Gt, lane);
         slot_barrier(slot, stl);
         for (int pp = P.pair_ptr[ui.u] + stid; pp < P.pair_ptr[ui.u + 1]; pp += sthreads) {
             const int l = P.pair_l[pp], r = P.pair_r[pp];
@@ -801,7 +881,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
     constexpr int W = 32 * J;  // labels per warp
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Gmax1 = P.maxG + 1;
-    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [WALK_WARPS + 1][Gmax1]
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [2 * WALK_MAX_GROUPS (+1)][Gmax1]: per-chunk counts, counted / adding role
     uint32_t* nnzv = hist + (size_t)(WALK_WARPS + 1) * Gmax1;                // [Gmax1]
     int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);                      // [WALK_MAX_GROUPS + 1]
     uint32_t* misc = reinterpret_cast<uint32_t*>(bounds + WALK_MAX_GROUPS + 1);  // [4]
@@ -841,25 +921,6 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
             while (b < (int64_t)m && b > 0 && (st[b] & TIE_BIT)) ++b;
             bounds[tid] = (int)b;
         }
-        for (int k = tid; k < (groups + 1) * Gmax1; k += blockDim.x) hist[k] = 0;
-        __syncthreads();
-        for (uint32_t i = tid; i < m; i += blockDim.x) {
-            const uint32_t e = st[i];
-            if (SHIFT && (e & ROLE_L)) continue;
-            int cg = 0;
-            while (cg + 1 < groups && (int)i >= bounds[cg + 1]) ++cg;
-            atomicAdd(&hist[(cg + 1) * Gmax1 + (e & LAB_MASK)], 1u);
-        }
-        __syncthreads();
-        for (int R = tid; R < Gt; R += blockDim.x) {  // hist[cg][R]: label-R entries before chunk cg
-            uint32_t run = 0;
-            for (int cg = 0; cg <= groups; ++cg) {
-                run += hist[cg * Gmax1 + R];
-                hist[cg * Gmax1 + R] = run;
-            }
-            nnzv[R] = run;
-        }
-        __syncthreads();
         for (int tb = 0; tb < ntiles; tb += tpb) {
             const int bt = min(tpb, ntiles - tb);
             const size_t rpad = (size_t)bt * W;
@@ -869,7 +930,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
                 const int cg = warp / bt, tile = tb + warp % bt;
                 const int R0 = tile * W + lane;
                 walk_range<AccT, SHIFT, J>(st, bounds[cg], bounds[cg + 1], R0,
-                                           acc + (size_t)cg * Gt * rpad + (R0 - tb * W), rpad, hist + cg * Gmax1, Gt, lane);
+                                           acc + (size_t)cg * Gt * rpad + (R0 - tb * W), rpad, hist + cg * Gmax1,
+                                           hist + (WALK_MAX_GROUPS + cg) * Gmax1, Gt, lane);
             }
             __syncthreads();
             for (int k = tid; k < Gt * (int)rpad; k += blockDim.x) {
@@ -882,6 +944,30 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
             }
             __syncthreads();
         }
+        // Every chunk was walked with its running counts starting at zero. What the earlier chunks
+        // add to cell (L, R) is (entries of L in the chunk, adding role) x (entries of R before the
+        // chunk, counted role) -- twice that with a shift, where an adding entry takes the count
+        // before its run plus the count after it. The walkers left both per-chunk counts in `hist`.
+        uint32_t* hist_l = hist + (size_t)WALK_MAX_GROUPS * Gmax1;
+        for (int R = tid; R < Gt; R += blockDim.x) {
+            uint32_t run = 0;
+            for (int cg = 0; cg < groups; ++cg) {
+                const uint32_t here = hist[cg * Gmax1 + R];
+                hist[cg * Gmax1 + R] = run;
+                if (!SHIFT) hist_l[cg * Gmax1 + R] = here;
+                run += here;
+            }
+            nnzv[R] = run;
+        }
+        __syncthreads();
+        for (int k = tid; k < Gt * Gt; k += blockDim.x) {
+            const int L = k / Gt, R = k % Gt;
+            unsigned long long s = 0;
+            for (int cg = 1; cg < groups; ++cg)
+                s += (unsigned long long)hist_l[cg * Gmax1 + L] * (unsigned long long)hist[cg * Gmax1 + R];
+            bfull[k] += SHIFT ? 2ull * s : s;
+        }
+        __syncthreads();
         for (int pp = P.pair_ptr[ui.u] + tid; pp < P.pair_ptr[ui.u + 1]; pp += blockDim.x) {
             const int l = P.pair_l[pp], r = P.pair_r[pp];
             const long long nL = ut.ncells_dev[ui.first + l], nR = ut.ncells_dev[ui.first + r];
