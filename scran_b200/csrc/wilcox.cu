@@ -785,11 +785,60 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
             for (int j = 0; j < J; ++j) r[a][32 * j] = v[a][j];
         }
     };
+    // Long runs of equal values (integer-valued data): inside a run every entry adds the SAME vector
+    // (the counts at the run start) to its label's row, and the running counts only matter again when
+    // the run ends. Blocks of 32 entries that lie wholly inside a run are therefore only counted
+    // per label (cd, in registers: lane R holds the count of its own labels), and the rows are
+    // brought up to date once, when the run ends: row[L] += cd[L] * cs. Needs the warp to own every
+    // label of the unit (one wide tile), since the count of label L lives in L's lane.
+    const bool can_defer = !SHIFT && R0 == lane && Gt <= 32 * J;
+    uint32_t cd[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) cd[j] = 0u;
+    bool deferred = false;
+    auto flush = [&]() {
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            for (int src = 0; src < 32; ++src) {
+                const int L = 32 * j + src;
+                if (L >= Gt) break;
+                const uint32_t h = __shfl_sync(0xffffffffu, cd[j], src);
+                if (h != 0u) {
+                    AccT* row = reinterpret_cast<AccT*>(colb + (uint32_t)L * rowbytes);
+#pragma unroll
+                    for (int q = 0; q < J; ++q) row[32 * q] += (AccT)h * (AccT)cs[q];
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            c[j] += cd[j];
+            cd[j] = 0u;
+        }
+        deferred = false;
+    };
+    // The next block's entries are requested before the current block is walked.
+    uint32_t ent_next = (i_lo + lane) < i_hi ? (uint32_t)st[i_lo + lane] : 0u;
     for (int i0 = i_lo; i0 < i_hi; i0 += 32) {
-        const int mine = i0 + lane;
-        const uint32_t ent = mine < i_hi ? (uint32_t)st[mine] : 0u;
+        const uint32_t ent = ent_next;
+        {
+            const int nxt = i0 + 32 + lane;
+            ent_next = nxt < i_hi ? (uint32_t)st[nxt] : 0u;
+        }
         if (i_hi - i0 >= 32) {
-            if (!SHIFT && !__any_sync(0xffffffffu, (ent & TIE_BIT) != 0u)) {
+            const unsigned tied = __ballot_sync(0xffffffffu, (ent & TIE_BIT) != 0u);
+            if (can_defer && tied == 0xffffffffu) {
+                deferred = true;
+#pragma unroll 8
+                for (int k = 0; k < 32; ++k) {
+                    const int lab = (int)(__shfl_sync(0xffffffffu, ent, k) & LAB_MASK);
+#pragma unroll
+                    for (int j = 0; j < J; ++j) bump(cd[j], lab, Rj[j]);
+                }
+                continue;
+            }
+            if (deferred) flush();
+            if (!SHIFT && tied == 0u) {
 #pragma unroll
                 for (int k = 0; k < 28; k += QN) {
                     uint32_t l[QN];
@@ -808,10 +857,12 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
                 for (int k = 0; k < 32; ++k) step(__shfl_sync(0xffffffffu, ent, k));
             }
         } else {
+            if (deferred) flush();
             const int cnt = i_hi - i0;
             for (int k = 0; k < cnt; ++k) step(__shfl_sync(0xffffffffu, ent, k));
         }
     }
+    if (deferred) flush();
 #pragma unroll
     for (int j = 0; j < J; ++j) {
         if (Rj[j] < Gt) {
@@ -916,10 +967,18 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         const int ntiles = (Gt + W - 1) / W;  // wide tiles
         const int tpb = min(P.tiles_per_batch, ntiles);
         int groups = max(1, min(P.groups, WALK_WARPS / tpb));
-        if (tid <= groups) {
-            int64_t b = tid == groups ? (int64_t)m : ((int64_t)m * tid) / groups;
-            while (b < (int64_t)m && b > 0 && (st[b] & TIE_BIT)) ++b;
-            bounds[tid] = (int)b;
+        if (warp <= groups) {  // chunk starts: the first run start at or after the even split (a warp scans 32 entries a step)
+            int64_t b = warp == groups ? (int64_t)m : ((int64_t)m * warp) / groups;
+            while (b < (int64_t)m && b > 0) {
+                const bool stop = b + lane >= (int64_t)m || !(st[b + lane] & TIE_BIT);
+                const unsigned found = __ballot_sync(0xffffffffu, stop);
+                if (found) {
+                    b += __ffs(found) - 1;
+                    break;
+                }
+                b += 32;
+            }
+            if (lane == 0) bounds[warp] = (int)b;
         }
         for (int tb = 0; tb < ntiles; tb += tpb) {
             const int bt = min(tpb, ntiles - tb);

@@ -129,6 +129,28 @@ def test_overlap_large_units(sb, port_lib):
         assert np.array_equal(t, pt)
 
 
+def test_overlap_long_tie_runs(sb, port_lib):
+    """Integer-valued data: runs of equal values much longer than a warp's block of 32 entries, in
+    units small enough for the warp-group walk, with 3 and with 40 groups (one and two labels a lane)."""
+    rng = np.random.default_rng(78)
+    ncells = 9000
+    x = np.zeros((5, ncells))
+    x[0] = rng.poisson(1.5, ncells)
+    x[1] = np.where(rng.random(ncells) < 0.5, rng.poisson(4, ncells), 0)
+    x[2] = np.where(rng.random(ncells) < 0.3, 2.0, 0)                       # one run
+    x[3] = np.where(rng.random(ncells) < 0.5, -rng.poisson(1, ncells), rng.poisson(1, ncells))  # both sides of zero
+    x[4] = np.where(rng.random(ncells) < 0.6, np.round(rng.normal(size=ncells), 1), 0)  # short and long runs mixed
+    for ngroups in (3, 40):
+        g = rng.integers(0, ngroups, ncells)
+        groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(ngroups)]
+        left, right = all_pairs(ngroups)
+        for lfc in (0.0, 1.0):
+            u, t = sb.overlap_exprs_paired(as_csc(x), left, right, groups, lfc, want_ties=True)
+            pu, pt = port_lib.overlap_paired(as_csc(x), left, right, groups, lfc, want_ties=True)
+            assert np.array_equal(u, pu)
+            assert np.array_equal(t, pt)
+
+
 # ---------------------------------------------------------------------------------------------
 # computeMinRank
 # ---------------------------------------------------------------------------------------------
