@@ -50,7 +50,7 @@ constexpr uint32_t LAB_MASK = 0x3fff;
 constexpr uint32_t ROLE_L = 0x4000;
 constexpr uint32_t TIE_BIT = 0x8000;
 constexpr int MAX_LABELS = 16383;
-constexpr int MAXB = 512;      // units per job at most
+constexpr int MAXB = 256;      // units per job at most (also: the 256 value buckets of a large unit)
 constexpr int MAXSEG = 4096;   // segment boundaries staged per job at most
 
 struct UnitTables {
@@ -198,7 +198,7 @@ struct SortParams {
     const double* vals;
     const double *vmin, *vmax;  // per (device combination, gene) value range from K2
     double shift;
-    int cap, maxG;
+    int cap, segcap, maxG;
     uint16_t* stream;
     uint32_t* unit_m;
     uint64_t *g_ka, *g_kb;   // global scratch, indexed like the stream (units beyond cap only)
@@ -209,49 +209,65 @@ struct SortParams {
     unsigned long long* job_counter;
 };
 
+// Shared memory of k3_sort. The big "region" of 12 bytes per element holds key[cap] (8 B) |
+// lab[cap] (2 B) | bk[cap] (2 B): one 16-bit counter per bucket. The radix fallback for a value
+// bucket beyond the capacity works in global memory and borrows the region for its histograms.
 struct SortSmem {
-    uint64_t *ka, *kb;
-    uint32_t *pa, *pb;
-    uint32_t* whist;
-    uint32_t* seg;       // MAXSEG + MAXB + 8 staged segment boundaries
+    uint64_t* key;
+    uint16_t* lab;
+    uint32_t* bk;        // cap / 2 words: two 16-bit bucket counters a word
+    uint32_t* whist;     // SORT_HIST_WORDS at the start of the region: radix passes of the fallback sort
+    uint32_t* seg;       // segcap + MAXB + 8 staged segment boundaries
     uint32_t* segptr;    // MAXB + 1
-    uint32_t* off;       // MAXB + 1: compact element offset of each unit in the job
-    uint32_t* drop;      // MAXB
+    uint32_t* off;       // MAXB + 1: compact element offset of each segment of the job
+    uint32_t* drop;      // MAXB: stored zeros of the segment (they are not part of the stream)
     uint32_t* n;         // MAXB
+    uint32_t* src;       // MAXB: scratch segments: where the segment starts in the unit's scratch
+    uint32_t* limit;     // MAXB: scratch segments: entries of the segment that belong to the stream
     int64_t* vbase;      // MAXB
-    int64_t* soff;       // MAXB
+    int64_t* soff;       // MAXB: stream position of the segment's first entry
+    double* fmin;        // MAXB: value range of the segment -> bucket = (v - fmin) * scale
+    double* scale;       // MAXB
     uint32_t* boff;      // 258: bucket offsets of the value partition
     unsigned long long *bmin, *bmax;  // 256 each: smallest / largest key of every bucket
     uint32_t* gcur;      // 256: write cursor of every bucket in global scratch
-    uint32_t* tb;        // 260: bucket starts inside the current tile
+    uint32_t* biglist;   // cap / BUCKET_RANK_MAX + 2: buckets too large for all-pairs ranking
+    uint32_t* scan;      // 40: block scan exchange
     uint32_t* misc;      // 16
 };
 
-constexpr size_t sort_fixed_bytes() {
-    return (size_t)SORT_HIST_WORDS * 4 + (size_t)(MAXSEG + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 2 +
-           (size_t)MAXB * 8 * 2 + 512 * 8 + 258 * 4 + 256 * 4 + 260 * 4 + 16 * 4 + 64;
+constexpr int BUCKET_RANK_MAX = 32;  // buckets up to this size are ranked by all-pairs counting
+
+constexpr size_t sort_fixed_bytes(int cap, int segcap) {
+    return (size_t)(segcap + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 4 + (size_t)MAXB * 8 * 4 + 512 * 8 +
+           258 * 4 + 256 * 4 + (size_t)(cap / BUCKET_RANK_MAX + 2) * 4 + 40 * 4 + 16 * 4 + 128;
 }
 
-__device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap) {
+__device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap, int segcap) {
     SortSmem s;
-    s.ka = reinterpret_cast<uint64_t*>(raw);
-    s.kb = s.ka + cap;
-    s.vbase = reinterpret_cast<int64_t*>(s.kb + cap);
+    s.key = reinterpret_cast<uint64_t*>(raw);
+    s.lab = reinterpret_cast<uint16_t*>(s.key + cap);
+    s.bk = reinterpret_cast<uint32_t*>(s.lab + cap);
+    s.whist = reinterpret_cast<uint32_t*>(raw);
+    unsigned char* p = raw + (size_t)cap * 12;
+    s.vbase = reinterpret_cast<int64_t*>(p);
     s.soff = s.vbase + MAXB;
-    s.bmin = reinterpret_cast<unsigned long long*>(s.soff + MAXB);
+    s.fmin = reinterpret_cast<double*>(s.soff + MAXB);
+    s.scale = s.fmin + MAXB;
+    s.bmin = reinterpret_cast<unsigned long long*>(s.scale + MAXB);
     s.bmax = s.bmin + 256;
-    s.pa = reinterpret_cast<uint32_t*>(s.bmax + 256);
-    s.pb = s.pa + cap;
-    s.whist = s.pb + cap;
-    s.seg = s.whist + SORT_HIST_WORDS;
-    s.segptr = s.seg + (MAXSEG + MAXB + 8);
+    s.seg = reinterpret_cast<uint32_t*>(s.bmax + 256);
+    s.segptr = s.seg + (segcap + MAXB + 8);
     s.off = s.segptr + (MAXB + 1);
     s.drop = s.off + (MAXB + 1);
     s.n = s.drop + MAXB;
-    s.boff = s.n + MAXB;
+    s.src = s.n + MAXB;
+    s.limit = s.src + MAXB;
+    s.boff = s.limit + MAXB;
     s.gcur = s.boff + 258;
-    s.tb = s.gcur + 256;
-    s.misc = s.tb + 260;
+    s.biglist = s.gcur + 256;
+    s.scan = s.biglist + (cap / BUCKET_RANK_MAX + 2);
+    s.misc = s.scan + 40;
     return s;
 }
 
@@ -281,7 +297,7 @@ __device__ inline void unit_element(const double* __restrict__ vals, int64_t vba
     key = keep ? key_of(v) : ~0ull;
 }
 
-// Key of element e without its label (enough for the range and the bucket histogram).
+// Key of element e without its label (enough for the bucket counts).
 __device__ inline void unit_key(const double* __restrict__ vals, int64_t vbase, uint32_t n, double shift, uint32_t e,
                                 uint64_t& key, bool& keep) {
     const uint32_t per_role = n + 1;
@@ -297,22 +313,285 @@ __device__ inline void unit_key(const double* __restrict__ vals, int64_t vbase, 
     key = keep ? key_of(v) : ~0ull;
 }
 
-// Value bucket of a key: 256 buckets of equal width in VALUE space over [fmin, fmax] (equal width
-// in key space would follow the exponent and put a whole binade range into one bucket). Monotone
-// in the value, so the buckets are ordered; values outside the range (the probes) clamp to the
-// ends; dropped entries go to the last bucket, where their all-ones key sorts them last.
-__device__ __forceinline__ unsigned value_bucket(uint64_t key, bool keep, double fmin, double scale) {
-    if (!keep) return 255u;
+// Value bucket of a key: `nbuckets` buckets of equal width in VALUE space over [fmin, fmax] (equal
+// width in key space would follow the exponent and put a whole binade range into one bucket).
+// Monotone in the value, so the buckets are ordered and equal values share a bucket; values outside
+// the range (the probes) clamp to the ends; dropped entries go to the last bucket, where their
+// all-ones key sorts them last.
+__device__ __forceinline__ unsigned value_bucket(uint64_t key, bool keep, double fmin, double scale, unsigned nbuckets) {
+    if (!keep) return nbuckets - 1u;
     const double x = (value_of(key) - fmin) * scale;
-    return x >= 255.0 ? 255u : (x > 0.0 ? (unsigned)x : 0u);
+    return x >= (double)(nbuckets - 1u) ? nbuckets - 1u : (x > 0.0 ? (unsigned)x : 0u);
+}
+
+// Segment of compact element / bucket index p: last s with off[s] <= p.
+__device__ __forceinline__ int find_segment(const uint32_t* off, int nb, uint32_t p) {
+    if (nb == 1) return 0;
+    int lo = 0, hi = nb;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (off[mid] <= p) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// (key, role) order: inside a tie the R role (bit clear) comes before the L role.
+__device__ __forceinline__ bool elem_before(uint64_t ka, uint32_t la, uint64_t kb, uint32_t lb) {
+    return ka < kb || (ka == kb && (la & ROLE_L) < (lb & ROLE_L));
+}
+
+// In-place sort of sz (key, label) pairs in shared memory by one warp: a bitonic network whose
+// merges start with a "flip" so that every compare-exchange is ascending; positions >= sz act as
+// +infinity and are simply never touched.
+__device__ inline void warp_bitonic(uint64_t* k, uint16_t* l, int sz, int lane) {
+    int n2 = 2;
+    while (n2 < sz) n2 <<= 1;
+    auto cmpx = [&](int a, int b) {
+        const uint64_t ka = k[a], kb = k[b];
+        const uint16_t la = l[a], lb = l[b];
+        if (elem_before(kb, lb, ka, la)) {
+            k[a] = kb;
+            k[b] = ka;
+            l[a] = lb;
+            l[b] = la;
+        }
+    };
+    for (int span = 2; span <= n2; span <<= 1) {
+        const int half = span >> 1;
+        for (int i = lane; i < (n2 >> 1); i += 32) {
+            const int blk = i / half, r = i - blk * half;
+            const int a = blk * span + r, b = blk * span + span - 1 - r;
+            if (b < sz) cmpx(a, b);
+        }
+        __syncwarp();
+        for (int j = span >> 2; j > 0; j >>= 1) {
+            for (int i = lane; i < (n2 >> 1); i += 32) {
+                const int a = ((i / j) * 2 * j) + (i % j), b = a + j;
+                if (b < sz) cmpx(a, b);
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// Sorts the `nb` segments of a job (together `total` <= cap elements) and writes their label
+// streams. No radix passes: an element goes straight to one of as many equal-width value buckets
+// as its segment has elements (one counting pass, one scan, one scatter, all in shared memory),
+// after which almost every bucket holds a handful of elements or copies of one value:
+//  * buckets of up to BUCKET_RANK_MAX elements: every element counts the elements of its bucket
+//    that precede it (all pairs) and so knows its final position and whether it ties with its
+//    predecessor;
+//  * larger buckets (many equal values, or a very uneven value distribution) go to a list and
+//    are finished by one warp each: nothing to do if all keys are equal, else a bitonic sort.
+// The bucket index space is the element index space: bucket off[s] + b of segment s.
+// SCRATCH = false: segments are whole units, elements are read from K1's values;
+// SCRATCH = true:  segments are value buckets of ONE unit that the tile split left in global memory.
+template <bool SCRATCH>
+__device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, uint32_t total, const uint64_t* gk,
+                                const uint32_t* gp) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool two_roles = P.ut.mult == 2;
+    uint16_t* bh = reinterpret_cast<uint16_t*>(S.bk);
+    auto fetch = [&](uint32_t e, bool want_label, uint64_t& key, uint32_t& lab, bool& keep, int& s) {
+        s = find_segment(S.off, nb, e);
+        const uint32_t el = e - S.off[s];
+        if (SCRATCH) {
+            key = gk[S.src[s] + el];
+            lab = want_label ? (gp[S.src[s] + el] & 0xffffu) : 0u;
+            keep = key != ~0ull;
+        } else if (want_label) {
+            unit_element(P.vals, S.vbase[s], S.n[s], S.seg + S.segptr[s], (int)(S.segptr[s + 1] - S.segptr[s]) - 1, P.shift,
+                         el, key, lab, keep);
+        } else {
+            lab = 0u;
+            unit_key(P.vals, S.vbase[s], S.n[s], P.shift, el, key, keep);
+        }
+    };
+    auto bucket_of = [&](uint64_t key, bool keep, int s) {
+        return S.off[s] + value_bucket(key, keep, S.fmin[s], S.scale[s], S.off[s + 1] - S.off[s]);
+    };
+
+    // ---- counts ----
+    for (uint32_t i = tid; i < ((total + 1) >> 1); i += blockDim.x) S.bk[i] = 0;
+    if (tid == 0) S.misc[5] = 0;
+    __syncthreads();
+    for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {  // four loads in flight per thread
+        uint64_t key[4];
+        uint32_t lab;
+        bool keep[4], valid[4];
+        int s[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t e = t + q * blockDim.x;
+            valid[q] = e < total;
+            key[q] = 0;
+            keep[q] = false;
+            s[q] = 0;
+            if (valid[q]) fetch(e, false, key[q], lab, keep[q], s[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (valid[q]) {
+                const uint32_t b = bucket_of(key[q], keep[q], s[q]);
+                atomicAdd(&S.bk[b >> 1], 1u << ((b & 1u) * 16u));
+                if (!SCRATCH && !keep[q]) atomicAdd(&S.drop[s[q]], 1u);
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- exclusive scan of the counts (in place), large buckets noted ----
+    {
+        const uint32_t per = (total + blockDim.x - 1) / blockDim.x;
+        const uint32_t lo = min(total, (uint32_t)tid * per), hi = min(total, lo + per);
+        uint32_t sum = 0;
+        for (uint32_t i = lo; i < hi; ++i) sum += bh[i];
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) S.scan[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t v = S.scan[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += y;
+            }
+            S.scan[lane] = v;
+        }
+        __syncthreads();
+        uint32_t at = (warp ? S.scan[warp - 1] : 0u) + incl - sum;
+        for (uint32_t i = lo; i < hi; ++i) {
+            const uint32_t c = bh[i];
+            bh[i] = (uint16_t)at;
+            at += c;
+            if (c > (uint32_t)BUCKET_RANK_MAX) S.biglist[atomicAdd(&S.misc[5], 1u)] = i;
+        }
+    }
+    __syncthreads();
+
+    // ---- scatter into bucket order: afterwards bh[b] is the END of bucket b ----
+    for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {
+        uint64_t key[4];
+        uint32_t lab[4];
+        bool keep[4], valid[4];
+        int s[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t e = t + q * blockDim.x;
+            valid[q] = e < total;
+            key[q] = 0;
+            lab[q] = 0;
+            keep[q] = false;
+            s[q] = 0;
+            if (valid[q]) fetch(e, true, key[q], lab[q], keep[q], s[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (valid[q]) {
+                const uint32_t b = bucket_of(key[q], keep[q], s[q]);
+                const uint32_t sh = (b & 1u) * 16u;
+                const uint32_t pos = (atomicAdd(&S.bk[b >> 1], 1u << sh) >> sh) & 0xffffu;
+                S.key[pos] = key[q];
+                S.lab[pos] = (uint16_t)lab[q];
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- small buckets: rank by counting, one thread per element ----
+    for (uint32_t p = tid; p < total; p += blockDim.x) {
+        const uint64_t key = S.key[p];
+        const int s = find_segment(S.off, nb, p);
+        const uint32_t b = bucket_of(key, key != ~0ull, s);
+        const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
+        if (end - start > (uint32_t)BUCKET_RANK_MAX) continue;
+        const uint32_t lp = S.lab[p];
+        uint32_t rank = 0;
+        bool tie = false;
+        if (end - start > 1) {
+            if (two_roles) {
+                for (uint32_t j = start; j < end; ++j) {
+                    const uint64_t kj = S.key[j];
+                    const uint32_t lj = S.lab[j];
+                    const bool eq = kj == key;
+                    const bool before = kj < key || (eq && ((lj & ROLE_L) < (lp & ROLE_L) || ((lj & ROLE_L) == (lp & ROLE_L) && j < p)));
+                    rank += before ? 1u : 0u;
+                    tie |= eq && before;
+                }
+            } else {
+                for (uint32_t j = start; j < end; ++j) {
+                    const uint64_t kj = S.key[j];
+                    const bool eq = kj == key;
+                    const bool before = kj < key || (eq && j < p);
+                    rank += before ? 1u : 0u;
+                    tie |= eq && before;
+                }
+            }
+        }
+        const uint32_t q = start + rank - S.off[s];
+        const uint32_t lim = SCRATCH ? S.limit[s] : (S.off[s + 1] - S.off[s]) - S.drop[s];
+        if (q < lim) P.stream[S.soff[s] + q] = (uint16_t)((lp & 0x7fffu) | (tie ? TIE_BIT : 0u));
+    }
+
+    // ---- large buckets: one warp each ----
+    const uint32_t nbig = S.misc[5];
+    for (uint32_t w = warp; w < nbig; w += blockDim.x / 32) {
+        const uint32_t b = S.biglist[w];
+        const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
+        const int sz = (int)(end - start);
+        const int s = find_segment(S.off, nb, b);
+        const uint32_t lim = SCRATCH ? S.limit[s] : (S.off[s + 1] - S.off[s]) - S.drop[s];
+        uint64_t* k = S.key + start;
+        uint16_t* l = S.lab + start;
+        const uint64_t k0 = k[0];
+        bool same = true;
+        for (int i = lane; i < sz; i += 32) same &= k[i] == k0;
+        same = __all_sync(0xffffffffu, same);
+        const uint32_t base = start - S.off[s];
+        if (same && two_roles) {
+            // one value in both roles: R-role entries first, each role in the order found
+            uint32_t n_r = 0;
+            for (int i = lane; i < sz; i += 32) n_r += (l[i] & ROLE_L) ? 0u : 1u;
+            for (int o = 16; o > 0; o >>= 1) n_r += __shfl_xor_sync(0xffffffffu, n_r, o);
+            uint32_t seen_r = 0, seen_l = 0;
+            for (int i0 = 0; i0 < sz; i0 += 32) {
+                const int i = i0 + lane;
+                const bool valid = i < sz;
+                const uint32_t lab = valid ? (uint32_t)l[i] : 0u;
+                const bool is_l = valid && (lab & ROLE_L);
+                const unsigned ml = __ballot_sync(0xffffffffu, is_l), mr = __ballot_sync(0xffffffffu, valid && !is_l);
+                const unsigned below = (1u << lane) - 1u;
+                if (valid) {
+                    const uint32_t q = is_l ? n_r + seen_l + __popc(ml & below) : seen_r + __popc(mr & below);
+                    if (base + q < lim) P.stream[S.soff[s] + base + q] = (uint16_t)((lab & 0x7fffu) | (q > 0 ? TIE_BIT : 0u));
+                }
+                seen_l += __popc(ml);
+                seen_r += __popc(mr);
+            }
+            continue;
+        }
+        if (!same) warp_bitonic(k, l, sz, lane);
+        for (int i = lane; i < sz; i += 32) {
+            if (base + i < lim) {
+                const bool tie = i > 0 && k[i] == k[i - 1];
+                P.stream[S.soff[s] + base + i] = (uint16_t)(((uint32_t)l[i] & 0x7fffu) | (tie ? TIE_BIT : 0u));
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const SortSmem S = carve_sort_smem(smem_raw, P.cap);
+    const SortSmem S = carve_sort_smem(smem_raw, P.cap, P.segcap);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int njobs = *P.njobs;
     const UnitTables& ut = P.ut;
+    const double inf = __longlong_as_double(0x7ff0000000000000ll);
 
     while (true) {
         __syncthreads();
@@ -323,7 +602,6 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         const int64_t t0 = P.jobs[job], t1 = P.jobs[job + 1];
         const int nb = (int)(t1 - t0);
 
-        PHASE_T(p_t0);
         // ---- per-unit tables -------------------------------------------------------------
         if (tid < nb) {
             const UnitInfo ui = unit_info(ut, t0 + tid);
@@ -374,74 +652,13 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
             const uint32_t seg0 = ut.seg_off[(size_t)first * ut.ngenes + g];
             S.seg[e] = ut.seg_off[(size_t)(first + (e - S.segptr[lo])) * ut.ngenes + g] - seg0;
         }
-        __syncthreads();
-
-        if (total <= (uint32_t)P.cap) {
-            PHASE_T(p_b0);
-            // ---- shared-memory path: all units of the job in one sort ---------------------
-            for (uint32_t e = tid; e < total; e += blockDim.x) {
-                int lo = 0, hi = nb;
-                while (hi - lo > 1) {
-                    const int mid = (lo + hi) >> 1;
-                    if (S.off[mid] <= e) lo = mid; else hi = mid;
-                }
-                uint64_t key;
-                uint32_t lab;
-                bool keep;
-                unit_element(P.vals, S.vbase[lo], S.n[lo], S.seg + S.segptr[lo], (int)(S.segptr[lo + 1] - S.segptr[lo]) - 1,
-                             P.shift, e - S.off[lo], key, lab, keep);
-                S.ka[e] = key;
-                S.pa[e] = ((uint32_t)lo << 16) | lab;
-                if (!keep) atomicAdd(&S.drop[lo], 1u);
-            }
-            __syncthreads();
-            PHASE_T(p_b1);
-            int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)total, S.whist);
-            PHASE_T(p_b2);
-            if (nb > 1) {  // regroup by unit slot (stable): one pass per slot byte
-                uint64_t* k0 = cur ? S.kb : S.ka;
-                uint32_t* p0 = cur ? S.pb : S.pa;
-                uint64_t* k1 = cur ? S.ka : S.kb;
-                uint32_t* p1 = cur ? S.pa : S.pb;
-                const int c2 = block_radix_sort<uint32_t, true>(k0, p0, k1, p1, (int)total, 16, nb > 256 ? 32 : 24, S.whist);
-                cur = c2 ? (cur ^ 1) : cur;
-            }
-            PHASE_T(p_b3);
-            const uint64_t* rk = cur ? S.kb : S.ka;
-            const uint32_t* rp = cur ? S.pb : S.pa;
-            for (uint32_t j = tid; j < total; j += blockDim.x) {
-                const uint32_t pay = rp[j];
-                const uint32_t slot = pay >> 16;
-                const uint32_t pos = j - S.off[slot];
-                const uint32_t m = (S.off[slot + 1] - S.off[slot]) - S.drop[slot];
-                if (pos < m) {
-                    uint32_t e = pay & 0x7fffu;
-                    if (pos > 0 && rk[j] == rk[j - 1]) e |= TIE_BIT;
-                    P.stream[S.soff[slot] + pos] = (uint16_t)e;
-                }
-            }
-            PHASE_T(p_b4); PHASE_ADD(0, p_t0, p_b0); PHASE_ADD(1, p_b0, p_b1); PHASE_ADD(2, p_b1, p_b2); PHASE_ADD(3, p_b2, p_b3); PHASE_ADD(4, p_b3, p_b4);
-            if (tid < nb) P.unit_m[t0 + tid] = (S.off[tid + 1] - S.off[tid]) - S.drop[tid];
-            continue;
-        }
-
-        // ---- one unit beyond the shared-memory capacity ------------------------------------
-        // (nb == 1 by construction.) Split by value into 256 ordered buckets with one stable pass
-        // into global scratch, then sort runs of consecutive buckets in shared memory.
-        const int64_t vbase = S.vbase[0], soff = S.soff[0];
-        const uint32_t n = S.n[0];
-        const int G = (int)nseg - 1;
-        uint64_t* ga = P.g_ka + soff;
-        uint32_t* gp = P.g_pa + soff;
-        uint64_t* gb = P.g_kb + soff;
-        uint32_t* gq = P.g_pb + soff;
-        PHASE_T(p_g0); PHASE_ADD(0, p_t0, p_g0);
-        // pass 0: value range of the unit (both roles, probes excluded), from the per-segment ranges
-        // that K2 left behind: no pass over the values
-        if (tid == 0) S.misc[3] = 0;  // dropped (stored zero) entries, counted in pass 1
-        double fmin = __longlong_as_double(0x7ff0000000000000ll), fmax = -fmin;
-        if (warp == 0) {
-            const int first = ut.unit_first[(int)(t0 % ut.U)], gene = (int)(t0 / ut.U);
+        // value range of every unit (both roles, probes excluded), from the per-segment ranges that
+        // K2 left behind: no pass over the values
+        for (int s = warp; s < nb; s += blockDim.x / 32) {
+            const int64_t task = t0 + s;
+            const int gene = (int)(task / ut.U), first = ut.unit_first[(int)(task % ut.U)];
+            const int G = (int)(S.segptr[s + 1] - S.segptr[s]) - 1;
+            double fmin = inf, fmax = -inf;
             for (int k = lane; k < G; k += 32) {
                 const double lo_v = P.vmin[(size_t)(first + k) * ut.ngenes + gene];
                 const double hi_v = P.vmax[(size_t)(first + k) * ut.ngenes + gene];
@@ -460,23 +677,44 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 fmax = fmax > b ? fmax : b;
             }
             if (lane == 0) {
-                double* red = reinterpret_cast<double*>(S.whist);
-                red[0] = fmin;
-                red[1] = fmax;
+                const uint32_t cnt = S.off[s + 1] - S.off[s];
+                S.fmin[s] = fmax > fmin ? fmin : 0.0;
+                S.scale[s] = fmax > fmin ? (double)cnt / (fmax - fmin) : 0.0;
+                if (nb == 1) {  // the plain range, for the 256-way split of a unit beyond the capacity
+                    double* red = reinterpret_cast<double*>(S.scan);
+                    red[0] = fmin;
+                    red[1] = fmax;
+                }
             }
         }
         __syncthreads();
-        fmin = reinterpret_cast<double*>(S.whist)[0];
-        fmax = reinterpret_cast<double*>(S.whist)[1];
-        __syncthreads();
-        const double scale = fmax > fmin ? 256.0 / (fmax - fmin) : 0.0;
 
-        PHASE_T(p_g1); PHASE_ADD(5, p_g0, p_g1);
-        // pass 1: stable split by value bucket (dropped entries: bucket 255) into global
-        // scratch. First the unit-wide bucket counts, then tile by tile: a tile is put in bucket
-        // order in shared memory (one stable radix pass) and each bucket's run of the tile is appended
-        // to the bucket's region, so that global memory sees runs of consecutive entries instead
-        // of one scattered 12-byte write per entry.
+        if (total <= (uint32_t)P.cap) {
+            // ---- shared-memory path: all units of the job at once -----------------------------
+            bucket_sort_job<false>(P, S, nb, total, nullptr, nullptr);
+            if (tid < nb) P.unit_m[t0 + tid] = (S.off[tid + 1] - S.off[tid]) - S.drop[tid];
+            continue;
+        }
+
+        // ---- one unit beyond the shared-memory capacity ------------------------------------
+        // (nb == 1 by construction.) Split by value into 256 ordered buckets with one stable pass
+        // into global scratch; consecutive buckets that fit shared memory together are then sorted
+        // there, every bucket as a segment with its own value range.
+        const int64_t vbase = S.vbase[0], soff = S.soff[0];
+        const uint32_t n = S.n[0];
+        const int G = (int)nseg - 1;
+        uint64_t* ga = P.g_ka + soff;
+        uint32_t* gp = P.g_pa + soff;
+        uint64_t* gb = P.g_kb + soff;
+        uint32_t* gq = P.g_pb + soff;
+        const double fmin = reinterpret_cast<double*>(S.scan)[0], fmax = reinterpret_cast<double*>(S.scan)[1];
+        const double scale = fmax > fmin ? 256.0 / (fmax - fmin) : 0.0;
+        if (tid == 0) S.misc[3] = 0;  // dropped (stored zero) entries, counted in pass 1
+        __syncthreads();
+
+        // pass 1: the unit-wide bucket counts, then every element straight to the next free place of
+        // its bucket's region (the order inside a bucket is free; each region is filled front to back
+        // within microseconds, so L2 collects the 12-byte writes into whole lines)
         {
             for (int i = tid; i < 256; i += blockDim.x) {
                 S.gcur[i] = 0;
@@ -499,9 +737,9 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     if (valid[q]) {
-                        const unsigned d = value_bucket(key[q], keep[q], fmin, scale);
+                        const unsigned d = value_bucket(key[q], keep[q], fmin, scale, 256u);
                         atomicAdd(&S.gcur[d], 1u);
-                        if (keep[q]) {  // key range of every bucket, for the digit skipping of the sorts
+                        if (keep[q]) {  // key range of every bucket: its own value range in pass 2
                             atomicMin(&S.bmin[d], (unsigned long long)key[q]);
                             atomicMax(&S.bmax[d], (unsigned long long)key[q]);
                         }
@@ -535,86 +773,81 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 if (lane == 31) S.boff[256] = at;
             }
             __syncthreads();
-            PHASE_T(p_h1); PHASE_ADD(10, p_g1, p_h1);
-            for (uint32_t tile = 0; tile < total; tile += (uint32_t)P.cap) {
-                const uint32_t tn = min((uint32_t)P.cap, total - tile);
-                for (uint32_t j = tid; j < tn; j += blockDim.x) {
-                    uint64_t key;
-                    uint32_t lab;
-                    bool keep;
-                    unit_element(P.vals, vbase, n, S.seg, G, P.shift, tile + j, key, lab, keep);
-                    const unsigned d = value_bucket(key, keep, fmin, scale);
-                    S.ka[j] = key;
-                    S.pa[j] = lab | (d << 16);
+            for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {
+                uint64_t key[4];
+                uint32_t lab[4];
+                bool keep[4], valid[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t e = t + q * blockDim.x;
+                    valid[q] = e < total;
+                    key[q] = 0;
+                    lab[q] = 0;
+                    keep[q] = false;
+                    if (valid[q]) unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key[q], lab[q], keep[q]);
                 }
-                __syncthreads();
-                const int cur = block_radix_sort<uint32_t, true>(S.ka, S.pa, S.kb, S.pb, (int)tn, 16, 24, S.whist, 0ull, S.tb);
-                const uint64_t* rk = cur ? S.kb : S.ka;
-                const uint32_t* rp = cur ? S.pb : S.pa;
-                for (uint32_t j = tid; j < tn; j += blockDim.x) {
-                    const uint32_t pay = rp[j];
-                    const unsigned d = pay >> 16;
-                    const uint32_t dst = S.gcur[d] + (j - S.tb[d]);
-                    ga[dst] = rk[j];
-                    gp[dst] = pay & 0xffffu;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (valid[q]) {
+                        const unsigned d = value_bucket(key[q], keep[q], fmin, scale, 256u);
+                        const uint32_t dst = atomicAdd(&S.gcur[d], 1u);
+                        ga[dst] = key[q];
+                        gp[dst] = lab[q];
+                    }
                 }
-                __syncthreads();
-                if (tid < 256) S.gcur[tid] += S.tb[tid + 1] - S.tb[tid];
-                __syncthreads();
             }
+            __syncthreads();
         }
-        const uint32_t m = total - S.misc[3];
+        const uint32_t ndropped = S.misc[3];
+        const uint32_t m = total - ndropped;
 
-        PHASE_T(p_g2); PHASE_ADD(6, p_g1, p_g2);  // includes slot 10
         // pass 2: runs of consecutive buckets that fit shared memory
         int d0 = 0;
         while (d0 < 256) {
             __syncthreads();
-            if (tid == 0) {  // extend the run of buckets while it fits; note the key range of the run
+            if (tid == 0) {  // extend the run of buckets while it fits
                 const uint32_t st0 = S.boff[d0];
                 int d = d0 + 1;
                 while (d < 256 && S.boff[d + 1] - st0 <= (uint32_t)P.cap) ++d;
                 S.misc[1] = (uint32_t)d;
-                unsigned long long lo_k = ~0ull, hi_k = 0ull;
-                for (int q = d0; q < d; ++q) {
-                    lo_k = S.bmin[q] < lo_k ? S.bmin[q] : lo_k;
-                    hi_k = S.bmax[q] > hi_k ? S.bmax[q] : hi_k;
-                }
-                // bits above the highest bit in which the smallest and the largest key of the run
-                // differ are common to all its keys (the dropped entries of the last bucket, whose
-                // key is not a value, switch this shortcut off)
-                int tb = 64;
-                if (hi_k >= lo_k && !(d == 256 && S.misc[3] > 0)) tb = lo_k == hi_k ? 0 : 64 - __clzll((long long)(lo_k ^ hi_k));
-                S.misc[4] = (uint32_t)tb;
             }
             __syncthreads();
             const uint32_t start = S.boff[d0];
             const int d1 = (int)S.misc[1];
             const uint32_t cnt = S.boff[d1] - start;
-            const int top_bit = (int)S.misc[4];
-            const uint64_t sub = 0;
+            const int dfirst = d0;
             d0 = d1;
             if (cnt == 0) continue;
-            const uint64_t* rk;
-            const uint32_t* rp;
             if (cnt <= (uint32_t)P.cap) {
-                PHASE_T(p_l0);
-                for (uint32_t j = tid; j < cnt; j += blockDim.x) {
-                    S.ka[j] = ga[start + j];
-                    S.pa[j] = gp[start + j];
+                const int nrun = d1 - dfirst;
+                if (tid < nrun) {
+                    const int d = dfirst + tid;
+                    const uint32_t c = S.boff[d + 1] - S.boff[d];
+                    const bool has = S.bmax[d] >= S.bmin[d];
+                    const double lo_v = has ? value_of(S.bmin[d]) : 0.0, hi_v = has ? value_of(S.bmax[d]) : 0.0;
+                    S.off[tid] = S.boff[d] - start;
+                    S.src[tid] = S.boff[d];
+                    S.soff[tid] = soff + S.boff[d];
+                    S.limit[tid] = d == 255 ? c - ndropped : c;
+                    S.fmin[tid] = lo_v;
+                    S.scale[tid] = hi_v > lo_v ? (double)c / (hi_v - lo_v) : 0.0;
                 }
+                if (tid == 0) S.off[nrun] = cnt;
                 __syncthreads();
-                PHASE_T(p_l1); PHASE_ADD(7, p_l0, p_l1);
-                const int cur = block_sort_keys<uint32_t>(S.ka, S.pa, S.kb, S.pb, (int)cnt, S.whist, top_bit, sub);
-                PHASE_T(p_l2); PHASE_ADD(8, p_l1, p_l2);
-                rk = cur ? S.kb : S.ka;
-                rp = cur ? S.pb : S.pa;
-            } else {  // a single bucket larger than shared memory (e.g. one heavily tied value)
-                const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist, top_bit, sub);
-                rk = cur ? gb + start : ga + start;
-                rp = cur ? gq + start : gp + start;
+                bucket_sort_job<true>(P, S, nrun, cnt, ga, gp);
+                continue;
             }
-            PHASE_T(p_e0);
+            // a single bucket larger than shared memory (e.g. one heavily tied value): radix sort in
+            // global memory, skipping the digits above the highest bit in which the smallest and the
+            // largest key differ (dropped entries, whose key is not a value, switch that off)
+            int top_bit = 64;
+            {
+                const unsigned long long lo_k = S.bmin[dfirst], hi_k = S.bmax[dfirst];
+                if (hi_k >= lo_k && !(d1 == 256 && ndropped > 0)) top_bit = lo_k == hi_k ? 0 : 64 - __clzll((long long)(lo_k ^ hi_k));
+            }
+            const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist, top_bit, 0ull);
+            const uint64_t* rk = cur ? gb + start : ga + start;
+            const uint32_t* rp = cur ? gq + start : gp + start;
             for (uint32_t j = tid; j < cnt; j += blockDim.x) {
                 const uint32_t pos = start + j;
                 if (pos < m) {
@@ -623,8 +856,6 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                     P.stream[soff + pos] = (uint16_t)e;
                 }
             }
-            __syncthreads();
-            PHASE_T(p_e1); PHASE_ADD(9, p_e0, p_e1);
         }
         if (tid == 0) P.unit_m[t0] = m;
     }
@@ -1209,12 +1440,16 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     int32_t* order = jobs + (ntasks + 2);
 
     // ---- plan ----
-    const size_t fixed = sort_fixed_bytes();
-    int cap = (int)((ctx->smem_optin - fixed) / 24);
-    cap &= ~31;
-    const size_t sort_smem = (size_t)cap * 24 + fixed;
+    // capacity of the shared-memory sort: 12 bytes per element plus the fixed tables (which hold a
+    // list with one entry per BUCKET_RANK_MAX elements)
+    const int segcap = std::max(2048, L.maxG + 1);  // staged segment boundaries of a job
+    int cap = (int)((ctx->smem_optin - sort_fixed_bytes(0, segcap)) * 8 / 97);
+    cap = std::min(cap, 65280) & ~63;
+    while (cap > 64 && (size_t)cap * 12 + sort_fixed_bytes(cap, segcap) > ctx->smem_optin) cap -= 64;
+    if ((size_t)cap * 12 < (size_t)SORT_HIST_WORDS * 4) throw Error("internal: shared memory too small for the sort");
+    const size_t sort_smem = (size_t)cap * 12 + sort_fixed_bytes(cap, segcap);
     const uint32_t small_max = (uint32_t)cap / 2, window = (uint32_t)cap - small_max;
-    const int maxb = std::max(1, std::min(MAXB, MAXSEG / (L.maxG + 1)));
+    const int maxb = std::max(1, std::min(MAXB, segcap / (L.maxG + 1)));
     SB_LAUNCH(ctx, k3_plan, 1, 1024, 0, ut, small_max, window, maxb, jobs, njobs);
     SB_LAUNCH(ctx, k3_order, 1, 1024, 0, ut, jobs, njobs, 16384u, order, nbig);
 
@@ -1235,6 +1470,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     if (!T.vmin || !T.vmax) throw Error("internal: the value ranges of the segments are missing");
     sp.shift = lfc;
     sp.cap = cap;
+    sp.segcap = segcap;
     sp.maxG = L.maxG;
     sp.stream = ctx->stream_lab.as<uint16_t>();
     sp.unit_m = ctx->unit_m.as<uint32_t>();
