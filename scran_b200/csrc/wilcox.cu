@@ -271,33 +271,8 @@ __device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap, int segc
     return s;
 }
 
-// Element e of a unit's list: (key, label | role). Dropped (stored zero) entries get key ~0.
-__device__ inline void unit_element(const double* __restrict__ vals, int64_t vbase, uint32_t n, const uint32_t* segb,
-                                    int G, double shift, uint32_t e, uint64_t& key, uint32_t& lab, bool& keep) {
-    const uint32_t per_role = n + 1;
-    const bool role = e >= per_role;
-    const uint32_t k = role ? e - per_role : e;
-    double v = 0.0;
-    lab = (uint32_t)G;
-    keep = true;
-    if (k < n) {
-        v = vals[vbase + k];
-        keep = v != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
-        int lo = 0, hi = G;  // label = last boundary <= k
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (segb[mid] <= k) lo = mid; else hi = mid;
-        }
-        lab = (uint32_t)lo;
-    }
-    if (role) {
-        v = v - shift;
-        lab |= ROLE_L;
-    }
-    key = keep ? key_of(v) : ~0ull;
-}
-
-// Key of element e without its label (enough for the bucket counts).
+// Key of element e of a unit's list, without its label (enough for the bucket counts). Dropped
+// (stored zero) entries get key ~0.
 __device__ inline void unit_key(const double* __restrict__ vals, int64_t vbase, uint32_t n, double shift, uint32_t e,
                                 uint64_t& key, bool& keep) {
     const uint32_t per_role = n + 1;
@@ -319,9 +294,9 @@ __device__ inline void unit_key(const double* __restrict__ vals, int64_t vbase, 
 // the range (the probes) clamp to the ends; dropped entries go to the last bucket, where their
 // all-ones key sorts them last.
 __device__ __forceinline__ unsigned value_bucket(uint64_t key, bool keep, double fmin, double scale, unsigned nbuckets) {
-    if (!keep) return nbuckets - 1u;
-    const double x = (value_of(key) - fmin) * scale;
-    return x >= (double)(nbuckets - 1u) ? nbuckets - 1u : (x > 0.0 ? (unsigned)x : 0u);
+    // the conversion saturates: below the range (and NaN) -> 0, far above -> 2^32 - 1
+    const unsigned b = __double2uint_rz((value_of(key) - fmin) * scale);
+    return keep ? min(b, nbuckets - 1u) : nbuckets - 1u;
 }
 
 // Segment of compact element / bucket index p: last s with off[s] <= p.
@@ -392,20 +367,65 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool two_roles = P.ut.mult == 2;
     uint16_t* bh = reinterpret_cast<uint16_t*>(S.bk);
-    auto fetch = [&](uint32_t e, bool want_label, uint64_t& key, uint32_t& lab, bool& keep, int& s) {
-        s = find_segment(S.off, nb, e);
-        const uint32_t el = e - S.off[s];
-        if (SCRATCH) {
-            key = gk[S.src[s] + el];
-            lab = want_label ? (gp[S.src[s] + el] & 0xffffu) : 0u;
-            keep = key != ~0ull;
-        } else if (want_label) {
-            unit_element(P.vals, S.vbase[s], S.n[s], S.seg + S.segptr[s], (int)(S.segptr[s + 1] - S.segptr[s]) - 1, P.shift,
-                         el, key, lab, keep);
-        } else {
-            lab = 0u;
-            unit_key(P.vals, S.vbase[s], S.n[s], P.shift, el, key, keep);
+    // Every warp owns a contiguous chunk of the job's elements and steps through it 32 at a time, so
+    // the segment of an element, and inside a unit its group label, only ever move forward: a cursor
+    // that advances replaces the binary searches.
+    const uint32_t nwarps = blockDim.x / 32;
+    const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
+    const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
+    struct Cursor {
+        int s;
+        uint32_t lab;
+        bool role;
+    };
+    auto start_cursor = [&](uint32_t e) {
+        Cursor c;
+        c.s = e < total ? find_segment(S.off, nb, e) : 0;
+        c.lab = 0;
+        c.role = false;
+        return c;
+    };
+    // element e >= the cursor's last element: its segment, (key, label) and whether it is a stored zero
+    auto fetch = [&](Cursor& c, uint32_t e, bool want_label, uint64_t& key, uint32_t& lab, bool& keep) {
+        while (e >= S.off[c.s + 1]) {
+            ++c.s;
+            c.lab = 0;
+            c.role = false;
         }
+        const uint32_t el = e - S.off[c.s];
+        if (SCRATCH) {
+            key = gk[S.src[c.s] + el];
+            lab = want_label ? (gp[S.src[c.s] + el] & 0xffffu) : 0u;
+            keep = key != ~0ull;
+            return;
+        }
+        const uint32_t n = S.n[c.s];
+        const bool role = el > n;
+        const uint32_t k = role ? el - (n + 1u) : el;
+        double v = 0.0;
+        keep = true;
+        lab = 0u;
+        if (k < n) {
+            v = P.vals[S.vbase[c.s] + k];
+            keep = v != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
+        }
+        if (want_label) {
+            const uint32_t* segb = S.seg + S.segptr[c.s];
+            const uint32_t G = S.segptr[c.s + 1] - S.segptr[c.s] - 1u;
+            if (role != c.role) {
+                c.role = role;
+                c.lab = 0;
+            }
+            if (k < n) {
+                while (c.lab + 1u < G && segb[c.lab + 1u] <= k) ++c.lab;  // label = last boundary <= k
+                lab = c.lab;
+            } else {
+                lab = G;  // the probe
+            }
+            if (role) lab |= ROLE_L;
+        }
+        if (role) v = v - P.shift;
+        key = keep ? key_of(v) : ~0ull;
     };
     auto bucket_of = [&](uint64_t key, bool keep, int s) {
         return S.off[s] + value_bucket(key, keep, S.fmin[s], S.scale[s], S.off[s + 1] - S.off[s]);
@@ -415,26 +435,29 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     for (uint32_t i = tid; i < ((total + 1) >> 1); i += blockDim.x) S.bk[i] = 0;
     if (tid == 0) S.misc[5] = 0;
     __syncthreads();
-    for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {  // four loads in flight per thread
-        uint64_t key[4];
-        uint32_t lab;
-        bool keep[4], valid[4];
-        int s[4];
+    {
+        Cursor c = start_cursor(c_lo + lane);
+        for (uint32_t t = c_lo + lane; t < c_hi; t += 128) {  // four loads in flight per thread
+            uint64_t key[4];
+            uint32_t lab;
+            bool keep[4], valid[4];
+            int s[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const uint32_t e = t + q * blockDim.x;
-            valid[q] = e < total;
-            key[q] = 0;
-            keep[q] = false;
-            s[q] = 0;
-            if (valid[q]) fetch(e, false, key[q], lab, keep[q], s[q]);
-        }
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t e = t + q * 32;
+                valid[q] = e < c_hi;
+                key[q] = 0;
+                keep[q] = false;
+                if (valid[q]) fetch(c, e, false, key[q], lab, keep[q]);
+                s[q] = c.s;
+            }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            if (valid[q]) {
-                const uint32_t b = bucket_of(key[q], keep[q], s[q]);
-                atomicAdd(&S.bk[b >> 1], 1u << ((b & 1u) * 16u));
-                if (!SCRATCH && !keep[q]) atomicAdd(&S.drop[s[q]], 1u);
+            for (int q = 0; q < 4; ++q) {
+                if (valid[q]) {
+                    const uint32_t b = bucket_of(key[q], keep[q], s[q]);
+                    atomicAdd(&S.bk[b >> 1], 1u << ((b & 1u) * 16u));
+                    if (!SCRATCH && !keep[q]) atomicAdd(&S.drop[s[q]], 1u);
+                }
             }
         }
     }
@@ -475,67 +498,73 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     __syncthreads();
 
     // ---- scatter into bucket order: afterwards bh[b] is the END of bucket b ----
-    for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {
-        uint64_t key[4];
-        uint32_t lab[4];
-        bool keep[4], valid[4];
-        int s[4];
+    {
+        Cursor c = start_cursor(c_lo + lane);
+        for (uint32_t t = c_lo + lane; t < c_hi; t += 128) {
+            uint64_t key[4];
+            uint32_t lab[4];
+            bool keep[4], valid[4];
+            int s[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const uint32_t e = t + q * blockDim.x;
-            valid[q] = e < total;
-            key[q] = 0;
-            lab[q] = 0;
-            keep[q] = false;
-            s[q] = 0;
-            if (valid[q]) fetch(e, true, key[q], lab[q], keep[q], s[q]);
-        }
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t e = t + q * 32;
+                valid[q] = e < c_hi;
+                key[q] = 0;
+                lab[q] = 0;
+                keep[q] = false;
+                if (valid[q]) fetch(c, e, true, key[q], lab[q], keep[q]);
+                s[q] = c.s;
+            }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            if (valid[q]) {
-                const uint32_t b = bucket_of(key[q], keep[q], s[q]);
-                const uint32_t sh = (b & 1u) * 16u;
-                const uint32_t pos = (atomicAdd(&S.bk[b >> 1], 1u << sh) >> sh) & 0xffffu;
-                S.key[pos] = key[q];
-                S.lab[pos] = (uint16_t)lab[q];
+            for (int q = 0; q < 4; ++q) {
+                if (valid[q]) {
+                    const uint32_t b = bucket_of(key[q], keep[q], s[q]);
+                    const uint32_t sh = (b & 1u) * 16u;
+                    const uint32_t pos = (atomicAdd(&S.bk[b >> 1], 1u << sh) >> sh) & 0xffffu;
+                    S.key[pos] = key[q];
+                    S.lab[pos] = (uint16_t)lab[q];
+                }
             }
         }
     }
     __syncthreads();
 
     // ---- small buckets: rank by counting, one thread per element ----
-    for (uint32_t p = tid; p < total; p += blockDim.x) {
-        const uint64_t key = S.key[p];
-        const int s = find_segment(S.off, nb, p);
-        const uint32_t b = bucket_of(key, key != ~0ull, s);
-        const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
-        if (end - start > (uint32_t)BUCKET_RANK_MAX) continue;
-        const uint32_t lp = S.lab[p];
-        uint32_t rank = 0;
-        bool tie = false;
-        if (end - start > 1) {
-            if (two_roles) {
-                for (uint32_t j = start; j < end; ++j) {
-                    const uint64_t kj = S.key[j];
-                    const uint32_t lj = S.lab[j];
-                    const bool eq = kj == key;
-                    const bool before = kj < key || (eq && ((lj & ROLE_L) < (lp & ROLE_L) || ((lj & ROLE_L) == (lp & ROLE_L) && j < p)));
-                    rank += before ? 1u : 0u;
-                    tie |= eq && before;
-                }
-            } else {
-                for (uint32_t j = start; j < end; ++j) {
-                    const uint64_t kj = S.key[j];
-                    const bool eq = kj == key;
-                    const bool before = kj < key || (eq && j < p);
-                    rank += before ? 1u : 0u;
-                    tie |= eq && before;
+    {
+        int s = c_lo + lane < total ? find_segment(S.off, nb, c_lo + lane) : 0;
+        for (uint32_t p = c_lo + lane; p < c_hi; p += 32) {
+            while (p >= S.off[s + 1]) ++s;
+            const uint64_t key = S.key[p];
+            const uint32_t b = bucket_of(key, key != ~0ull, s);
+            const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
+            if (end - start > (uint32_t)BUCKET_RANK_MAX) continue;
+            const uint32_t lp = S.lab[p];
+            uint32_t rank = 0;
+            bool tie = false;
+            if (end - start > 1) {
+                if (two_roles) {
+                    for (uint32_t j = start; j < end; ++j) {
+                        const uint64_t kj = S.key[j];
+                        const uint32_t lj = S.lab[j];
+                        const bool eq = kj == key;
+                        const bool before = kj < key || (eq && ((lj & ROLE_L) < (lp & ROLE_L) || ((lj & ROLE_L) == (lp & ROLE_L) && j < p)));
+                        rank += before ? 1u : 0u;
+                        tie |= eq && before;
+                    }
+                } else {
+                    for (uint32_t j = start; j < end; ++j) {
+                        const uint64_t kj = S.key[j];
+                        const bool eq = kj == key;
+                        const bool before = kj < key || (eq && j < p);
+                        rank += before ? 1u : 0u;
+                        tie |= eq && before;
+                    }
                 }
             }
+            const uint32_t q = start + rank - S.off[s];
+            const uint32_t lim = SCRATCH ? S.limit[s] : (S.off[s + 1] - S.off[s]) - S.drop[s];
+            if (q < lim) P.stream[S.soff[s] + q] = (uint16_t)((lp & 0x7fffu) | (tie ? TIE_BIT : 0u));
         }
-        const uint32_t q = start + rank - S.off[s];
-        const uint32_t lim = SCRATCH ? S.limit[s] : (S.off[s + 1] - S.off[s]) - S.drop[s];
-        if (q < lim) P.stream[S.soff[s] + q] = (uint16_t)((lp & 0x7fffu) | (tie ? TIE_BIT : 0u));
     }
 
     // ---- large buckets: one warp each ----
@@ -773,26 +802,54 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 if (lane == 31) S.boff[256] = at;
             }
             __syncthreads();
-            for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {
-                uint64_t key[4];
-                uint32_t lab[4];
-                bool keep[4], valid[4];
+            {  // warp chunks, so that the group label of a lane's elements only moves forward
+                const uint32_t nwarps = blockDim.x / 32;
+                const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
+                const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
+                uint32_t cur_lab = 0;
+                bool cur_role = false;
+                for (uint32_t t = c_lo + lane; t < c_hi; t += 128) {
+                    uint64_t key[4];
+                    uint32_t lab[4];
+                    bool keep[4], valid[4];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const uint32_t e = t + q * blockDim.x;
-                    valid[q] = e < total;
-                    key[q] = 0;
-                    lab[q] = 0;
-                    keep[q] = false;
-                    if (valid[q]) unit_element(P.vals, vbase, n, S.seg, G, P.shift, e, key[q], lab[q], keep[q]);
-                }
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t e = t + q * 32;
+                        valid[q] = e < c_hi;
+                        key[q] = 0;
+                        lab[q] = 0;
+                        keep[q] = false;
+                        if (valid[q]) {
+                            const bool role = e > n;
+                            const uint32_t k = role ? e - (n + 1u) : e;
+                            if (role != cur_role) {
+                                cur_role = role;
+                                cur_lab = 0;
+                            }
+                            double v = 0.0;
+                            keep[q] = true;
+                            lab[q] = (uint32_t)G;
+                            if (k < n) {
+                                v = P.vals[vbase + k];
+                                keep[q] = v != 0.0;
+                                while (cur_lab + 1u < (uint32_t)G && S.seg[cur_lab + 1u] <= k) ++cur_lab;
+                                lab[q] = cur_lab;
+                            }
+                            if (role) {
+                                v = v - P.shift;
+                                lab[q] |= ROLE_L;
+                            }
+                            key[q] = keep[q] ? key_of(v) : ~0ull;
+                        }
+                    }
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if (valid[q]) {
-                        const unsigned d = value_bucket(key[q], keep[q], fmin, scale, 256u);
-                        const uint32_t dst = atomicAdd(&S.gcur[d], 1u);
-                        ga[dst] = key[q];
-                        gp[dst] = lab[q];
+                    for (int q = 0; q < 4; ++q) {
+                        if (valid[q]) {
+                            const unsigned d = value_bucket(key[q], keep[q], fmin, scale, 256u);
+                            const uint32_t dst = atomicAdd(&S.gcur[d], 1u);
+                            ga[dst] = key[q];
+                            gp[dst] = lab[q];
+                        }
                     }
                 }
             }
