@@ -222,14 +222,12 @@ struct SortSmem {
     uint32_t* off;       // MAXB + 1: compact element offset of each segment of the job
     uint32_t* drop;      // MAXB: stored zeros of the segment (they are not part of the stream)
     uint32_t* n;         // MAXB
-    uint32_t* src;       // MAXB: scratch segments: where the segment starts in the unit's scratch
-    uint32_t* limit;     // MAXB: scratch segments: entries of the segment that belong to the stream
     int64_t* vbase;      // MAXB
     int64_t* soff;       // MAXB: stream position of the segment's first entry
     double* fmin;        // MAXB: value range of the segment -> bucket = (v - fmin) * scale
     double* scale;       // MAXB
     uint32_t* boff;      // 258: bucket offsets of the value partition
-    unsigned long long *bmin, *bmax;  // 256 each: smallest / largest key of every bucket
+    unsigned long long* bmin;  // 2: smallest / largest key of a bucket that takes the radix fallback
     uint32_t* gcur;      // 256: write cursor of every bucket in global scratch
     uint32_t* biglist;   // cap / BUCKET_RANK_MAX + 2: buckets too large for all-pairs ranking
     uint32_t* scan;      // 40: block scan exchange
@@ -239,7 +237,7 @@ struct SortSmem {
 constexpr int BUCKET_RANK_MAX = 32;  // buckets up to this size are ranked by all-pairs counting
 
 constexpr size_t sort_fixed_bytes(int cap, int segcap) {
-    return (size_t)(segcap + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 4 + (size_t)MAXB * 8 * 4 + 512 * 8 +
+    return (size_t)(segcap + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 2 + (size_t)MAXB * 8 * 4 + 2 * 8 +
            258 * 4 + 256 * 4 + (size_t)(cap / BUCKET_RANK_MAX + 2) * 4 + 40 * 4 + 16 * 4 + 128;
 }
 
@@ -255,15 +253,12 @@ __device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap, int segc
     s.fmin = reinterpret_cast<double*>(s.soff + MAXB);
     s.scale = s.fmin + MAXB;
     s.bmin = reinterpret_cast<unsigned long long*>(s.scale + MAXB);
-    s.bmax = s.bmin + 256;
-    s.seg = reinterpret_cast<uint32_t*>(s.bmax + 256);
+    s.seg = reinterpret_cast<uint32_t*>(s.bmin + 2);
     s.segptr = s.seg + (segcap + MAXB + 8);
     s.off = s.segptr + (MAXB + 1);
     s.drop = s.off + (MAXB + 1);
     s.n = s.drop + MAXB;
-    s.src = s.n + MAXB;
-    s.limit = s.src + MAXB;
-    s.boff = s.limit + MAXB;
+    s.boff = s.n + MAXB;
     s.gcur = s.boff + 258;
     s.biglist = s.gcur + 256;
     s.scan = s.biglist + (cap / BUCKET_RANK_MAX + 2);
@@ -360,10 +355,31 @@ __device__ inline void warp_bitonic(uint64_t* k, uint16_t* l, int sz, int lane) 
 //    are finished by one warp each: nothing to do if all keys are equal, else a bitonic sort.
 // The bucket index space is the element index space: bucket off[s] + b of segment s.
 // SCRATCH = false: segments are whole units, elements are read from K1's values;
-// SCRATCH = true:  segments are value buckets of ONE unit that the tile split left in global memory.
+// SCRATCH = true:  one run of consecutive coarse buckets of ONE large unit, which the split left in
+//                  global memory (gk, gp: the run's first element). There are no segments: the fine
+//                  bucket of a value follows from the unit-wide coarse offsets (fine_bucket()).
+struct ScratchRun {
+    uint32_t start;  // position of the run inside the unit (= its first fine bucket)
+    uint32_t lim;    // entries of the run that belong to the stream (the stored zeros at the very end do not)
+    int64_t out;     // stream position of the run's first entry
+    double fmin, scale;  // the unit's coarse bucket map
+};
+
+// Fine bucket of a key inside a large unit: coarse bucket d (256 of equal width over the unit's value
+// range, the same expression as the split used) is divided into as many fine buckets as it has
+// elements, so the fine buckets follow the density of the values and number exactly the unit's
+// elements: fine = boff[d] + floor(frac * count_d). Monotone in the value.
+__device__ __forceinline__ uint32_t fine_bucket(uint64_t key, const uint32_t* boff, double fmin, double scale) {
+    if (key == ~0ull) return boff[256] - 1u;  // stored zeros: the very last bucket
+    const double x = (value_of(key) - fmin) * scale;
+    const uint32_t d = min(__double2uint_rz(x), 255u);
+    const uint32_t lo = boff[d], c = boff[d + 1] - lo;
+    return lo + min(__double2uint_rz((x - (double)d) * (double)c), c - 1u);
+}
+
 template <bool SCRATCH>
 __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, uint32_t total, const uint64_t* gk,
-                                const uint32_t* gp) {
+                                const uint32_t* gp, const ScratchRun run) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool two_roles = P.ut.mult == 2;
     uint16_t* bh = reinterpret_cast<uint16_t*>(S.bk);
@@ -380,54 +396,55 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     };
     auto start_cursor = [&](uint32_t e) {
         Cursor c;
-        c.s = e < total ? find_segment(S.off, nb, e) : 0;
+        c.s = !SCRATCH && e < total ? find_segment(S.off, nb, e) : 0;
         c.lab = 0;
         c.role = false;
         return c;
     };
     // element e >= the cursor's last element: its segment, (key, label) and whether it is a stored zero
     auto fetch = [&](Cursor& c, uint32_t e, bool want_label, uint64_t& key, uint32_t& lab, bool& keep) {
-        while (e >= S.off[c.s + 1]) {
-            ++c.s;
-            c.lab = 0;
-            c.role = false;
-        }
-        const uint32_t el = e - S.off[c.s];
-        if (SCRATCH) {
-            key = gk[S.src[c.s] + el];
-            lab = want_label ? (gp[S.src[c.s] + el] & 0xffffu) : 0u;
+        if constexpr (SCRATCH) {
+            key = gk[e];
+            lab = want_label ? (gp[e] & 0xffffu) : 0u;
             keep = key != ~0ull;
-            return;
-        }
-        const uint32_t n = S.n[c.s];
-        const bool role = el > n;
-        const uint32_t k = role ? el - (n + 1u) : el;
-        double v = 0.0;
-        keep = true;
-        lab = 0u;
-        if (k < n) {
-            v = P.vals[S.vbase[c.s] + k];
-            keep = v != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
-        }
-        if (want_label) {
-            const uint32_t* segb = S.seg + S.segptr[c.s];
-            const uint32_t G = S.segptr[c.s + 1] - S.segptr[c.s] - 1u;
-            if (role != c.role) {
-                c.role = role;
+        } else {
+            while (e >= S.off[c.s + 1]) {
+                ++c.s;
                 c.lab = 0;
+                c.role = false;
             }
+            const uint32_t el = e - S.off[c.s];
+            const uint32_t n = S.n[c.s];
+            const bool role = el > n;
+            const uint32_t k = role ? el - (n + 1u) : el;
+            double v = 0.0;
+            keep = true;
+            lab = 0u;
             if (k < n) {
-                while (c.lab + 1u < G && segb[c.lab + 1u] <= k) ++c.lab;  // label = last boundary <= k
-                lab = c.lab;
-            } else {
-                lab = G;  // the probe
+                v = P.vals[S.vbase[c.s] + k];
+                keep = v != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
             }
-            if (role) lab |= ROLE_L;
+            if (want_label) {
+                const uint32_t* segb = S.seg + S.segptr[c.s];
+                const uint32_t G = S.segptr[c.s + 1] - S.segptr[c.s] - 1u;
+                if (role != c.role) {
+                    c.role = role;
+                    c.lab = 0;
+                }
+                if (k < n) {
+                    while (c.lab + 1u < G && segb[c.lab + 1u] <= k) ++c.lab;  // label = last boundary <= k
+                    lab = c.lab;
+                } else {
+                    lab = G;  // the probe
+                }
+                if (role) lab |= ROLE_L;
+            }
+            if (role) v = v - P.shift;
+            key = keep ? key_of(v) : ~0ull;
         }
-        if (role) v = v - P.shift;
-        key = keep ? key_of(v) : ~0ull;
     };
     auto bucket_of = [&](uint64_t key, bool keep, int s) {
+        if (SCRATCH) return fine_bucket(key, S.boff, run.fmin, run.scale) - run.start;
         return S.off[s] + value_bucket(key, keep, S.fmin[s], S.scale[s], S.off[s + 1] - S.off[s]);
     };
 
@@ -531,9 +548,11 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
 
     // ---- small buckets: rank by counting, one thread per element ----
     {
-        int s = c_lo + lane < total ? find_segment(S.off, nb, c_lo + lane) : 0;
+        int s = !SCRATCH && c_lo + lane < total ? find_segment(S.off, nb, c_lo + lane) : 0;
         for (uint32_t p = c_lo + lane; p < c_hi; p += 32) {
-            while (p >= S.off[s + 1]) ++s;
+            if (!SCRATCH) {
+                while (p >= S.off[s + 1]) ++s;
+            }
             const uint64_t key = S.key[p];
             const uint32_t b = bucket_of(key, key != ~0ull, s);
             const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
@@ -561,9 +580,9 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                     }
                 }
             }
-            const uint32_t q = start + rank - S.off[s];
-            const uint32_t lim = SCRATCH ? S.limit[s] : (S.off[s + 1] - S.off[s]) - S.drop[s];
-            if (q < lim) P.stream[S.soff[s] + q] = (uint16_t)((lp & 0x7fffu) | (tie ? TIE_BIT : 0u));
+            const uint32_t q = start + rank - (SCRATCH ? 0u : S.off[s]);
+            const uint32_t lim = SCRATCH ? run.lim : (S.off[s + 1] - S.off[s]) - S.drop[s];
+            if (q < lim) P.stream[(SCRATCH ? run.out : S.soff[s]) + q] = (uint16_t)((lp & 0x7fffu) | (tie ? TIE_BIT : 0u));
         }
     }
 
@@ -573,15 +592,16 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
         const uint32_t b = S.biglist[w];
         const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
         const int sz = (int)(end - start);
-        const int s = find_segment(S.off, nb, b);
-        const uint32_t lim = SCRATCH ? S.limit[s] : (S.off[s + 1] - S.off[s]) - S.drop[s];
+        const int s = SCRATCH ? 0 : find_segment(S.off, nb, b);
+        const uint32_t lim = SCRATCH ? run.lim : (S.off[s + 1] - S.off[s]) - S.drop[s];
+        const int64_t out = SCRATCH ? run.out : S.soff[s];
         uint64_t* k = S.key + start;
         uint16_t* l = S.lab + start;
         const uint64_t k0 = k[0];
         bool same = true;
         for (int i = lane; i < sz; i += 32) same &= k[i] == k0;
         same = __all_sync(0xffffffffu, same);
-        const uint32_t base = start - S.off[s];
+        const uint32_t base = start - (SCRATCH ? 0u : S.off[s]);
         if (same && two_roles) {
             // one value in both roles: R-role entries first, each role in the order found
             uint32_t n_r = 0;
@@ -597,7 +617,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                 const unsigned below = (1u << lane) - 1u;
                 if (valid) {
                     const uint32_t q = is_l ? n_r + seen_l + __popc(ml & below) : seen_r + __popc(mr & below);
-                    if (base + q < lim) P.stream[S.soff[s] + base + q] = (uint16_t)((lab & 0x7fffu) | (q > 0 ? TIE_BIT : 0u));
+                    if (base + q < lim) P.stream[out + base + q] = (uint16_t)((lab & 0x7fffu) | (q > 0 ? TIE_BIT : 0u));
                 }
                 seen_l += __popc(ml);
                 seen_r += __popc(mr);
@@ -608,7 +628,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
         for (int i = lane; i < sz; i += 32) {
             if (base + i < lim) {
                 const bool tie = i > 0 && k[i] == k[i - 1];
-                P.stream[S.soff[s] + base + i] = (uint16_t)(((uint32_t)l[i] & 0x7fffu) | (tie ? TIE_BIT : 0u));
+                P.stream[out + base + i] = (uint16_t)(((uint32_t)l[i] & 0x7fffu) | (tie ? TIE_BIT : 0u));
             }
         }
     }
@@ -720,7 +740,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 
         if (total <= (uint32_t)P.cap) {
             // ---- shared-memory path: all units of the job at once -----------------------------
-            bucket_sort_job<false>(P, S, nb, total, nullptr, nullptr);
+            bucket_sort_job<false>(P, S, nb, total, nullptr, nullptr, ScratchRun());
             if (tid < nb) P.unit_m[t0 + tid] = (S.off[tid + 1] - S.off[tid]) - S.drop[tid];
             continue;
         }
@@ -745,11 +765,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         // its bucket's region (the order inside a bucket is free; each region is filled front to back
         // within microseconds, so L2 collects the 12-byte writes into whole lines)
         {
-            for (int i = tid; i < 256; i += blockDim.x) {
-                S.gcur[i] = 0;
-                S.bmin[i] = ~0ull;
-                S.bmax[i] = 0ull;
-            }
+            for (int i = tid; i < 256; i += blockDim.x) S.gcur[i] = 0;
             __syncthreads();
             uint32_t ndrop = 0;
             for (uint32_t t = tid; t < total; t += 4 * blockDim.x) {  // four loads in flight per thread
@@ -768,10 +784,6 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                     if (valid[q]) {
                         const unsigned d = value_bucket(key[q], keep[q], fmin, scale, 256u);
                         atomicAdd(&S.gcur[d], 1u);
-                        if (keep[q]) {  // key range of every bucket: its own value range in pass 2
-                            atomicMin(&S.bmin[d], (unsigned long long)key[q]);
-                            atomicMax(&S.bmax[d], (unsigned long long)key[q]);
-                        }
                         ndrop += keep[q] ? 0u : 1u;
                     }
                 }
@@ -872,36 +884,47 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
             const uint32_t start = S.boff[d0];
             const int d1 = (int)S.misc[1];
             const uint32_t cnt = S.boff[d1] - start;
-            const int dfirst = d0;
             d0 = d1;
             if (cnt == 0) continue;
             if (cnt <= (uint32_t)P.cap) {
-                const int nrun = d1 - dfirst;
-                if (tid < nrun) {
-                    const int d = dfirst + tid;
-                    const uint32_t c = S.boff[d + 1] - S.boff[d];
-                    const bool has = S.bmax[d] >= S.bmin[d];
-                    const double lo_v = has ? value_of(S.bmin[d]) : 0.0, hi_v = has ? value_of(S.bmax[d]) : 0.0;
-                    S.off[tid] = S.boff[d] - start;
-                    S.src[tid] = S.boff[d];
-                    S.soff[tid] = soff + S.boff[d];
-                    S.limit[tid] = d == 255 ? c - ndropped : c;
-                    S.fmin[tid] = lo_v;
-                    S.scale[tid] = hi_v > lo_v ? (double)c / (hi_v - lo_v) : 0.0;
-                }
-                if (tid == 0) S.off[nrun] = cnt;
-                __syncthreads();
-                bucket_sort_job<true>(P, S, nrun, cnt, ga, gp);
+                ScratchRun run;
+                run.start = start;
+                run.lim = m > start ? min(cnt, m - start) : 0u;
+                run.out = soff + start;
+                run.fmin = fmin;
+                run.scale = scale;
+                bucket_sort_job<true>(P, S, 1, cnt, ga + start, gp + start, run);
                 continue;
             }
-            // a single bucket larger than shared memory (e.g. one heavily tied value): radix sort in
-            // global memory, skipping the digits above the highest bit in which the smallest and the
+            // a single coarse bucket larger than shared memory (e.g. one heavily tied value): radix sort
+            // in global memory, skipping the digits above the highest bit in which the smallest and the
             // largest key differ (dropped entries, whose key is not a value, switch that off)
+            if (tid < 2) S.bmin[tid] = tid == 0 ? ~0ull : 0ull;
+            __syncthreads();
+            {
+                unsigned long long lo_k = ~0ull, hi_k = 0ull;
+                for (uint32_t j = tid; j < cnt; j += blockDim.x) {
+                    const unsigned long long k = ga[start + j];
+                    lo_k = k < lo_k ? k : lo_k;
+                    hi_k = k > hi_k ? k : hi_k;
+                }
+                for (int o = 16; o > 0; o >>= 1) {
+                    const unsigned long long a = __shfl_xor_sync(0xffffffffu, lo_k, o), b = __shfl_xor_sync(0xffffffffu, hi_k, o);
+                    lo_k = a < lo_k ? a : lo_k;
+                    hi_k = b > hi_k ? b : hi_k;
+                }
+                if (lane == 0) {
+                    atomicMin(&S.bmin[0], lo_k);
+                    atomicMax(&S.bmin[1], hi_k);
+                }
+            }
+            __syncthreads();
             int top_bit = 64;
             {
-                const unsigned long long lo_k = S.bmin[dfirst], hi_k = S.bmax[dfirst];
-                if (hi_k >= lo_k && !(d1 == 256 && ndropped > 0)) top_bit = lo_k == hi_k ? 0 : 64 - __clzll((long long)(lo_k ^ hi_k));
+                const unsigned long long lo_k = S.bmin[0], hi_k = S.bmin[1];
+                if (hi_k != ~0ull) top_bit = lo_k == hi_k ? 0 : 64 - __clzll((long long)(lo_k ^ hi_k));
             }
+            __syncthreads();
             const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist, top_bit, 0ull);
             const uint64_t* rk = cur ? gb + start : ga + start;
             const uint32_t* rp = cur ? gq + start : gp + start;

@@ -1,6 +1,6 @@
 import csv, sys, subprocess
 rep, kern = sys.argv[1], sys.argv[2]
-out = subprocess.run(["ncu","-i",rep,"--page","source","--print-source","cuda,sass","--csv","--kernel-name","regex:"+kern],capture_output=True,text=True).stdout
+out = subprocess.run(["ncu","-i",rep,"--page","source","--print-source","cuda,sass","--csv"],capture_output=True,text=True).stdout
 rows=list(csv.reader(out.splitlines()))
 hdr=None; fname=None; agg={}
 for r in rows:
