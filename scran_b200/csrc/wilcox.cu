@@ -383,101 +383,94 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool two_roles = P.ut.mult == 2;
     uint16_t* bh = reinterpret_cast<uint16_t*>(S.bk);
-    // Every warp owns a contiguous chunk of the job's elements and steps through it 32 at a time, so
-    // the segment of an element, and inside a unit its group label, only ever move forward: a cursor
-    // that advances replaces the binary searches.
+    // Every warp owns a contiguous chunk of the job's elements and goes through it unit by unit, 32
+    // elements a step: what belongs to the unit (offsets, value range, group boundaries) is loaded
+    // once and is the same for all lanes, and the group label of a lane's elements only ever moves
+    // forward, so a cursor replaces the binary search.
     const uint32_t nwarps = blockDim.x / 32;
     const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
     const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
-    struct Cursor {
-        int s;
-        uint32_t lab;
-        bool role;
-    };
-    auto start_cursor = [&](uint32_t e) {
-        Cursor c;
-        c.s = !SCRATCH && e < total ? find_segment(S.off, nb, e) : 0;
-        c.lab = 0;
-        c.role = false;
-        return c;
-    };
-    // element e >= the cursor's last element: its segment, (key, label) and whether it is a stored zero
-    auto fetch = [&](Cursor& c, uint32_t e, bool want_label, uint64_t& key, uint32_t& lab, bool& keep) {
+
+    // body(key, label | role, keep, bucket, segment) for every element of the warp's chunk
+    auto for_each_element = [&](bool want_label, auto&& body) {
         if constexpr (SCRATCH) {
-            key = gk[e];
-            lab = want_label ? (gp[e] & 0xffffu) : 0u;
-            keep = key != ~0ull;
+            for (uint32_t t = c_lo + lane; t < c_hi; t += 128) {  // four loads in flight per thread
+                uint64_t key[4];
+                uint32_t lab[4];
+                bool valid[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t e = t + q * 32;
+                    valid[q] = e < c_hi;
+                    key[q] = valid[q] ? gk[e] : 0ull;
+                    lab[q] = valid[q] && want_label ? (gp[e] & 0xffffu) : 0u;
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (valid[q]) body(key[q], lab[q], key[q] != ~0ull, fine_bucket(key[q], S.boff, run.fmin, run.scale) - run.start, 0);
+            }
         } else {
-            while (e >= S.off[c.s + 1]) {
-                ++c.s;
-                c.lab = 0;
-                c.role = false;
-            }
-            const uint32_t el = e - S.off[c.s];
-            const uint32_t n = S.n[c.s];
-            const bool role = el > n;
-            const uint32_t k = role ? el - (n + 1u) : el;
-            double v = 0.0;
-            keep = true;
-            lab = 0u;
-            if (k < n) {
-                v = P.vals[S.vbase[c.s] + k];
-                keep = v != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
-            }
-            if (want_label) {
-                const uint32_t* segb = S.seg + S.segptr[c.s];
-                const uint32_t G = S.segptr[c.s + 1] - S.segptr[c.s] - 1u;
-                if (role != c.role) {
-                    c.role = role;
-                    c.lab = 0;
+            if (c_lo >= c_hi) return;
+            int s = find_segment(S.off, nb, c_lo);
+            uint32_t pos = c_lo;
+            while (pos < c_hi) {
+                while (pos >= S.off[s + 1]) ++s;
+                const uint32_t off_lo = S.off[s], off_hi = S.off[s + 1], cnt = off_hi - off_lo;
+                const uint32_t n = S.n[s];
+                const double* vals = P.vals + S.vbase[s];
+                const uint32_t* segb = S.seg + S.segptr[s];
+                const uint32_t G = S.segptr[s + 1] - S.segptr[s] - 1u;
+                const double fmin = S.fmin[s], scale = S.scale[s];
+                const uint32_t el_lo = pos - off_lo, el_hi = min(c_hi, off_hi) - off_lo;
+                for (int role = 0; role < (two_roles ? 2 : 1); ++role) {
+                    // this role's part of the unit's list: n values, then the probe
+                    const uint32_t base = role ? n + 1u : 0u;
+                    const uint32_t part_lo = max(el_lo, base), part_hi = min(el_hi, base + n + 1u);
+                    if (part_lo >= part_hi) continue;
+                    const uint32_t k_lo = part_lo - base, k_hi = min(part_hi - base, n);
+                    const uint32_t rolebit = role ? ROLE_L : 0u;
+                    uint32_t lab = 0;
+                    for (uint32_t k = k_lo + lane; k < k_hi; k += 128) {  // four loads in flight per thread
+                        double v[4];
+                        bool ok[4];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            ok[q] = k + 32 * q < k_hi;
+                            v[q] = ok[q] ? vals[k + 32 * q] : 1.0;
+                        }
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            if (ok[q]) {
+                                const uint32_t kk = k + 32 * q;
+                                const bool keep = v[q] != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
+                                if (want_label) {
+                                    while (lab + 1u < G && segb[lab + 1u] <= kk) ++lab;  // label = last boundary <= kk
+                                }
+                                const double vv = role ? v[q] - P.shift : v[q];
+                                const uint64_t key = keep ? key_of(vv) : ~0ull;
+                                body(key, lab | rolebit, keep, off_lo + value_bucket(key, keep, fmin, scale, cnt), s);
+                            }
+                        }
+                    }
+                    if (part_hi - base == n + 1u && lane == 0) {  // the probe: 0, or 0 - lfc in the L role
+                        const double vv = role ? 0.0 - P.shift : 0.0;
+                        const uint64_t key = key_of(vv);
+                        body(key, G | rolebit, true, off_lo + value_bucket(key, true, fmin, scale, cnt), s);
+                    }
                 }
-                if (k < n) {
-                    while (c.lab + 1u < G && segb[c.lab + 1u] <= k) ++c.lab;  // label = last boundary <= k
-                    lab = c.lab;
-                } else {
-                    lab = G;  // the probe
-                }
-                if (role) lab |= ROLE_L;
+                pos = off_lo + el_hi;
             }
-            if (role) v = v - P.shift;
-            key = keep ? key_of(v) : ~0ull;
         }
-    };
-    auto bucket_of = [&](uint64_t key, bool keep, int s) {
-        if (SCRATCH) return fine_bucket(key, S.boff, run.fmin, run.scale) - run.start;
-        return S.off[s] + value_bucket(key, keep, S.fmin[s], S.scale[s], S.off[s + 1] - S.off[s]);
     };
 
     // ---- counts ----
     for (uint32_t i = tid; i < ((total + 1) >> 1); i += blockDim.x) S.bk[i] = 0;
     if (tid == 0) S.misc[5] = 0;
     __syncthreads();
-    {
-        Cursor c = start_cursor(c_lo + lane);
-        for (uint32_t t = c_lo + lane; t < c_hi; t += 128) {  // four loads in flight per thread
-            uint64_t key[4];
-            uint32_t lab;
-            bool keep[4], valid[4];
-            int s[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const uint32_t e = t + q * 32;
-                valid[q] = e < c_hi;
-                key[q] = 0;
-                keep[q] = false;
-                if (valid[q]) fetch(c, e, false, key[q], lab, keep[q]);
-                s[q] = c.s;
-            }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (valid[q]) {
-                    const uint32_t b = bucket_of(key[q], keep[q], s[q]);
-                    atomicAdd(&S.bk[b >> 1], 1u << ((b & 1u) * 16u));
-                    if (!SCRATCH && !keep[q]) atomicAdd(&S.drop[s[q]], 1u);
-                }
-            }
-        }
-    }
+    for_each_element(false, [&](uint64_t, uint32_t, bool keep, uint32_t b, int s) {
+        atomicAdd(&S.bk[b >> 1], 1u << ((b & 1u) * 16u));
+        if (!SCRATCH && !keep) atomicAdd(&S.drop[s], 1u);
+    });
     __syncthreads();
 
     // ---- exclusive scan of the counts (in place), large buckets noted ----
@@ -495,7 +488,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
         if (lane == 31) S.scan[warp] = incl;
         __syncthreads();
         if (warp == 0) {
-            uint32_t v = S.scan[lane];
+            uint32_t v = lane < (int)nwarps ? S.scan[lane] : 0u;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
@@ -515,74 +508,64 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     __syncthreads();
 
     // ---- scatter into bucket order: afterwards bh[b] is the END of bucket b ----
-    {
-        Cursor c = start_cursor(c_lo + lane);
-        for (uint32_t t = c_lo + lane; t < c_hi; t += 128) {
-            uint64_t key[4];
-            uint32_t lab[4];
-            bool keep[4], valid[4];
-            int s[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const uint32_t e = t + q * 32;
-                valid[q] = e < c_hi;
-                key[q] = 0;
-                lab[q] = 0;
-                keep[q] = false;
-                if (valid[q]) fetch(c, e, true, key[q], lab[q], keep[q]);
-                s[q] = c.s;
-            }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (valid[q]) {
-                    const uint32_t b = bucket_of(key[q], keep[q], s[q]);
-                    const uint32_t sh = (b & 1u) * 16u;
-                    const uint32_t pos = (atomicAdd(&S.bk[b >> 1], 1u << sh) >> sh) & 0xffffu;
-                    S.key[pos] = key[q];
-                    S.lab[pos] = (uint16_t)lab[q];
-                }
-            }
-        }
-    }
+    for_each_element(true, [&](uint64_t key, uint32_t lab, bool, uint32_t b, int) {
+        const uint32_t sh = (b & 1u) * 16u;
+        const uint32_t pos = (atomicAdd(&S.bk[b >> 1], 1u << sh) >> sh) & 0xffffu;
+        S.key[pos] = key;
+        S.lab[pos] = (uint16_t)lab;
+    });
     __syncthreads();
 
     // ---- small buckets: rank by counting, one thread per element ----
-    {
-        int s = !SCRATCH && c_lo + lane < total ? find_segment(S.off, nb, c_lo + lane) : 0;
-        for (uint32_t p = c_lo + lane; p < c_hi; p += 32) {
-            if (!SCRATCH) {
-                while (p >= S.off[s + 1]) ++s;
-            }
-            const uint64_t key = S.key[p];
-            const uint32_t b = bucket_of(key, key != ~0ull, s);
-            const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
-            if (end - start > (uint32_t)BUCKET_RANK_MAX) continue;
-            const uint32_t lp = S.lab[p];
-            uint32_t rank = 0;
-            bool tie = false;
-            if (end - start > 1) {
-                if (two_roles) {
-                    for (uint32_t j = start; j < end; ++j) {
-                        const uint64_t kj = S.key[j];
-                        const uint32_t lj = S.lab[j];
-                        const bool eq = kj == key;
-                        const bool before = kj < key || (eq && ((lj & ROLE_L) < (lp & ROLE_L) || ((lj & ROLE_L) == (lp & ROLE_L) && j < p)));
-                        rank += before ? 1u : 0u;
-                        tie |= eq && before;
-                    }
-                } else {
-                    for (uint32_t j = start; j < end; ++j) {
-                        const uint64_t kj = S.key[j];
-                        const bool eq = kj == key;
-                        const bool before = kj < key || (eq && j < p);
-                        rank += before ? 1u : 0u;
-                        tie |= eq && before;
-                    }
+    auto rank_element = [&](uint32_t p, uint64_t key, uint32_t b, uint32_t seg_lo, uint32_t lim, int64_t out) {
+        const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
+        if (end - start > (uint32_t)BUCKET_RANK_MAX) return;
+        const uint32_t lp = S.lab[p];
+        uint32_t rank = 0;
+        bool tie = false;
+        if (end - start > 1) {
+            if (two_roles) {
+                for (uint32_t j = start; j < end; ++j) {
+                    const uint64_t kj = S.key[j];
+                    const uint32_t lj = S.lab[j];
+                    const bool eq = kj == key;
+                    const bool before = kj < key || (eq && ((lj & ROLE_L) < (lp & ROLE_L) || ((lj & ROLE_L) == (lp & ROLE_L) && j < p)));
+                    rank += before ? 1u : 0u;
+                    tie |= eq && before;
+                }
+            } else {
+                for (uint32_t j = start; j < end; ++j) {
+                    const uint64_t kj = S.key[j];
+                    const bool eq = kj == key;
+                    const bool before = kj < key || (eq && j < p);
+                    rank += before ? 1u : 0u;
+                    tie |= eq && before;
                 }
             }
-            const uint32_t q = start + rank - (SCRATCH ? 0u : S.off[s]);
-            const uint32_t lim = SCRATCH ? run.lim : (S.off[s + 1] - S.off[s]) - S.drop[s];
-            if (q < lim) P.stream[(SCRATCH ? run.out : S.soff[s]) + q] = (uint16_t)((lp & 0x7fffu) | (tie ? TIE_BIT : 0u));
+        }
+        const uint32_t q = start + rank - seg_lo;
+        if (q < lim) P.stream[out + q] = (uint16_t)((lp & 0x7fffu) | (tie ? TIE_BIT : 0u));
+    };
+    if constexpr (SCRATCH) {
+        for (uint32_t p = c_lo + lane; p < c_hi; p += 32) {
+            const uint64_t key = S.key[p];
+            rank_element(p, key, fine_bucket(key, S.boff, run.fmin, run.scale) - run.start, 0u, run.lim, run.out);
+        }
+    } else if (c_lo < c_hi) {
+        int s = find_segment(S.off, nb, c_lo);
+        uint32_t pos = c_lo;
+        while (pos < c_hi) {
+            while (pos >= S.off[s + 1]) ++s;
+            const uint32_t off_lo = S.off[s], off_hi = S.off[s + 1], cnt = off_hi - off_lo;
+            const double fmin = S.fmin[s], scale = S.scale[s];
+            const uint32_t lim = cnt - S.drop[s];
+            const int64_t out = S.soff[s];
+            const uint32_t hi = min(c_hi, off_hi);
+            for (uint32_t p = pos + lane; p < hi; p += 32) {
+                const uint64_t key = S.key[p];
+                rank_element(p, key, off_lo + value_bucket(key, key != ~0ull, fmin, scale, cnt), off_lo, lim, out);
+            }
+            pos = hi;
         }
     }
 
@@ -925,7 +908,19 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 if (hi_k != ~0ull) top_bit = lo_k == hi_k ? 0 : 64 - __clzll((long long)(lo_k ^ hi_k));
             }
             __syncthreads();
-            const int cur = block_sort_keys<uint32_t>(ga + start, gp + start, gb + start, gq + start, (int)cnt, S.whist, top_bit, 0ull);
+            // the split left the bucket in no particular order; with two roles a stable pass on the
+            // payload byte that holds the role bit comes first, so that R entries precede L entries
+            // among equal keys after the (stable) key passes
+            int cur = 0;
+            if (ut.mult == 2) cur = block_radix_sort<uint32_t, true>(ga + start, gp + start, gb + start, gq + start, (int)cnt, 8, 16, S.whist);
+            {
+                uint64_t* k0 = cur ? gb + start : ga + start;
+                uint32_t* p0 = cur ? gq + start : gp + start;
+                uint64_t* k1 = cur ? ga + start : gb + start;
+                uint32_t* p1 = cur ? gp + start : gq + start;
+                const int c2 = block_sort_keys<uint32_t>(k0, p0, k1, p1, (int)cnt, S.whist, top_bit, 0ull);
+                cur = c2 ? (cur ^ 1) : cur;
+            }
             const uint64_t* rk = cur ? gb + start : ga + start;
             const uint32_t* rp = cur ? gq + start : gp + start;
             for (uint32_t j = tid; j < cnt; j += blockDim.x) {
@@ -1523,12 +1518,17 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     // capacity of the shared-memory sort: 12 bytes per element plus the fixed tables (which hold a
     // list with one entry per BUCKET_RANK_MAX elements)
     const int segcap = std::max(2048, L.maxG + 1);  // staged segment boundaries of a job
-    int cap = (int)((ctx->smem_optin - sort_fixed_bytes(0, segcap)) * 8 / 97);
-    cap = std::min(cap, 65280) & ~63;
-    while (cap > 64 && (size_t)cap * 12 + sort_fixed_bytes(cap, segcap) > ctx->smem_optin) cap -= 64;
-    if ((size_t)cap * 12 < (size_t)SORT_HIST_WORDS * 4) throw Error("internal: shared memory too small for the sort");
-    const size_t sort_smem = (size_t)cap * 12 + sort_fixed_bytes(cap, segcap);
-    const uint32_t small_max = (uint32_t)cap / 2, window = (uint32_t)cap - small_max;
+    auto cap_for = [&](size_t budget) {
+        int c = (int)((budget - sort_fixed_bytes(0, segcap)) * 8 / 97);
+        c = std::min(c, 65280) & ~63;
+        while (c > 64 && (size_t)c * 12 + sort_fixed_bytes(c, segcap) > budget) c -= 64;
+        return c;
+    };
+    // (Two CTAs of 512 threads per SM with half the capacity each were tried for the small jobs, so
+    // that one computes while the other waits at a barrier: slower, 10.2 vs 9.7 ms at config 2.)
+    const int cap_large = cap_for(ctx->smem_optin);
+    if ((size_t)cap_large * 12 < (size_t)SORT_HIST_WORDS * 4) throw Error("internal: shared memory too small for the sort");
+    const uint32_t small_max = (uint32_t)cap_large / 2, window = (uint32_t)cap_large - small_max;
     const int maxb = std::max(1, std::min(MAXB, segcap / (L.maxG + 1)));
     SB_LAUNCH(ctx, k3_plan, 1, 1024, 0, ut, small_max, window, maxb, jobs, njobs);
     SB_LAUNCH(ctx, k3_order, 1, 1024, 0, ut, jobs, njobs, 16384u, order, nbig);
@@ -1549,14 +1549,13 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     sp.vmax = T.vmax;
     if (!T.vmin || !T.vmax) throw Error("internal: the value ranges of the segments are missing");
     sp.shift = lfc;
-    sp.cap = cap;
     sp.segcap = segcap;
     sp.maxG = L.maxG;
     sp.stream = ctx->stream_lab.as<uint16_t>();
     sp.unit_m = ctx->unit_m.as<uint32_t>();
     sp.g_ka = sp.g_kb = nullptr;
     sp.g_pa = sp.g_pb = nullptr;
-    if (max_m > cap) {  // some unit may not fit shared memory: scratch laid out like the stream
+    if (max_m > cap_large) {  // some unit may not fit shared memory: scratch laid out like the stream
         ctx->sort_keys.reserve((size_t)stream_len * 16 + 64);
         ctx->sort_labs.reserve((size_t)stream_len * 8 + 64);
         sp.g_ka = ctx->sort_keys.as<uint64_t>();
@@ -1568,10 +1567,11 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     sp.njobs = njobs;
     sp.order = order;
     sp.job_counter = counter;
-    allow_smem(k3_sort, sort_smem);
+    allow_smem(k3_sort, (size_t)cap_large * 12 + sort_fixed_bytes(cap_large, segcap));
+    sp.cap = cap_large;
     SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
-    const int sort_grid = (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count);
-    SB_LAUNCH(ctx, k3_sort, sort_grid, SORT_THREADS, sort_smem, sp);
+    SB_LAUNCH(ctx, k3_sort, (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count), SORT_THREADS,
+              (size_t)cap_large * 12 + sort_fixed_bytes(cap_large, segcap), sp);
     phase_mark(ctx, PH_SORT);
 #ifdef SB_PHASE_PROBE
     cudaStreamSynchronize(ctx->stream);

@@ -114,11 +114,16 @@ def test_overlap_large_units(sb, port_lib):
     entries (64-bit count table)."""
     rng = np.random.default_rng(77)
     ncells = 150000
-    x = np.zeros((4, ncells))
+    x = np.zeros((5, ncells))
     x[0] = np.where(rng.random(ncells) < 0.6, np.log2(1 + rng.poisson(3, ncells) + rng.random(ncells)), 0)
     x[1] = np.where(rng.random(ncells) < 0.2, rng.poisson(2, ncells), 0)          # ties, > cap
     x[2] = np.where(rng.random(ncells) < 0.03, rng.random(ncells), 0)             # fits shared memory
     x[3] = 1.0 + 1e-13 * rng.integers(0, 1000, ncells)                             # equal high words
+    # nearly everything inside one coarse value bucket (two outliers stretch the range): the radix
+    # fallback; on a grid of 2^-20 so that with lfc = 2^-10 values of the two roles coincide exactly
+    x[4] = np.where(rng.random(ncells) < 0.3, 1.0 + rng.integers(0, 4096, ncells) * 2.0 ** -20, 0)
+    x[4, 5] = 1000.0
+    x[4, 6] = 1e-3
     g = rng.integers(0, 3, ncells)
     groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(3)]
     left, right = all_pairs(3)
