@@ -13,62 +13,86 @@ namespace sb {
 
 namespace {
 
-__global__ void __launch_bounds__(256)
+// A CTA takes K2_GENES genes x 32 consecutive combinations: warp w owns gene g0 + w and its lanes
+// the 32 combinations, whose segments lie next to each other in the gene's row. The 32 streams of
+// a warp therefore stay inside one stretch of memory of 32 segments (a gene-major mapping would
+// spread them over 32 rows, hundreds of kilobytes apart: a different DRAM page and TLB entry each).
+// The results go through shared memory so that each output array is written K2_GENES consecutive
+// genes at a time.
+constexpr int K2_GENES = 8;
+
+__global__ void __launch_bounds__(K2_GENES * 32)
 k2_stats(const double* __restrict__ vals, const int64_t* __restrict__ row_ptr, const uint32_t* __restrict__ seg_off,
          int ngenes, int C, const int32_t* __restrict__ caller_of_dev, const int64_t* __restrict__ ncells_dev,
          double* __restrict__ mean, double* __restrict__ var, double* __restrict__ ndet, double* __restrict__ vmin,
          double* __restrict__ vmax) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= (int64_t)ngenes * C) return;
-    const int g = (int)(t % ngenes);
-    const int dc = (int)(t / ngenes);
-    const int64_t base = row_ptr[g];
-    const int64_t lo = base + seg_off[(size_t)dc * ngenes + g];
-    const int64_t hi = base + seg_off[(size_t)(dc + 1) * ngenes + g];
-
-    double M = 0.0, S = 0.0, nz = 0.0, det = 0.0;
-    double lo_v = __longlong_as_double(0x7ff0000000000000ll), hi_v = -lo_v;  // range of the non-zero values (for K3)
-    auto update = [&](double v) {
-        if (v != 0.0) {
-            lo_v = fmin(lo_v, v);
-            hi_v = fmax(hi_v, v);
-        }
-        nz += 1.0;
-        const double delta = v - M;
-        M += delta / nz;
-        S += delta * (v - M);
-        det += (v > 0.0) ? 1.0 : 0.0;
-    };
-    int64_t k = lo;
-    // The update chain is sequential by definition; the loads are not. Eight values are fetched
-    // ahead of the arithmetic so that every thread keeps several memory requests in flight.
-    for (; k + 8 <= hi; k += 8) {
-        double v[8];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) v[q] = vals[k + q];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) update(v[q]);
-    }
-    for (; k < hi; ++k) update(vals[k]);
-
-    const int64_t n = ncells_dev[dc];
+    __shared__ double stage[5][32][K2_GENES + 1];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int g = blockIdx.x * K2_GENES + w;
+    const int dc = blockIdx.y * 32 + lane;
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
-    if (n <= 0) M = nan;
-    if (n <= 1) {
-        S = nan;
-    } else {
-        const double total = (double)n;
-        const double ratio = nz / total;
-        S += M * M * ratio * (total - nz);
-        M *= ratio;
-        S /= (double)(n - 1);
+    if (g < ngenes && dc < C) {
+        const int64_t base = row_ptr[g];
+        const int64_t lo = base + seg_off[(size_t)dc * ngenes + g];
+        const int64_t hi = base + seg_off[(size_t)(dc + 1) * ngenes + g];
+
+        double M = 0.0, S = 0.0, nz = 0.0, det = 0.0;
+        double lo_v = __longlong_as_double(0x7ff0000000000000ll), hi_v = -lo_v;  // range of the non-zero values (for K3)
+        auto update = [&](double v) {
+            if (v != 0.0) {
+                lo_v = fmin(lo_v, v);
+                hi_v = fmax(hi_v, v);
+            }
+            nz += 1.0;
+            const double delta = v - M;
+            M += delta / nz;
+            S += delta * (v - M);
+            det += (v > 0.0) ? 1.0 : 0.0;
+        };
+        int64_t k = lo;
+        // The update chain is sequential by definition; the loads are not. Eight values are fetched
+        // ahead of the arithmetic so that every thread keeps several memory requests in flight.
+        for (; k + 8 <= hi; k += 8) {
+            double v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = vals[k + q];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) update(v[q]);
+        }
+        for (; k < hi; ++k) update(vals[k]);
+
+        const int64_t n = ncells_dev[dc];
+        if (n <= 0) M = nan;
+        if (n <= 1) {
+            S = nan;
+        } else {
+            const double total = (double)n;
+            const double ratio = nz / total;
+            S += M * M * ratio * (total - nz);
+            M *= ratio;
+            S /= (double)(n - 1);
+        }
+        stage[0][lane][w] = M;
+        stage[1][lane][w] = S;
+        stage[2][lane][w] = det;
+        stage[3][lane][w] = lo_v;
+        stage[4][lane][w] = hi_v;
     }
-    const size_t at = (size_t)caller_of_dev[dc] * ngenes + g;
-    if (mean) mean[at] = M;
-    if (var) var[at] = S;
-    if (ndet) ndet[at] = det;
-    vmin[(size_t)dc * ngenes + g] = lo_v;
-    vmax[(size_t)dc * ngenes + g] = hi_v;
+    __syncthreads();
+    const int g0 = blockIdx.x * K2_GENES;
+    for (int idx = threadIdx.x; idx < 5 * 32 * K2_GENES; idx += blockDim.x) {
+        const int arr = idx / (32 * K2_GENES), rest = idx % (32 * K2_GENES);
+        const int c = rest / K2_GENES, gi = rest % K2_GENES;
+        const int odc = blockIdx.y * 32 + c;
+        if (odc >= C || g0 + gi >= ngenes) continue;
+        const double x = stage[arr][c][gi];
+        if (arr < 3) {
+            double* out = arr == 0 ? mean : (arr == 1 ? var : ndet);
+            if (out) out[(size_t)caller_of_dev[odc] * ngenes + g0 + gi] = x;
+        } else {
+            (arr == 3 ? vmin : vmax)[(size_t)odc * ngenes + g0 + gi] = x;
+        }
+    }
 }
 
 }  // namespace
@@ -80,7 +104,8 @@ void run_stats(scranb200_ctx* ctx, Transposed& T, const PairLayout& L, double* d
     ctx->vmax.reserve((size_t)total * 8);
     T.vmin = ctx->vmin.as<double>();
     T.vmax = ctx->vmax.as<double>();
-    SB_LAUNCH(ctx, k2_stats, (unsigned)ceil_div(total, 256), 256, 0, T.vals, T.row_ptr, T.seg_off, T.ngenes, T.C,
+    const dim3 grid((unsigned)ceil_div(T.ngenes, K2_GENES), (unsigned)ceil_div(T.C, 32));
+    SB_LAUNCH(ctx, k2_stats, grid, K2_GENES * 32, 0, T.vals, T.row_ptr, T.seg_off, T.ngenes, T.C,
               L.d_caller_of_dev, L.d_ncells_dev, d_mean, d_var, d_ndet, ctx->vmin.as<double>(), ctx->vmax.as<double>());
 }
 
