@@ -73,35 +73,55 @@ __global__ void __launch_bounds__(256) k4_effects(EffParams P) {
     if (g >= P.ngenes) return;
 
     const int j0 = P.avg_ptr[q], j1 = P.avg_ptr[q + 1];
-    // Pass 1: sum of weights over the blocks where each effect is defined.
     double wsum[3] = {0.0, 0.0, 0.0};
-    for (int j = j0; j < j1; ++j) {
-        const int p = P.avg_idx[j];
-        const int l = P.left[p], r = P.right[p];
-        const double nL = P.ncells[l], nR = P.ncells[r];
-        const double w = nL * nR;
-        const size_t al = (size_t)l * P.ngenes + g, ar = (size_t)r * P.ngenes + g;
-        const double d = effect_cohen(P.mean[al], P.mean[ar], P.var[al], P.var[ar], P.lfc);
-        if (!isnan(d)) wsum[0] += w;
-        const double a = P.u[(size_t)g * P.npairs + p] / w;
-        if (!isnan(a)) wsum[1] += w;
-        const double f = effect_detected(P.ndet[al], P.ndet[ar], nL, nR);
-        if (!isnan(f)) wsum[2] += w;
-    }
-    // Pass 2: sum of (w / wsum) * effect.
     DD acc[3] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
-    for (int j = j0; j < j1; ++j) {
+    auto block_effects = [&](int j, double& w, double& d, double& a, double& f) {
         const int p = P.avg_idx[j];
         const int l = P.left[p], r = P.right[p];
         const double nL = P.ncells[l], nR = P.ncells[r];
-        const double w = nL * nR;
+        w = nL * nR;
         const size_t al = (size_t)l * P.ngenes + g, ar = (size_t)r * P.ngenes + g;
-        const double d = effect_cohen(P.mean[al], P.mean[ar], P.var[al], P.var[ar], P.lfc);
-        if (!isnan(d)) dd_add(acc[0], (w / wsum[0]) * d);
-        const double a = P.u[(size_t)g * P.npairs + p] / w;
-        if (!isnan(a)) dd_add(acc[1], (w / wsum[1]) * a);
-        const double f = effect_detected(P.ndet[al], P.ndet[ar], nL, nR);
-        if (!isnan(f)) dd_add(acc[2], (w / wsum[2]) * f);
+        d = effect_cohen(P.mean[al], P.mean[ar], P.var[al], P.var[ar], P.lfc);
+        a = P.u[(size_t)g * P.npairs + p] / w;
+        f = effect_detected(P.ndet[al], P.ndet[ar], nL, nR);
+    };
+    constexpr int KEEP = 8;  // block levels whose effects stay in registers between the two passes
+    if (j1 - j0 <= KEEP) {
+        double w[KEEP], d[KEEP], a[KEEP], f[KEEP];
+        // Pass 1: the effects, and the sum of weights over the blocks where each effect is defined.
+#pragma unroll
+        for (int jj = 0; jj < KEEP; ++jj) {
+            if (j0 + jj < j1) {
+                block_effects(j0 + jj, w[jj], d[jj], a[jj], f[jj]);
+                if (!isnan(d[jj])) wsum[0] += w[jj];
+                if (!isnan(a[jj])) wsum[1] += w[jj];
+                if (!isnan(f[jj])) wsum[2] += w[jj];
+            }
+        }
+        // Pass 2: sum of (w / wsum) * effect.
+#pragma unroll
+        for (int jj = 0; jj < KEEP; ++jj) {
+            if (j0 + jj < j1) {
+                if (!isnan(d[jj])) dd_add(acc[0], (w[jj] / wsum[0]) * d[jj]);
+                if (!isnan(a[jj])) dd_add(acc[1], (w[jj] / wsum[1]) * a[jj]);
+                if (!isnan(f[jj])) dd_add(acc[2], (w[jj] / wsum[2]) * f[jj]);
+            }
+        }
+    } else {  // many block levels: the effects are computed twice
+        for (int j = j0; j < j1; ++j) {
+            double w, d, a, f;
+            block_effects(j, w, d, a, f);
+            if (!isnan(d)) wsum[0] += w;
+            if (!isnan(a)) wsum[1] += w;
+            if (!isnan(f)) wsum[2] += w;
+        }
+        for (int j = j0; j < j1; ++j) {
+            double w, d, a, f;
+            block_effects(j, w, d, a, f);
+            if (!isnan(d)) dd_add(acc[0], (w / wsum[0]) * d);
+            if (!isnan(a)) dd_add(acc[1], (w / wsum[1]) * a);
+            if (!isnan(f)) dd_add(acc[2], (w / wsum[2]) * f);
+        }
     }
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
     for (int e = 0; e < 3; ++e) {
