@@ -76,6 +76,20 @@ int64_t scranb200_mat_nnz(const scranb200_mat* mat);
 int scranb200_blocked_stats(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* block, int nblocks,
                             double* mean_out, double* var_out, double* ndetected_out);
 
+/* ---- compute_blocked_stats_lognorm / _norm: src/compute_blocked_stats.cpp:129-185 ------------
+ * (.Call symbols _scran_compute_blocked_stats_lognorm, src/RcppExports.cpp:52-64, and
+ * _scran_compute_blocked_stats_norm, :66-77.) The same statistics after a per-cell transformation
+ * of the values: transform = 1: log(x / sf[cell] + pseudo) / M_LN2 (:136); transform = 2:
+ * x / sf[cell] (:168; pseudo ignored). sf: one size factor per cell. norm is bit-identical to the
+ * reference (IEEE division); lognorm agrees to the accuracy of the device's log (<= 1 ulp per
+ * value; tests: 1e-12 relative). With pseudo != 1 the reference leaves its sparse branch (:142);
+ * here the zeros' common value log(pseudo) / M_LN2 is subtracted before and added to the mean
+ * after, which is the same mean and variance up to rounding (tests: 1e-12 relative, and 1e-12
+ * absolute on means that cancel to ~0). */
+int scranb200_blocked_stats_transformed(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* block, int nblocks,
+                                        int transform, const double* sf, double pseudo, double* mean_out,
+                                        double* var_out);
+
 /* ---- overlap_exprs_paired: src/overlap_exprs.cpp:196-220 ------------------------------------
  * groups: the reference's list of 0-based cell-index vectors, flattened: group g owns
  * group_cells[group_ptr[g] .. group_ptr[g+1]). A cell may belong to at most one group (the

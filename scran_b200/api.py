@@ -181,6 +181,33 @@ def compute_blocked_stats_none(x, block, nblocks, want_detected=False):
     return mean.T, var.T
 
 
+def _blocked_stats_transformed(x, block, nblocks, transform, sf, pseudo):
+    m = _as_matrix(x)
+    block = np.ascontiguousarray(block, np.int32)
+    sf = np.ascontiguousarray(sf, np.float64)
+    if block.shape[0] != m.shape[1]:
+        raise ValueError("length of 'block' should be the same as 'ncol(x)'")
+    if sf.shape[0] != m.shape[1]:
+        raise ValueError("length of 'sf' should be the same as 'ncol(x)'")
+    mean = np.zeros((nblocks, m.shape[0]), np.float64)
+    var = np.zeros((nblocks, m.shape[0]), np.float64)
+    check(lib().scranb200_blocked_stats_transformed(m.ctx.handle, m.handle, ptr(block), int(nblocks), int(transform),
+                                                    ptr(sf), float(pseudo), ptr(mean), ptr(var)))
+    return mean.T, var.T
+
+
+def compute_blocked_stats_lognorm(x, block, nblocks, sf, pseudo):
+    """R: compute_blocked_stats_lognorm(mat, block, nblocks, sf, pseudo) (R/RcppExports.R:16-18):
+    mean / variance per block of log2(x / sf + pseudo)."""
+    return _blocked_stats_transformed(x, block, nblocks, 1, sf, pseudo)
+
+
+def compute_blocked_stats_norm(x, block, nblocks, sf):
+    """R: compute_blocked_stats_norm(mat, block, nblocks, sf) (R/RcppExports.R:20-22): mean /
+    variance per block of x / sf."""
+    return _blocked_stats_transformed(x, block, nblocks, 2, sf, 1.0)
+
+
 def _flatten_groups(groups):
     gptr = np.zeros(len(groups) + 1, np.int64)
     for k, g in enumerate(groups):

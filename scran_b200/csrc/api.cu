@@ -177,6 +177,28 @@ void score_stage1(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_
     phase_mark(ctx, PH_SUMMARY);
 }
 
+// The transformers of src/compute_blocked_stats.cpp:129-177 applied to the stored values: one warp per
+// column (the size factor belongs to the column). lognorm: log(x / sf + pseudo) / M_LN2 (:136), the
+// natural log followed by a division like the reference; norm: x / sf (:168). `shift` is subtracted
+// (0 unless the zeros do not stay zero, see scranb200_blocked_stats_transformed).
+__global__ void __launch_bounds__(256) transform_values(const int64_t* __restrict__ p, const double* __restrict__ x, int64_t ncol,
+                                                        const double* __restrict__ sf, int transform, double pseudo,
+                                                        double shift, double* __restrict__ y) {
+    const int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (c >= ncol) return;
+    const double target = sf[c];
+    for (int64_t k = p[c] + (threadIdx.x & 31); k < p[c + 1]; k += 32) {
+        const double v = x[k];
+        y[k] = transform == 1 ? log(v / target + pseudo) / 0.693147180559945309417232121458176568 - shift : v / target;
+    }
+}
+
+__global__ void __launch_bounds__(256) shift_means(double* mean, int64_t n, double shift) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) mean[t] += shift;  // NaN (empty block) stays NaN
+}
+
+
 }  // namespace
 }  // namespace sb
 
@@ -355,6 +377,47 @@ int scranb200_download_csc(scranb200_ctx* ctx, const scranb200_mat* mat, int64_t
         SB_CUDA(cudaMemcpyAsync(x, mat->d_x, (size_t)mat->nnz * 8, cudaMemcpyDeviceToHost, ctx->stream));
     }
     SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+int scranb200_blocked_stats_transformed(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* block, int nblocks,
+                                        int transform, const double* sf, double pseudo, double* mean_out,
+                                        double* var_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    if (transform != 1 && transform != 2) throw Error("transform must be 1 (lognorm) or 2 (norm)");
+    if (nblocks < 0) throw Error("negative number of blocks");
+    for (int64_t c = 0; c < mat->ncol; ++c) {
+        if (block[c] >= nblocks) throw Error("block id out of range");
+    }
+    // lognorm with pseudo != 1 does not keep zeros at zero (the reference then reads dense columns,
+    // src/compute_blocked_stats.cpp:69-82,142). Every zero becomes the same constant z0 =
+    // log(pseudo) / M_LN2, so the statistics are those of (value - z0), whose zeros are zeros again,
+    // with z0 added back to the mean; the variance is unchanged by the shift.
+    const double shift = transform == 1 && pseudo != 1.0 ? std::log(pseudo) / 0.693147180559945309417232121458176568 : 0.0;
+    ctx->io_a.reserve(std::max<size_t>(1, (size_t)mat->nnz) * 8);
+    ctx->io_b.reserve(std::max<size_t>(1, (size_t)mat->ncol) * 8);
+    if (mat->ncol) SB_CUDA(cudaMemcpyAsync(ctx->io_b.p, sf, (size_t)mat->ncol * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (mat->ncol) {
+        SB_LAUNCH(ctx, transform_values, (unsigned)ceil_div(mat->ncol * 32, 256), 256, 0, mat->d_p, mat->d_x, mat->ncol,
+                  ctx->io_b.as<double>(), transform, pseudo, shift, ctx->io_a.as<double>());
+    }
+    scranb200_mat view = *mat;
+    view.d_x = ctx->io_a.as<double>();
+    view.owned = false;
+    PairLayout L;
+    build_layout(block, mat->ncol, nblocks, nullptr, nullptr, 0, ctx->sm_count * 4, L);
+    upload_layout(ctx, L, ctx->layout_i32);
+    phase_begin(ctx);
+    run_pairs(ctx, &view, L, ctx->layout_i32, true, 0.0, false, false);
+    const int64_t cells = mat->nrow * (int64_t)nblocks;
+    if (cells) {
+        if (shift != 0.0) SB_LAUNCH(ctx, shift_means, (unsigned)ceil_div(cells, 256), 256, 0, ctx->mean.as<double>(), cells, shift);
+        SB_CUDA(cudaMemcpyAsync(mean_out, ctx->mean.p, (size_t)cells * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        SB_CUDA(cudaMemcpyAsync(var_out, ctx->var.p, (size_t)cells * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
     API_END
 }
 

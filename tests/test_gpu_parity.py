@@ -43,6 +43,30 @@ def test_blocked_stats_bit_exact(sb, oracle_lib, sparse):
     assert np.allclose(var[:, 1], x[:, keep].var(1, ddof=1), rtol=1e-10, atol=1e-14)
 
 
+@pytest.mark.parametrize("sparse", [True, False])
+def test_blocked_stats_norm_and_lognorm(sb, oracle_lib, sparse):
+    """compute_blocked_stats_norm / _lognorm (src/compute_blocked_stats.cpp:129-185): norm bit-exact;
+    lognorm within 1e-12 (device log), including pseudo != 1 where the reference reads dense columns."""
+    from oracle import native
+    rng = np.random.default_rng(31)
+    x = np.where(rng.random((90, 301)) < 0.3, rng.poisson(4.0, (90, 301)).astype(float), 0.0)
+    x[5] = 0.0
+    x[6] = rng.poisson(30.0, 301) + 1.0
+    block = rng.integers(0, 4, 301).astype(np.int32)
+    block[::17] = native.NA_INT
+    sf = np.exp(rng.normal(0, 0.4, 301))
+    m = as_csc(x) if sparse else x
+    mean, var = sb.compute_blocked_stats_norm(m, block, 4, sf)
+    rmean, rvar = oracle_lib.blocked_stats(m, block, 4, transform=2, sf=sf)
+    assert np.array_equal(mean, rmean, equal_nan=True)
+    assert np.array_equal(var, rvar, equal_nan=True)
+    for pseudo in (1.0, 0.5, 2.0):
+        mean, var = sb.compute_blocked_stats_lognorm(m, block, 4, sf, pseudo)
+        rmean, rvar = oracle_lib.blocked_stats(m, block, 4, transform=1, sf=sf, pseudo=pseudo)
+        np.testing.assert_allclose(mean, rmean, rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(var, rvar, rtol=1e-12, atol=1e-13)
+
+
 def test_blocked_stats_stored_zeros_follow_sparse_branch(sb, oracle_lib):
     import scipy.sparse as sp
     x = make_matrix(50, 120, seed=5)
