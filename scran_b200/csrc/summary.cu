@@ -212,6 +212,355 @@ __global__ void k5_fill_i32(int32_t* d, int64_t n, int32_t v) {
     if (t < n) d[t] = v;
 }
 
+// ------------------------------------------------------------------------------------------
+// k5_rank_buckets: the same ranks without sorting the column. One CTA per "run" = one comparison
+// column seen through one key (x, or 1 - x for the mirrored AUC table, whose rounding may merge
+// neighbouring values: R/scoreMarkers.R:373-377) and up to two output tables: 1 + #(key > own key)
+// and 1 + #(key < own key).
+// The valid (non-NaN) values are spread over as many value buckets as there are values: 1024
+// equal-width coarse buckets over [min, max], each divided into as many fine buckets as it has
+// values (so the fine buckets follow the density). Count -> scan gives every fine bucket's
+// position range [start, end) in the sorted order without sorting; what is left is the order
+// INSIDE a gene's own bucket, for which the keys of a window of buckets are scattered to shared
+// memory: a bucket of <= 32 is scanned, a larger one (thousands of genes share AUC = 0.5 or d = 0)
+// is checked for a single value, else sorted by one warp and searched. 1 + #greater = 1 + (valid -
+// end) + greater inside the bucket; 1 + #less = 1 + start + less inside the bucket.
+// ------------------------------------------------------------------------------------------
+constexpr int RB_COARSE = 1024;
+constexpr int RB_SMALL = 32;
+
+struct RankRunParams {
+    const double* x;
+    int64_t ld;
+    int n, nruns, capk;
+    const int32_t *src, *flip, *tab_greater, *tab_less;  // per run
+    int32_t* minrank;
+};
+
+__device__ __forceinline__ uint32_t rb_fine(uint64_t key, const uint32_t* coff, double fmin, double scale) {
+    const double x = (value_of(key) - fmin) * scale;  // the conversions saturate; +-inf end up in the end buckets
+    const uint32_t d = min(__double2uint_rz(x), (uint32_t)RB_COARSE - 1u);
+    const uint32_t lo = coff[d], c = coff[d + 1] - lo;
+    return lo + min(__double2uint_rz((x - (double)d) * (double)c), c - 1u);
+}
+
+// in-place ascending sort of sz keys in shared memory by one warp (bitonic with flips; positions >= sz
+// act as +infinity and are never touched)
+__device__ inline void rb_warp_sort(uint64_t* k, int sz, int lane) {
+    int n2 = 2;
+    while (n2 < sz) n2 <<= 1;
+    for (int span = 2; span <= n2; span <<= 1) {
+        const int half = span >> 1;
+        for (int i = lane; i < (n2 >> 1); i += 32) {
+            const int blk = i / half, r = i - blk * half;
+            const int a = blk * span + r, b = blk * span + span - 1 - r;
+            if (b < sz) {
+                const uint64_t ka = k[a], kb = k[b];
+                if (kb < ka) {
+                    k[a] = kb;
+                    k[b] = ka;
+                }
+            }
+        }
+        __syncwarp();
+        for (int j = span >> 2; j > 0; j >>= 1) {
+            for (int i = lane; i < (n2 >> 1); i += 32) {
+                const int a = ((i / j) * 2 * j) + (i % j), b = a + j;
+                if (b < sz) {
+                    const uint64_t ka = k[a], kb = k[b];
+                    if (kb < ka) {
+                        k[a] = kb;
+                        k[b] = ka;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int n = P.n;
+    uint64_t* skeys = reinterpret_cast<uint64_t*>(smem_raw);                 // [capk]
+    double* red = reinterpret_cast<double*>(skeys + P.capk);                  // [64]
+    unsigned long long* kred = reinterpret_cast<unsigned long long*>(red + 64);  // [2]
+    uint32_t* coff = reinterpret_cast<uint32_t*>(kred + 2);                   // [RB_COARSE + 1]
+    uint32_t* scan = coff + RB_COARSE + 1;                                    // [32]
+    uint32_t* misc = scan + 32;                                               // [8]
+    uint32_t* biglist = misc + 8;                                             // [n / RB_SMALL + 2]
+    uint32_t* bk = biglist + (n / RB_SMALL + 2);                              // [(n + 1) / 2]: 16-bit counters
+    uint16_t* bh = reinterpret_cast<uint16_t*>(bk);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const double inf = __longlong_as_double(0x7ff0000000000000ll);
+
+    for (int run = blockIdx.x; run < P.nruns; run += gridDim.x) {
+        const double* col = P.x + (size_t)P.src[run] * P.ld;
+        const bool flip = P.flip[run] != 0;
+        const int tg = P.tab_greater[run], tl = P.tab_less[run];
+        auto value = [&](int i) {
+            const double v = col[i];
+            return flip ? 1.0 - v : v;
+        };
+        __syncthreads();
+        // ---- valid count and finite range ----
+        {
+            double lo = inf, hi = -inf;
+            uint32_t nans = 0;
+            for (int i = tid; i < n; i += blockDim.x) {
+                const double v = value(i);
+                if (isnan(v)) {
+                    ++nans;
+                } else if (!isinf(v)) {
+                    lo = fmin(lo, v);
+                    hi = fmax(hi, v);
+                }
+            }
+            for (int o = 16; o > 0; o >>= 1) {
+                lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+                hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+                nans += __shfl_xor_sync(0xffffffffu, nans, o);
+            }
+            if (lane == 0) {
+                red[warp] = lo;
+                red[32 + warp] = hi;
+                scan[warp] = nans;
+            }
+            for (int i = tid; i <= RB_COARSE; i += blockDim.x) coff[i] = 0;
+            for (int i = tid; i < (n + 1) / 2; i += blockDim.x) bk[i] = 0;
+            __syncthreads();
+            if (warp == 0) {
+                double a = lane < nwarps ? red[lane] : inf, b = lane < nwarps ? red[32 + lane] : -inf;
+                uint32_t c = lane < nwarps ? scan[lane] : 0u;
+                for (int o = 16; o > 0; o >>= 1) {
+                    a = fmin(a, __shfl_xor_sync(0xffffffffu, a, o));
+                    b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+                    c += __shfl_xor_sync(0xffffffffu, c, o);
+                }
+                if (lane == 0) {
+                    red[0] = a;
+                    red[1] = b;
+                    misc[0] = c;
+                    misc[1] = 0;  // number of large buckets
+                }
+            }
+            __syncthreads();
+        }
+        const double fmin_v = red[0] <= red[1] ? red[0] : 0.0, fmax_v = red[0] <= red[1] ? red[1] : 0.0;
+        const double scale = fmax_v > fmin_v ? (double)RB_COARSE / (fmax_v - fmin_v) : 0.0;
+        const uint32_t nv = (uint32_t)n - misc[0];
+        if (nv == 0) continue;
+        // ---- coarse counts -> offsets ----
+        for (int i = tid; i < n; i += blockDim.x) {
+            const double v = value(i);
+            if (!isnan(v)) {  // the same expression as rb_fine
+                const double xx = (value_of(key_of(v)) - fmin_v) * scale;
+                atomicAdd(&coff[min(__double2uint_rz(xx), (uint32_t)RB_COARSE - 1u)], 1u);
+            }
+        }
+        __syncthreads();
+        if (warp == 0) {  // exclusive scan of RB_COARSE counts: 32 per lane
+            uint32_t c[RB_COARSE / 32], sum = 0;
+#pragma unroll
+            for (int q = 0; q < RB_COARSE / 32; ++q) {
+                c[q] = coff[lane * (RB_COARSE / 32) + q];
+                sum += c[q];
+            }
+            uint32_t incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += y;
+            }
+            uint32_t at = incl - sum;
+#pragma unroll
+            for (int q = 0; q < RB_COARSE / 32; ++q) {
+                coff[lane * (RB_COARSE / 32) + q] = at;
+                at += c[q];
+            }
+            if (lane == 31) coff[RB_COARSE] = at;
+        }
+        __syncthreads();
+        // ---- fine counts -> start offsets (in place), large buckets noted ----
+        for (int i = tid; i < n; i += blockDim.x) {
+            const double v = value(i);
+            if (!isnan(v)) {
+                const uint32_t b = rb_fine(key_of(v), coff, fmin_v, scale);
+                atomicAdd(&bk[b >> 1], 1u << ((b & 1u) * 16u));
+            }
+        }
+        __syncthreads();
+        {
+            const uint32_t per = (nv + blockDim.x - 1) / blockDim.x;
+            const uint32_t lo = min(nv, (uint32_t)tid * per), hi = min(nv, lo + per);
+            uint32_t sum = 0;
+            for (uint32_t i = lo; i < hi; ++i) sum += bh[i];
+            uint32_t incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += y;
+            }
+            if (lane == 31) scan[warp] = incl;
+            __syncthreads();
+            if (warp == 0) {
+                uint32_t v = lane < nwarps ? scan[lane] : 0u;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+                    if (lane >= o) v += y;
+                }
+                scan[lane] = v;
+            }
+            __syncthreads();
+            uint32_t at = (warp ? scan[warp - 1] : 0u) + incl - sum;
+            for (uint32_t i = lo; i < hi; ++i) {
+                const uint32_t c = bh[i];
+                bh[i] = (uint16_t)at;
+                at += c;
+                if (c > (uint32_t)RB_SMALL) biglist[atomicAdd(&misc[1], 1u)] = i;
+            }
+        }
+        __syncthreads();
+        const uint32_t nbig = misc[1];
+
+        // ---- windows of consecutive fine buckets whose keys fit shared memory ----
+        uint32_t b0 = 0;  // first bucket not yet done; bh[b] = start for b >= b0, end for b < b0
+        while (b0 < nv) {
+            __syncthreads();
+            const uint32_t wstart = bh[b0];
+            if (tid == 0) {  // last bucket b1 with start[b1] - wstart <= capk (start[nv] = nv)
+                uint32_t lo = b0, hi = nv;  // invariant: start[lo] - wstart <= capk
+                while (lo < hi) {
+                    const uint32_t mid = (lo + hi + 1) >> 1;
+                    const uint32_t st = mid == nv ? nv : (uint32_t)bh[mid];
+                    if (st - wstart <= (uint32_t)P.capk) lo = mid; else hi = mid - 1;
+                }
+                misc[2] = lo;
+            }
+            __syncthreads();
+            uint32_t b1 = misc[2];
+            const bool giant = b1 == b0;  // bucket b0 alone exceeds the window
+            if (giant) b1 = b0 + 1;
+            const uint32_t wend = b1 == nv ? nv : (uint32_t)bh[b1];
+            __syncthreads();
+            if (giant) {
+                // One bucket with more keys than shared memory holds: in practice thousands of genes
+                // with one and the same value. Its key range tells; if the keys do differ (values
+                // clustered beyond the resolution of the two-level buckets) every member counts over
+                // the whole column instead.
+                if (tid < 2) kred[tid] = tid == 0 ? ~0ull : 0ull;
+                __syncthreads();
+                unsigned long long klo = ~0ull, khi = 0ull;
+                for (int i = tid; i < n; i += blockDim.x) {
+                    const double v = value(i);
+                    if (isnan(v)) continue;
+                    const unsigned long long key = key_of(v);
+                    if (rb_fine(key, coff, fmin_v, scale) == b0) {
+                        klo = key < klo ? key : klo;
+                        khi = key > khi ? key : khi;
+                    }
+                }
+                for (int o = 16; o > 0; o >>= 1) {
+                    const unsigned long long a = __shfl_xor_sync(0xffffffffu, klo, o), b = __shfl_xor_sync(0xffffffffu, khi, o);
+                    klo = a < klo ? a : klo;
+                    khi = b > khi ? b : khi;
+                }
+                if (lane == 0) {
+                    atomicMin(&kred[0], klo);
+                    atomicMax(&kred[1], khi);
+                }
+                __syncthreads();
+                const bool uniform = kred[0] == kred[1];
+                for (int i = tid; i < n; i += blockDim.x) {
+                    const double v = value(i);
+                    if (isnan(v)) continue;
+                    const uint64_t key = key_of(v);
+                    if (rb_fine(key, coff, fmin_v, scale) != b0) continue;
+                    uint32_t greater = nv - wend, less = wstart;
+                    if (!uniform) {
+                        greater = 0;
+                        less = 0;
+                        for (int j = 0; j < n; ++j) {
+                            const double vj = value(j);
+                            if (isnan(vj)) continue;
+                            const uint64_t kj = key_of(vj);
+                            greater += kj > key ? 1u : 0u;
+                            less += kj < key ? 1u : 0u;
+                        }
+                    }
+                    if (tg >= 0) atomicMin(&P.minrank[(size_t)tg * n + i], (int)(1u + greater));
+                    if (tl >= 0) atomicMin(&P.minrank[(size_t)tl * n + i], (int)(1u + less));
+                }
+                __syncthreads();
+                if (tid == 0) bh[b0] = (uint16_t)wend;
+                b0 = b1;
+                continue;
+            }
+            // scatter the window's keys into bucket order: afterwards bh[b] is the END of bucket b
+            for (int i = tid; i < n; i += blockDim.x) {
+                const double v = value(i);
+                if (isnan(v)) continue;
+                const uint64_t key = key_of(v);
+                const uint32_t b = rb_fine(key, coff, fmin_v, scale);
+                if (b >= b0 && b < b1) {
+                    const uint32_t sh = (b & 1u) * 16u;
+                    const uint32_t pos = (atomicAdd(&bk[b >> 1], 1u << sh) >> sh) & 0xffffu;
+                    skeys[pos - wstart] = key;
+                }
+            }
+            __syncthreads();
+            // large buckets of the window: one warp each; left alone if all keys are equal, else sorted
+            for (uint32_t w = warp; w < nbig; w += nwarps) {
+                const uint32_t b = biglist[w];
+                if (b < b0 || b >= b1) continue;
+                const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
+                uint64_t* k = skeys + (start - wstart);
+                const int sz = (int)(end - start);
+                const uint64_t k0 = k[0];
+                bool same = true;
+                for (int i = lane; i < sz; i += 32) same &= k[i] == k0;
+                if (!__all_sync(0xffffffffu, same)) rb_warp_sort(k, sz, lane);
+            }
+            __syncthreads();
+            for (int i = tid; i < n; i += blockDim.x) {
+                const double v = value(i);
+                if (isnan(v)) continue;
+                const uint64_t key = key_of(v);
+                const uint32_t b = rb_fine(key, coff, fmin_v, scale);
+                if (b < b0 || b >= b1) continue;
+                const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
+                const uint64_t* k = skeys + (start - wstart);
+                const uint32_t sz = end - start;
+                uint32_t greater = 0, less = 0;
+                if (sz <= (uint32_t)RB_SMALL) {
+                    for (uint32_t j = 0; j < sz; ++j) {
+                        const uint64_t kj = k[j];
+                        greater += kj > key ? 1u : 0u;
+                        less += kj < key ? 1u : 0u;
+                    }
+                } else {  // sorted (or all equal): first key >= own, first key > own
+                    uint32_t lo = 0, hi = sz;
+                    while (lo < hi) {
+                        const uint32_t mid = (lo + hi) >> 1;
+                        if (k[mid] >= key) hi = mid; else lo = mid + 1;
+                    }
+                    less = lo;
+                    hi = sz;
+                    while (lo < hi) {
+                        const uint32_t mid = (lo + hi) >> 1;
+                        if (k[mid] > key) hi = mid; else lo = mid + 1;
+                    }
+                    greater = sz - lo;
+                }
+                if (tg >= 0) atomicMin(&P.minrank[(size_t)tg * n + i], (int)(1u + (nv - end) + greater));
+                if (tl >= 0) atomicMin(&P.minrank[(size_t)tl * n + i], (int)(1u + start + less));
+            }
+            b0 = b1;
+        }
+    }
+}
+
 __global__ void k5_finish(const int32_t* minrank, int64_t ngenes, int64_t ld, int K, double* out) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= ngenes * K * 3) return;
@@ -229,6 +578,49 @@ void launch_rank(scranb200_ctx* ctx, const double* d_x, int64_t ld, int64_t ngen
     const int ncols = (int)col_src.size();
     if (ncols == 0 || ngenes == 0) return;
     if (ngenes > 2147483647ll / 2) throw Error("too many genes to rank");
+    if (ngenes <= 65000) {  // bucket ranking (16-bit positions); longer columns take the sorting kernel below
+        std::vector<int32_t> src, flip, tg, tl;
+        for (int c = 0; c < ncols; ++c) {
+            if (tab_direct[c] < 0 && tab_flipped[c] < 0) continue;
+            if (!is_auc[c]) {  // -x > -x_t  <=>  x < x_t: both tables from one run
+                src.push_back(col_src[c]); flip.push_back(0); tg.push_back(tab_direct[c]); tl.push_back(tab_flipped[c]);
+            } else {
+                if (tab_direct[c] >= 0) {
+                    src.push_back(col_src[c]); flip.push_back(0); tg.push_back(tab_direct[c]); tl.push_back(-1);
+                }
+                if (tab_flipped[c] >= 0) {  // ranks of 1 - x, as computed values
+                    src.push_back(col_src[c]); flip.push_back(1); tg.push_back(tab_flipped[c]); tl.push_back(-1);
+                }
+            }
+        }
+        const int nruns = (int)src.size();
+        if (nruns == 0) return;
+        std::vector<int32_t> host;
+        host.insert(host.end(), src.begin(), src.end());
+        host.insert(host.end(), flip.begin(), flip.end());
+        host.insert(host.end(), tg.begin(), tg.end());
+        host.insert(host.end(), tl.begin(), tl.end());
+        ctx->io_c.reserve(host.size() * 4);
+        SB_CUDA(cudaMemcpyAsync(ctx->io_c.p, host.data(), host.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        SB_CUDA(cudaStreamSynchronize(ctx->stream));
+        RankRunParams rp;
+        rp.x = d_x;
+        rp.ld = ld;
+        rp.n = (int)ngenes;
+        rp.nruns = nruns;
+        rp.src = ctx->io_c.as<int32_t>();
+        rp.flip = rp.src + nruns;
+        rp.tab_greater = rp.flip + nruns;
+        rp.tab_less = rp.tab_greater + nruns;
+        rp.minrank = d_minrank;
+        const size_t fixed = 64 * 8 + 16 + (size_t)(RB_COARSE + 1 + 32 + 8) * 4 + (size_t)(ngenes / RB_SMALL + 2) * 4 +
+                             (size_t)((ngenes + 1) / 2) * 4 + 16;
+        rp.capk = (int)std::min<size_t>((ctx->smem_optin - fixed) / 8, (size_t)ngenes);
+        const size_t smem = (size_t)rp.capk * 8 + fixed;
+        allow_smem(k5_rank_buckets, smem);
+        SB_LAUNCH(ctx, k5_rank_buckets, std::min(nruns, ctx->sm_count), 1024, smem, rp);
+        return;
+    }
     std::vector<int32_t> host;
     host.insert(host.end(), col_src.begin(), col_src.end());
     host.insert(host.end(), tab_direct.begin(), tab_direct.end());

@@ -203,6 +203,37 @@ def test_compute_min_rank_many_rows(sb):
     assert np.array_equal(sb.compute_min_rank(x).astype(np.int64), rlevel.compute_min_rank(x))
 
 
+def test_compute_min_rank_degenerate_columns(sb):
+    """Columns that stress the bucket ranking: most genes sharing one value (one bucket larger than
+    shared memory), infinities and NaN, values clustered far beyond the bucket resolution with two
+    outliers stretching the range, a constant column."""
+    from oracle import rlevel
+    rng = np.random.default_rng(19)
+    n = 40000
+    x = np.empty((n, 5))
+    x[:, 0] = np.where(rng.random(n) < 0.8, 0.5, rng.random(n))            # AUC-like: 80 % exactly 0.5
+    x[:, 1] = rng.normal(size=n)
+    x[::7, 1] = np.inf
+    x[::11, 1] = -np.inf
+    x[::13, 1] = np.nan
+    x[:, 2] = 1.0 + 1e-13 * rng.permutation(n)                              # distinct, tightly clustered ...
+    x[0, 2] = 1e6                                                           # ... and two outliers
+    x[1, 2] = -1e6
+    x[:, 3] = 3.25
+    x[:, 4] = np.round(rng.normal(size=n), 1)
+    assert np.array_equal(sb.compute_min_rank(x).astype(np.int64), rlevel.compute_min_rank(x))
+    for c in range(5):
+        assert np.array_equal(sb.compute_min_rank(x[:, c:c + 1]).astype(np.int64), rlevel.compute_min_rank(x[:, c:c + 1]))
+
+
+def test_compute_min_rank_long_columns(sb):
+    """More rows than 16-bit positions hold: the sorting kernel."""
+    from oracle import rlevel
+    rng = np.random.default_rng(20)
+    x = np.round(rng.normal(size=(70000, 2)), 3)
+    assert np.array_equal(sb.compute_min_rank(x).astype(np.int64), rlevel.compute_min_rank(x))
+
+
 # ---------------------------------------------------------------------------------------------
 # scoreMarkers  (tests/testthat/test-score-markers.R)
 # ---------------------------------------------------------------------------------------------
