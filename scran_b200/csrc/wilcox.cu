@@ -475,10 +475,20 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
 
     // ---- exclusive scan of the counts (in place), large buckets noted ----
     {
-        const uint32_t per = (total + blockDim.x - 1) / blockDim.x;
+        // a thread owns a multiple of 8 counters = whole 16-byte words (counters past `total` are zero
+        // up to the end of the last 32-bit word; the words beyond that are never read)
+        const uint32_t per = ((total + blockDim.x * 8u - 1u) / (blockDim.x * 8u)) * 8u;
         const uint32_t lo = min(total, (uint32_t)tid * per), hi = min(total, lo + per);
         uint32_t sum = 0;
-        for (uint32_t i = lo; i < hi; ++i) sum += bh[i];
+        for (uint32_t i = lo; i < hi; i += 8) {
+            if (i + 8 <= hi) {
+                const uint4 w = *reinterpret_cast<const uint4*>(bh + i);
+                sum += (w.x & 0xffffu) + (w.x >> 16) + (w.y & 0xffffu) + (w.y >> 16) + (w.z & 0xffffu) + (w.z >> 16) +
+                       (w.w & 0xffffu) + (w.w >> 16);
+            } else {
+                for (uint32_t k = i; k < hi; ++k) sum += bh[k];
+            }
+        }
         uint32_t incl = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -908,6 +918,41 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 if (hi_k != ~0ull) top_bit = lo_k == hi_k ? 0 : 64 - __clzll((long long)(lo_k ^ hi_k));
             }
             __syncthreads();
+            if (S.bmin[0] == S.bmin[1]) {
+                // one value only (integer-valued data): any order inside a role will do, R role first
+                if (tid < 2) S.misc[6 + tid] = 0;
+                __syncthreads();
+                uint32_t n_r = 0;
+                for (uint32_t j = tid; j < cnt; j += blockDim.x) n_r += (gp[start + j] & ROLE_L) ? 0u : 1u;
+                for (int o = 16; o > 0; o >>= 1) n_r += __shfl_xor_sync(0xffffffffu, n_r, o);
+                if (lane == 0 && n_r) atomicAdd(&S.misc[6], n_r);
+                __syncthreads();
+                n_r = S.misc[6];
+                __syncthreads();
+                if (tid == 0) S.misc[6] = 0;
+                __syncthreads();
+                for (uint32_t j0 = 0; j0 < cnt; j0 += blockDim.x) {  // positions by warp-aggregated counters
+                    const uint32_t j = j0 + tid;
+                    const bool valid = j < cnt;
+                    const uint32_t lab = valid ? gp[start + j] & 0xffffu : 0u;
+                    const bool is_l = valid && (lab & ROLE_L);
+                    const unsigned ml = __ballot_sync(0xffffffffu, is_l), mr = __ballot_sync(0xffffffffu, valid && !is_l);
+                    uint32_t base_l = 0, base_r = 0;
+                    if (lane == 0) {
+                        base_r = atomicAdd(&S.misc[6], (uint32_t)__popc(mr));
+                        base_l = atomicAdd(&S.misc[7], (uint32_t)__popc(ml));
+                    }
+                    base_r = __shfl_sync(0xffffffffu, base_r, 0);
+                    base_l = __shfl_sync(0xffffffffu, base_l, 0);
+                    if (valid) {
+                        const unsigned below = (1u << lane) - 1u;
+                        const uint32_t q = is_l ? n_r + base_l + __popc(ml & below) : base_r + __popc(mr & below);
+                        if (start + q < m) P.stream[soff + start + q] = (uint16_t)((lab & 0x7fffu) | (q > 0 ? TIE_BIT : 0u));
+                    }
+                }
+                continue;
+            }
+            if (blockDim.x != SORT_THREADS) __trap();  // the radix passes below are written for SORT_THREADS threads
             // the split left the bucket in no particular order; with two roles a stable pass on the
             // payload byte that holds the role bit comes first, so that R entries precede L entries
             // among equal keys after the (stable) key passes
