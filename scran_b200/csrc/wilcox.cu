@@ -1696,20 +1696,24 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         const size_t acc_size = pass == 0 ? 4 : 8;
         if (pass == 1 && max_m <= 65536) break;
         wp.pass = pass;
-        const size_t per_tile = (size_t)Gt * W * acc_size;
+        if (walk_fixed > ctx->smem_optin) throw Error("too many groups inside one block for the shared-memory count table");
         const size_t budget = ctx->smem_optin - walk_fixed;
-        if (walk_fixed > ctx->smem_optin || per_tile > budget) {
-            // not even one wide tile fits (hundreds of groups with 64-bit counts); outside every
-            // configuration of BASELINE.json
-            throw Error("too many groups inside one block for the shared-memory count table");
-        }
+        // Labels per warp for this pass: the widest tile (fewest decodes of an entry) whose tiles all fit
+        // shared memory at once, so that the stream is walked once; with hundreds of groups the
+        // padding of wide tiles decides (201 labels: seven tiles of 32 fit, one tile of 256 does not).
+        // If not even the narrow tiles fit together (64-bit counts), they are walked in batches.
+        int Jp = J;
+        while (Jp > 1 && (size_t)Gt * 32 * Jp * acc_size * ((Gt + 32 * Jp - 1) / (32 * Jp)) > budget) Jp >>= 1;
+        const int Wp = 32 * Jp, ntiles_p = (Gt + Wp - 1) / Wp;
+        const size_t per_tile = (size_t)Gt * Wp * acc_size;
+        if (per_tile > budget) throw Error("too many groups inside one block for the shared-memory count table");
         int tpb, groups;
-        if (per_tile * ntiles <= budget) {
-            tpb = std::min(ntiles, WALK_WARPS);
-            groups = (int)std::min<size_t>(budget / (per_tile * ntiles), (size_t)WALK_MAX_GROUPS);
+        if (per_tile * ntiles_p <= budget) {
+            tpb = std::min(ntiles_p, WALK_WARPS);
+            groups = (int)std::min<size_t>(budget / (per_tile * ntiles_p), (size_t)WALK_MAX_GROUPS);
             groups = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
         } else {
-            tpb = (int)std::max<size_t>(1, std::min<size_t>(budget / per_tile, (size_t)ntiles));
+            tpb = (int)std::max<size_t>(1, std::min<size_t>(budget / per_tile, (size_t)ntiles_p));
             tpb = std::min(tpb, WALK_WARPS);
             groups = 1;
         }
@@ -1725,9 +1729,9 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     } while (0)
 #define SB_WALK_J(ACC, SH)                  \
     do {                                    \
-        if (J == 1) SB_WALK(ACC, SH, 1);    \
-        else if (J == 2) SB_WALK(ACC, SH, 2); \
-        else if (J == 4) SB_WALK(ACC, SH, 4); \
+        if (Jp == 1) SB_WALK(ACC, SH, 1);    \
+        else if (Jp == 2) SB_WALK(ACC, SH, 2); \
+        else if (Jp == 4) SB_WALK(ACC, SH, 4); \
         else SB_WALK(ACC, SH, 8);           \
     } while (0)
         if (pass == 0) {

@@ -158,6 +158,24 @@ def test_overlap_large_units(sb, port_lib):
         assert np.array_equal(t, pt)
 
 
+def test_overlap_many_groups_large_units(sb, port_lib):
+    """200 groups (config 5's count): the count table nearly fills shared memory, so the labels are
+    covered by narrow tiles, and with 64-bit counts (units beyond 65536 entries) in batches."""
+    rng = np.random.default_rng(79)
+    ncells, ngroups = 140000, 200
+    x = np.zeros((3, ncells))
+    x[0] = rng.random(ncells) + 0.1                                                   # every cell: 140,001 entries
+    x[1] = np.where(rng.random(ncells) < 0.07, np.log2(1 + rng.poisson(2, ncells) + rng.random(ncells)), 0)
+    x[2] = np.where(rng.random(ncells) < 0.6, rng.poisson(2, ncells), 0)              # long tie runs
+    g = rng.integers(0, ngroups, ncells)
+    groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(ngroups)]
+    left, right = all_pairs(ngroups)
+    u, t = sb.overlap_exprs_paired(as_csc(x), left, right, groups, 0.0, want_ties=True)
+    pu, pt = port_lib.overlap_paired(as_csc(x), left, right, groups, 0.0, want_ties=True)
+    assert np.array_equal(u, pu)
+    assert np.array_equal(t, pt)
+
+
 def test_overlap_long_tie_runs(sb, port_lib):
     """Integer-valued data: runs of equal values much longer than a warp's block of 32 entries, in
     units small enough for the warp-group walk, with 3 and with 40 groups (one and two labels a lane)."""
