@@ -1045,6 +1045,14 @@ __device__ inline void slot_barrier(int slot, int slot_tiles) {
 // The running counts start at zero: what the entries BEFORE i_lo contribute is linear in the
 // counts this function returns (cnt_r: entries per label in the counted role; cnt_l: entries per
 // label in the adding role, which is the same thing unless SHIFT) and is added by the caller.
+// One cell of a count table += x. 32-bit cells: a shared-memory atomic add is a single instruction
+// that nothing waits for (no load / add / store chain through shared memory); 64-bit cells have no
+// native shared-memory add (it compiles to a compare-and-swap loop), so they keep the plain form.
+template <typename AccT>
+__device__ __forceinline__ void add_cell(AccT* p, AccT x) {
+    if constexpr (sizeof(AccT) == 4) atomicAdd(p, x); else *p += x;
+}
+
 template <typename AccT, bool SHIFT, int J>
 __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_hi, int R0, AccT* col, size_t rpad,
                                            uint32_t* cnt_r, uint32_t* cnt_l, int Gt, int lane) {
@@ -1071,7 +1079,7 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
             if (e & ROLE_L) {
 #pragma unroll
                 for (int j = 0; j < J; ++j) {
-                    row[32 * j] += (AccT)cs[j] + (AccT)c[j];
+                    add_cell(&row[32 * j], (AccT)cs[j] + (AccT)c[j]);
                     bump(cl[j], lab, Rj[j]);
                 }
             } else {
@@ -1081,7 +1089,7 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         } else {
 #pragma unroll
             for (int j = 0; j < J; ++j) {
-                row[32 * j] += (AccT)cs[j];
+                add_cell(&row[32 * j], (AccT)cs[j]);
                 bump(c[j], lab, Rj[j]);
             }
         }
@@ -1093,7 +1101,7 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         AccT* row = reinterpret_cast<AccT*>(colb + lab * rowbytes);
 #pragma unroll
         for (int j = 0; j < J; ++j) {
-            row[32 * j] += (AccT)c[j];
+            add_cell(&row[32 * j], (AccT)c[j]);
             bump(c[j], (int)lab, Rj[j]);
         }
     };
@@ -1102,7 +1110,7 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
     // round trips. The labels are warp-uniform: when the four differ (checked without divergence)
     // their rows are disjoint, all loads go out first and the adds and stores follow.
     // (QN entries at once: four while the loaded table words fit in 16 registers, else two, else one.)
-    constexpr int QN = J * sizeof(AccT) <= 16 ? 4 : J * sizeof(AccT) <= 32 ? 2 : 1;
+    constexpr int QN = sizeof(AccT) == 4 ? 1 : (J * sizeof(AccT) <= 32 ? 2 : 1);  // (32-bit: atomics, nothing to overlap)
     auto multi_untied = [&](const uint32_t (&l)[QN]) {
         bool dup = false;
 #pragma unroll
@@ -1157,7 +1165,7 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
                 if (h != 0u) {
                     AccT* row = reinterpret_cast<AccT*>(colb + (uint32_t)L * rowbytes);
 #pragma unroll
-                    for (int q = 0; q < J; ++q) row[32 * q] += (AccT)h * (AccT)cs[q];
+                    for (int q = 0; q < J; ++q) add_cell(&row[32 * q], (AccT)h * (AccT)cs[q]);
                 }
             }
         }
