@@ -986,7 +986,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 // ------------------------------------------------------------------------------------------
 constexpr int WALK_THREADS = 1024;
 constexpr int WALK_WARPS = WALK_THREADS / 32;
-constexpr int WALK_MAX_GROUPS = 16;
+constexpr int WALK_MAX_GROUPS = 32;
 
 struct WalkParams {
     UnitTables ut;
@@ -1008,6 +1008,7 @@ struct WalkParams {
     int pass;             // 0: everything with m <= 65536 (uint32 tables); 1: only m > 65536 (uint64 tables)
     const int32_t* nbig;  // number of large single-unit jobs at the head of `order`
     uint32_t big_total;   // a unit with more entries than this is "large": walked by a whole CTA
+    int shared_table;     // large-unit kernel: the position chunks add into ONE table (32-bit cells, atomic adds)
     int by_task;          // large-unit kernel: walk EVERY unit (used when the per-warp mode has no room for its tables)
 };
 
@@ -1292,7 +1293,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Gmax1 = P.maxG + 1;
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [2 * WALK_MAX_GROUPS (+1)][Gmax1]: per-chunk counts, counted / adding role
-    uint32_t* nnzv = hist + (size_t)(WALK_WARPS + 1) * Gmax1;                // [Gmax1]
+    uint32_t* nnzv = hist + (size_t)(2 * WALK_MAX_GROUPS) * Gmax1;           // [Gmax1]
     int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);                      // [WALK_MAX_GROUPS + 1]
     uint32_t* misc = reinterpret_cast<uint32_t*>(bounds + WALK_MAX_GROUPS + 1);  // [4]
     size_t off = (size_t)((unsigned char*)(misc + 4) - smem_raw);
@@ -1326,8 +1327,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         const int ntiles = (Gt + W - 1) / W;  // wide tiles
         const int tpb = min(P.tiles_per_batch, ntiles);
         int groups = max(1, min(P.groups, WALK_WARPS / tpb));
-        if (warp <= groups) {  // chunk starts: the first run start at or after the even split (a warp scans 32 entries a step)
-            int64_t b = warp == groups ? (int64_t)m : ((int64_t)m * warp) / groups;
+        for (int cgb = warp; cgb <= groups; cgb += WALK_WARPS) {  // chunk starts: the first run start at or after the even split (a warp scans 32 entries a step)
+            int64_t b = cgb == groups ? (int64_t)m : ((int64_t)m * cgb) / groups;
             while (b < (int64_t)m && b > 0) {
                 const bool stop = b + lane >= (int64_t)m || !(st[b + lane] & TIE_BIT);
                 const unsigned found = __ballot_sync(0xffffffffu, stop);
@@ -1337,18 +1338,19 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
                 }
                 b += 32;
             }
-            if (lane == 0) bounds[warp] = (int)b;
+            if (lane == 0) bounds[cgb] = (int)b;
         }
         for (int tb = 0; tb < ntiles; tb += tpb) {
             const int bt = min(tpb, ntiles - tb);
             const size_t rpad = (size_t)bt * W;
-            for (int k = tid; k < groups * Gt * (int)rpad; k += blockDim.x) acc[k] = 0;
+            const int copies = P.shared_table ? 1 : groups;
+            for (int k = tid; k < copies * Gt * (int)rpad; k += blockDim.x) acc[k] = 0;
             __syncthreads();
             if (warp < groups * bt) {
                 const int cg = warp / bt, tile = tb + warp % bt;
                 const int R0 = tile * W + lane;
                 walk_range<AccT, SHIFT, J>(st, bounds[cg], bounds[cg + 1], R0,
-                                           acc + (size_t)cg * Gt * rpad + (R0 - tb * W), rpad, hist + cg * Gmax1,
+                                           acc + (size_t)(P.shared_table ? 0 : cg) * Gt * rpad + (R0 - tb * W), rpad, hist + cg * Gmax1,
                                            hist + (WALK_MAX_GROUPS + cg) * Gmax1, Gt, lane);
             }
             __syncthreads();
@@ -1356,7 +1358,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
                 const int L = k / (int)rpad, R = tb * W + k % (int)rpad;
                 if (R < Gt) {
                     unsigned long long s = 0;
-                    for (int cg = 0; cg < groups; ++cg) s += (unsigned long long)acc[(size_t)cg * Gt * rpad + k];
+                    for (int cg = 0; cg < copies; ++cg) s += (unsigned long long)acc[(size_t)cg * Gt * rpad + k];
                     bfull[(size_t)L * Gt + R] = s;
                 }
             }
@@ -1653,7 +1655,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     const int J = narrow_tiles <= 1 ? 1 : narrow_tiles <= 2 ? 2 : narrow_tiles <= 4 ? 4 : 8;
     const int W = 32 * J;
     const int ntiles = (Gt + W - 1) / W;  // wide tiles = warps per unit
-    const size_t walk_fixed = ((size_t)(WALK_WARPS + 1) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32;
+    const size_t walk_fixed = ((size_t)(2 * WALK_MAX_GROUPS) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32;
     const int walk_grid_max = ctx->sm_count * 2;
     ctx->plan_tmp.reserve((size_t)walk_grid_max * Gt * Gt * 8 + 64);
     wp.bfull = ctx->plan_tmp.as<unsigned long long>();
@@ -1716,10 +1718,18 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         const size_t per_tile = (size_t)Gt * Wp * acc_size;
         if (per_tile > budget) throw Error("too many groups inside one block for the shared-memory count table");
         int tpb, groups;
+        int copies = 1;
+        wp.shared_table = 0;
         if (per_tile * ntiles_p <= budget) {
             tpb = std::min(ntiles_p, WALK_WARPS);
-            groups = (int)std::min<size_t>(budget / (per_tile * ntiles_p), (size_t)WALK_MAX_GROUPS);
-            groups = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
+            if (pass == 0) {  // 32-bit cells take atomic adds: every warp walks a position chunk into one shared table
+                wp.shared_table = 1;
+                groups = std::max(1, std::min(WALK_MAX_GROUPS, WALK_WARPS / std::max(1, tpb)));
+            } else {
+                groups = (int)std::min<size_t>(budget / (per_tile * ntiles_p), (size_t)WALK_MAX_GROUPS);
+                groups = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
+                copies = groups;
+            }
         } else {
             tpb = (int)std::max<size_t>(1, std::min<size_t>(budget / per_tile, (size_t)ntiles_p));
             tpb = std::min(tpb, WALK_WARPS);
@@ -1727,7 +1737,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         }
         wp.tiles_per_batch = tpb;
         wp.groups = groups;
-        const size_t smem = walk_fixed + per_tile * tpb * groups;
+        const size_t smem = walk_fixed + per_tile * tpb * copies;
         SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
         const int grid = (int)std::min<int64_t>(ntasks, smem * 2 <= ctx->smem_optin ? walk_grid_max : ctx->sm_count);
 #define SB_WALK(ACC, SH, JJ)                                              \
