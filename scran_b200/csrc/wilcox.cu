@@ -1008,6 +1008,7 @@ struct WalkParams {
     int pass;             // 0: everything with m <= 65536 (uint32 tables); 1: only m > 65536 (uint64 tables)
     const int32_t* nbig;  // number of large single-unit jobs at the head of `order`
     uint32_t big_total;   // a unit with more entries than this is "large": walked by a whole CTA
+    int groups0;          // large-unit kernel: position chunks of the 32-bit pass (the 64-bit pass needs them to tell its units)
     int shared_table;     // large-unit kernel: the position chunks add into ONE table (32-bit cells, atomic adds)
     int by_task;          // large-unit kernel: walk EVERY unit (used when the per-warp mode has no room for its tables)
 };
@@ -1319,26 +1320,53 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         }
         // ---- one large unit, all warps: position chunks with private tables -----------------
         const uint32_t m = P.unit_m[t0];
-        const bool wide = m > 65536u;
-        if ((P.pass == 0) == wide) continue;
+        if (P.pass == 1 && m <= 65536u) continue;  // always fits 32-bit cells
         const UnitInfo ui = unit_info(ut, t0);
         const int G = ui.G, Gt = G + 1;
         const uint16_t* st = P.stream + ui.soff;
         const int ntiles = (Gt + W - 1) / W;  // wide tiles
         const int tpb = min(P.tiles_per_batch, ntiles);
         int groups = max(1, min(P.groups, WALK_WARPS / tpb));
-        for (int cgb = warp; cgb <= groups; cgb += WALK_WARPS) {  // chunk starts: the first run start at or after the even split (a warp scans 32 entries a step)
-            int64_t b = cgb == groups ? (int64_t)m : ((int64_t)m * cgb) / groups;
-            while (b < (int64_t)m && b > 0) {
-                const bool stop = b + lane >= (int64_t)m || !(st[b + lane] & TIE_BIT);
-                const unsigned found = __ballot_sync(0xffffffffu, stop);
-                if (found) {
-                    b += __ffs(found) - 1;
-                    break;
+        // chunk starts: the first run start at or after the even split (a warp scans 32 entries a step)
+        auto chunk_bounds = [&](int ng) {
+            for (int cgb = warp; cgb <= ng; cgb += WALK_WARPS) {
+                int64_t b = cgb == ng ? (int64_t)m : ((int64_t)m * cgb) / ng;
+                while (b < (int64_t)m && b > 0) {
+                    const bool stop = b + lane >= (int64_t)m || !(st[b + lane] & TIE_BIT);
+                    const unsigned found = __ballot_sync(0xffffffffu, stop);
+                    if (found) {
+                        b += __ffs(found) - 1;
+                        break;
+                    }
+                    b += 32;
                 }
-                b += 32;
+                if (lane == 0) bounds[cgb] = (int)b;
             }
-            if (lane == 0) bounds[cgb] = (int)b;
+        };
+        // Which pass owns the unit. Every chunk is walked from zero counts, so a cell receives at most
+        // the sum over the chunks of (entries / 2)^2 (twice that with a shift); the 32-bit pass takes
+        // the unit if that stays below 2^32 for ITS chunks (hundreds of thousands of entries do, unless
+        // one giant run of equal values keeps most of them in one chunk), the 64-bit pass what is left.
+        auto fits32 = [&](int ng) {
+            chunk_bounds(ng);
+            __syncthreads();
+            if (tid == 0) {
+                unsigned long long sum = 0;
+                for (int c = 0; c < ng; ++c) {
+                    const unsigned long long len = (unsigned long long)(bounds[c + 1] - bounds[c]);
+                    sum += len * len;
+                }
+                misc[1] = (sum / 4) * (SHIFT ? 2ull : 1ull) < 4000000000ull ? 1u : 0u;
+            }
+            __syncthreads();
+            return misc[1] != 0u;
+        };
+        if (P.pass == 0) {
+            if (!fits32(groups)) continue;
+        } else {
+            if (fits32(P.groups0)) continue;
+            __syncthreads();
+            chunk_bounds(groups);
         }
         for (int tb = 0; tb < ntiles; tb += tpb) {
             const int bt = min(tpb, ntiles - tb);
@@ -1737,6 +1765,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         }
         wp.tiles_per_batch = tpb;
         wp.groups = groups;
+        if (pass == 0) wp.groups0 = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
         const size_t smem = walk_fixed + per_tile * tpb * copies;
         SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
         const int grid = (int)std::min<int64_t>(ntasks, smem * 2 <= ctx->smem_optin ? walk_grid_max : ctx->sm_count);
