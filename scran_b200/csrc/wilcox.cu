@@ -1008,6 +1008,7 @@ struct WalkParams {
     int pass;             // 0: everything with m <= 65536 (uint32 tables); 1: only m > 65536 (uint64 tables)
     const int32_t* nbig;  // number of large single-unit jobs at the head of `order`
     uint32_t big_total;   // a unit with more entries than this is "large": walked by a whole CTA
+    int hist_groups;      // large-unit kernel: rows of per-chunk counts kept in shared memory
     int groups0;          // large-unit kernel: position chunks of the 32-bit pass (the 64-bit pass needs them to tell its units)
     int shared_table;     // large-unit kernel: the position chunks add into ONE table (32-bit cells, atomic adds)
     int by_task;          // large-unit kernel: walk EVERY unit (used when the per-warp mode has no room for its tables)
@@ -1293,8 +1294,9 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
     constexpr int W = 32 * J;  // labels per warp
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Gmax1 = P.maxG + 1;
-    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [2 * WALK_MAX_GROUPS (+1)][Gmax1]: per-chunk counts, counted / adding role
-    uint32_t* nnzv = hist + (size_t)(2 * WALK_MAX_GROUPS) * Gmax1;           // [Gmax1]
+    const int HG = P.hist_groups;  // chunk rows kept: enough for the groups of either pass
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [2 * HG][Gmax1]: per-chunk counts, counted / adding role
+    uint32_t* nnzv = hist + (size_t)(2 * HG) * Gmax1;                         // [Gmax1]
     int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);                      // [WALK_MAX_GROUPS + 1]
     uint32_t* misc = reinterpret_cast<uint32_t*>(bounds + WALK_MAX_GROUPS + 1);  // [4]
     size_t off = (size_t)((unsigned char*)(misc + 4) - smem_raw);
@@ -1379,7 +1381,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
                 const int R0 = tile * W + lane;
                 walk_range<AccT, SHIFT, J>(st, bounds[cg], bounds[cg + 1], R0,
                                            acc + (size_t)(P.shared_table ? 0 : cg) * Gt * rpad + (R0 - tb * W), rpad, hist + cg * Gmax1,
-                                           hist + (WALK_MAX_GROUPS + cg) * Gmax1, Gt, lane);
+                                           hist + (HG + cg) * Gmax1, Gt, lane);
             }
             __syncthreads();
             for (int k = tid; k < Gt * (int)rpad; k += blockDim.x) {
@@ -1396,7 +1398,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         // add to cell (L, R) is (entries of L in the chunk, adding role) x (entries of R before the
         // chunk, counted role) -- twice that with a shift, where an adding entry takes the count
         // before its run plus the count after it. The walkers left both per-chunk counts in `hist`.
-        uint32_t* hist_l = hist + (size_t)WALK_MAX_GROUPS * Gmax1;
+        uint32_t* hist_l = hist + (size_t)HG * Gmax1;
         for (int R = tid; R < Gt; R += blockDim.x) {
             uint32_t run = 0;
             for (int cg = 0; cg < groups; ++cg) {
@@ -1683,7 +1685,8 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     const int J = narrow_tiles <= 1 ? 1 : narrow_tiles <= 2 ? 2 : narrow_tiles <= 4 ? 4 : 8;
     const int W = 32 * J;
     const int ntiles = (Gt + W - 1) / W;  // wide tiles = warps per unit
-    const size_t walk_fixed = ((size_t)(2 * WALK_MAX_GROUPS) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32;
+    // fixed part of the large-unit kernel's shared memory, with rows for hg chunk groups
+    auto walk_fixed_for = [&](int hg) { return ((size_t)(2 * hg) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32; };
     const int walk_grid_max = ctx->sm_count * 2;
     ctx->plan_tmp.reserve((size_t)walk_grid_max * Gt * Gt * 8 + 64);
     wp.bfull = ctx->plan_tmp.as<unsigned long long>();
@@ -1734,14 +1737,23 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         const size_t acc_size = pass == 0 ? 4 : 8;
         if (pass == 1 && max_m <= 65536) break;
         wp.pass = pass;
-        if (walk_fixed > ctx->smem_optin) throw Error("too many groups inside one block for the shared-memory count table");
-        const size_t budget = ctx->smem_optin - walk_fixed;
         // Labels per warp for this pass: the widest tile (fewest decodes of an entry) whose tiles all fit
         // shared memory at once, so that the stream is walked once; with hundreds of groups the
         // padding of wide tiles decides (201 labels: seven tiles of 32 fit, one tile of 256 does not).
         // If not even the narrow tiles fit together (64-bit counts), they are walked in batches.
+        // Chunk groups never exceed the warps left per tile, which bounds the per-chunk count rows.
         int Jp = J;
-        while (Jp > 1 && (size_t)Gt * 32 * Jp * acc_size * ((Gt + 32 * Jp - 1) / (32 * Jp)) > budget) Jp >>= 1;
+        auto groups_max = [&](int jj) { return std::max(1, std::min(WALK_MAX_GROUPS, WALK_WARPS / std::min((Gt + 32 * jj - 1) / (32 * jj), WALK_WARPS))); };
+        auto all_fit = [&](int jj) {
+            const size_t need = (size_t)Gt * 32 * jj * acc_size * ((Gt + 32 * jj - 1) / (32 * jj)) + walk_fixed_for(groups_max(jj));
+            return need <= ctx->smem_optin;
+        };
+        while (Jp > 1 && !all_fit(Jp)) Jp >>= 1;
+        const int hist_groups = groups_max(Jp);
+        wp.hist_groups = hist_groups;
+        const size_t walk_fixed = walk_fixed_for(hist_groups);
+        if (walk_fixed > ctx->smem_optin) throw Error("too many groups inside one block for the shared-memory count table");
+        const size_t budget = ctx->smem_optin - walk_fixed;
         const int Wp = 32 * Jp, ntiles_p = (Gt + Wp - 1) / Wp;
         const size_t per_tile = (size_t)Gt * Wp * acc_size;
         if (per_tile > budget) throw Error("too many groups inside one block for the shared-memory count table");
@@ -1752,9 +1764,9 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
             tpb = std::min(ntiles_p, WALK_WARPS);
             if (pass == 0) {  // 32-bit cells take atomic adds: every warp walks a position chunk into one shared table
                 wp.shared_table = 1;
-                groups = std::max(1, std::min(WALK_MAX_GROUPS, WALK_WARPS / std::max(1, tpb)));
+                groups = std::max(1, std::min(hist_groups, WALK_WARPS / std::max(1, tpb)));
             } else {
-                groups = (int)std::min<size_t>(budget / (per_tile * ntiles_p), (size_t)WALK_MAX_GROUPS);
+                groups = (int)std::min<size_t>(budget / (per_tile * ntiles_p), (size_t)hist_groups);
                 groups = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
                 copies = groups;
             }
