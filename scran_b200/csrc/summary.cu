@@ -91,7 +91,41 @@ __global__ void __launch_bounds__(SUM_WARPS * 32) k5_summaries(SumParams P) {
         cnt = __shfl_sync(0xffffffffu, cnt, 0);
         // Median by rank counting: entry i has rank #(x_j < x_i) + #(x_j == x_i, j < i).
         double med_lo = nan, med_hi = nan;
-        if (cnt > 0) {
+        if (cnt > 0 && nr > 64) {
+            // Many comparisons: rank counting is quadratic. Bisect on the order-preserving key instead:
+            // the smallest key with at least r_lo + 1 values at or below it is the lower median.
+            const int r_lo = (cnt - 1) / 2, r_hi = cnt / 2;
+            mn = __shfl_sync(0xffffffffu, mn, 0);
+            mx = __shfl_sync(0xffffffffu, mx, 0);
+            unsigned long long* kv = reinterpret_cast<unsigned long long*>(v);
+            for (int j = lane; j < nr; j += 32) {
+                const double x = v[j];
+                kv[j] = isnan(x) ? ~0ull : key_of(x);  // NaN: above every key that is tried
+            }
+            __syncwarp();
+            unsigned long long lo = key_of(mn), hi = key_of(mx);
+            while (lo < hi) {
+                const unsigned long long mid = lo + ((hi - lo) >> 1);
+                int c = 0;
+                for (int j = lane; j < nr; j += 32) c += kv[j] <= mid ? 1 : 0;
+                c = __reduce_add_sync(0xffffffffu, c);
+                if (c >= r_lo + 1) hi = mid; else lo = mid + 1;
+            }
+            int c_le = 0;
+            unsigned long long next = ~0ull;  // smallest key above the lower median
+            for (int j = lane; j < nr; j += 32) {
+                const unsigned long long kj = kv[j];
+                c_le += kj <= lo ? 1 : 0;
+                if (kj > lo && kj < next) next = kj;
+            }
+            c_le = __reduce_add_sync(0xffffffffu, c_le);
+            for (int o = 16; o > 0; o >>= 1) {
+                const unsigned long long a = __shfl_xor_sync(0xffffffffu, next, o);
+                next = a < next ? a : next;
+            }
+            med_lo = value_of(lo);
+            med_hi = c_le >= r_hi + 1 ? med_lo : value_of(next);
+        } else if (cnt > 0) {
             const int r_lo = (cnt - 1) / 2, r_hi = cnt / 2;
             for (int i = lane; i < nr; i += 32) {
                 const double xi = v[i];

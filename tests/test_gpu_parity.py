@@ -327,6 +327,18 @@ def test_score_markers_many_groups(sb):
     assert_tables_match(got, want)
 
 
+def test_score_markers_seventy_groups(sb):
+    """More than 64 comparisons per group: the medians come from a bisection on the value keys; also
+    even / odd counts of defined comparisons (a group of one cell makes Cohen's d undefined)."""
+    x = make_matrix(60, 2100, seed=108, rate=0.8)
+    x[3] = 0.0                      # every effect of this gene ties
+    groups = np.random.default_rng(7).integers(0, 70, 2100)
+    groups[groups == 69] = 68       # 69 groups: 68 comparisons each
+    groups[0] = 69                  # ... and one group with a single cell
+    got, want = _score_both(sb, x, groups)
+    assert_tables_match(got, want)
+
+
 def test_score_markers_one_cell_groups(sb):
     """A group with a single cell: variance NA, so Cohen's d is NA unless the difference is 0
     (R/scoreMarkers.R:417-426); AUC and logFC.detected stay defined."""
