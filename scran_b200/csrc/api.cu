@@ -11,10 +11,23 @@ namespace sb {
 static thread_local std::string g_last_error;
 void set_last_error(const std::string& m) { g_last_error = m; }
 
+static thread_local scranb200_ctx* g_current_ctx = nullptr;
+
 void ctx_guard(scranb200_ctx* ctx) {
     if (!ctx) throw Error("null context");
     if (ctx->owner != getpid()) throw Error("this context was created in another process (fork); create a new one");
     SB_CUDA(cudaSetDevice(ctx->device));
+    g_current_ctx = ctx;
+}
+
+// Called by DevBuf::reserve when cudaMalloc fails: give back the spare matrix arrays of the context
+// this thread is working for; true if there was anything to give back.
+bool release_spares_current() {
+    scranb200_ctx* ctx = g_current_ctx;
+    if (!ctx || ctx->spare.empty()) return false;
+    for (auto& sp : ctx->spare) cudaFree(sp.p);
+    ctx->spare.clear();
+    return true;
 }
 
 void phase_collect(scranb200_ctx* ctx) {
@@ -33,10 +46,32 @@ void phase_collect(scranb200_ctx* ctx) {
 
 namespace {
 
+// Device array for an uploaded matrix: a spare one of a fitting size if the context has it, else a
+// new allocation (after giving the spares back if memory is short).
 template <typename T>
-T* dev_alloc(size_t n) {
+T* dev_alloc(scranb200_ctx* ctx, size_t n, size_t& bytes_out) {
+    const size_t need = std::max<size_t>(n, 1) * sizeof(T);
+    int best = -1;
+    for (int k = 0; k < (int)ctx->spare.size(); ++k) {
+        const size_t have = ctx->spare[k].bytes;
+        if (have >= need && have <= need + need / 4 + (1u << 20) && (best < 0 || have < ctx->spare[best].bytes)) best = k;
+    }
+    if (best >= 0) {
+        void* p = ctx->spare[best].p;
+        bytes_out = ctx->spare[best].bytes;
+        ctx->spare.erase(ctx->spare.begin() + best);
+        return reinterpret_cast<T*>(p);
+    }
     void* p = nullptr;
-    SB_CUDA(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        for (auto& sp : ctx->spare) cudaFree(sp.p);
+        ctx->spare.clear();
+        e = cudaMalloc(&p, need);
+    }
+    SB_CUDA(e);
+    bytes_out = need;
     return reinterpret_cast<T*>(p);
 }
 
@@ -109,8 +144,8 @@ scranb200_mat* new_mat(scranb200_ctx* ctx, int64_t nrow, int64_t ncol) {
 }
 
 void finish_upload(scranb200_ctx* ctx, scranb200_mat* m, const int32_t* i, const double* x) {
-    m->d_i = dev_alloc<int32_t>(m->nnz);
-    m->d_x = dev_alloc<double>(m->nnz);
+    m->d_i = dev_alloc<int32_t>(ctx, m->nnz, m->bytes_i);
+    m->d_x = dev_alloc<double>(ctx, m->nnz, m->bytes_x);
     if (m->nnz > 0) {
         SB_CUDA(cudaMemcpyAsync(m->d_i, i, (size_t)m->nnz * 4, cudaMemcpyHostToDevice, ctx->stream));
         SB_CUDA(cudaMemcpyAsync(m->d_x, x, (size_t)m->nnz * 8, cudaMemcpyHostToDevice, ctx->stream));
@@ -259,6 +294,8 @@ void scranb200_ctx_destroy(scranb200_ctx* ctx) {
                               &ctx->out, &ctx->minrank, &ctx->rank_keys, &ctx->rank_idx, &ctx->plan_tmp, &ctx->io_a,
                               &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit, &ctx->jobs, &ctx->split, &ctx->vmin, &ctx->vmax};
         for (sb::DevBuf* b : bufs) b->release();
+        for (auto& sp : ctx->spare) cudaFree(sp.p);
+        ctx->spare.clear();
         for (int k = 0; k < 16; ++k) {
             if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
         }
@@ -291,7 +328,7 @@ int scranb200_upload_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const i
     scranb200_mat* m = new_mat(ctx, nrow, ncol);
     m->nnz = p[ncol];
     if (m->nnz < 0) throw Error("negative number of stored entries");
-    m->d_p = dev_alloc<int64_t>(ncol + 1);
+    m->d_p = dev_alloc<int64_t>(ctx, ncol + 1, m->bytes_p);
     SB_CUDA(cudaMemcpyAsync(m->d_p, p, (size_t)(ncol + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
     finish_upload(ctx, m, i, x);
     *out = m;
@@ -305,7 +342,7 @@ int scranb200_upload_csc32(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const
     scranb200_mat* m = new_mat(ctx, nrow, ncol);
     m->nnz = p[ncol];
     if (m->nnz < 0) throw Error("negative number of stored entries");
-    m->d_p = dev_alloc<int64_t>(ncol + 1);
+    m->d_p = dev_alloc<int64_t>(ctx, ncol + 1, m->bytes_p);
     ctx->io_a.reserve((size_t)(ncol + 1) * 4);
     SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, p, (size_t)(ncol + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
     SB_LAUNCH(ctx, widen_i32, (unsigned)ceil_div(ncol + 1, 256), 256, 0, ctx->io_a.as<int32_t>(), ncol + 1, m->d_p);
@@ -322,7 +359,7 @@ int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const
     ctx->io_a.reserve(std::max<size_t>(cells, 1) * 8);
     ctx->io_b.reserve((size_t)(ncol + 1) * 8);
     if (cells) SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, x, cells * 8, cudaMemcpyHostToDevice, ctx->stream));
-    m->d_p = dev_alloc<int64_t>(ncol + 1);
+    m->d_p = dev_alloc<int64_t>(ctx, ncol + 1, m->bytes_p);
     if (ncol > 0) {
         SB_LAUNCH(ctx, dense_count, (unsigned)ceil_div(ncol * 32, 256), 256, 0, ctx->io_a.as<double>(), nrow, ncol,
                   ctx->io_b.as<int64_t>());
@@ -330,8 +367,8 @@ int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const
     SB_LAUNCH(ctx, scan_i64, 1, 1024, 0, ctx->io_b.as<int64_t>(), ncol, m->d_p);
     SB_CUDA(cudaMemcpyAsync(&m->nnz, m->d_p + ncol, 8, cudaMemcpyDeviceToHost, ctx->stream));
     SB_CUDA(cudaStreamSynchronize(ctx->stream));
-    m->d_i = dev_alloc<int32_t>(m->nnz);
-    m->d_x = dev_alloc<double>(m->nnz);
+    m->d_i = dev_alloc<int32_t>(ctx, m->nnz, m->bytes_i);
+    m->d_x = dev_alloc<double>(ctx, m->nnz, m->bytes_x);
     if (ncol > 0 && m->nnz > 0) {
         SB_LAUNCH(ctx, dense_fill, (unsigned)ceil_div(ncol * 32, 256), 256, 0, ctx->io_a.as<double>(), nrow, ncol, m->d_p,
                   m->d_i, m->d_x);
@@ -359,9 +396,15 @@ void scranb200_mat_free(scranb200_mat* mat) {
     if (!mat) return;
     if (mat->owned && mat->ctx && mat->ctx->owner == getpid()) {
         cudaSetDevice(mat->ctx->device);
-        cudaFree(mat->d_p);
-        cudaFree(mat->d_i);
-        cudaFree(mat->d_x);
+        // kept for the next upload; at most two matrices' worth
+        scranb200_ctx* ctx = mat->ctx;
+        void* ptrs[3] = {mat->d_p, mat->d_i, mat->d_x};
+        const size_t sizes[3] = {mat->bytes_p, mat->bytes_i, mat->bytes_x};
+        for (int k = 0; k < 3; ++k) {
+            if (!ptrs[k]) continue;
+            if (sizes[k] > 0 && ctx->spare.size() < 6) ctx->spare.push_back({ptrs[k], sizes[k]});
+            else cudaFree(ptrs[k]);
+        }
     }
     delete mat;
 }

@@ -29,6 +29,8 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 }
 #define SB_CUDA(x) ::sb::cuda_check((x), #x, __FILE__, __LINE__)
 
+bool release_spares_current();  // api.cu
+
 // A device allocation that only ever grows; contexts keep a few of these so that repeated
 // calls of the same shape do not go back to cudaMalloc.
 struct DevBuf {
@@ -40,7 +42,12 @@ struct DevBuf {
         p = nullptr;
         cap = 0;
         size_t want = bytes + (bytes >> 4) + 256;
-        SB_CUDA(cudaMalloc(&p, want));
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaErrorMemoryAllocation && release_spares_current()) {
+            cudaGetLastError();
+            e = cudaMalloc(&p, want);
+        }
+        SB_CUDA(e);
         cap = want;
     }
     void release() {
@@ -73,6 +80,13 @@ struct scranb200_ctx {
     sb::DevBuf table, seg_off, row_total, row_ptr, vals, stream_lab, unit_m, sort_keys, sort_labs, flags;
     sb::DevBuf mean, var, ndet, u_pairs, t_pairs, layout_i32, layout_f64;
     sb::DevBuf eff, out, minrank, rank_keys, rank_idx, plan_tmp, io_a, io_b, io_c, grp_avg, logit, jobs, split, vmin, vmax;
+    // device arrays of freed matrices, kept for the next upload of a similar size (cudaMalloc / cudaFree of
+    // tens of gigabytes costs as much as a tenth of the transfer itself)
+    struct Spare {
+        void* p;
+        size_t bytes;
+    };
+    std::vector<Spare> spare;
 };
 
 struct scranb200_mat {
@@ -81,6 +95,7 @@ struct scranb200_mat {
     int64_t* d_p = nullptr;
     int32_t* d_i = nullptr;
     double* d_x = nullptr;
+    size_t bytes_p = 0, bytes_i = 0, bytes_x = 0;  // allocation sizes (owned matrices)
     bool owned = false;
 };
 
