@@ -331,8 +331,18 @@ def main():
         gbs = (pb[k] / world) / (ms * 1e-3) / 1e9 if ms > 0 else None
         kernels[k] = {"ms": round(ms, 4), "alg_bytes": int(pb[k] / world),
                       "gbs": None if gbs is None else round(gbs, 1), "frac": None if gbs is None else round(gbs / peak, 4)}
+    # DRAM bytes of the dominant phase per step, from the committed ncu capture of this very workload
+    # (profiles/r01_dram_<workload>_n<N>.json); null when no capture exists for it
+    traffic = traffic_src = None
+    try:
+        cap = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
+                                          "r01_dram_%s_n%d.json" % (args.workload, world))))
+        traffic = int(cap["phase_bytes"][dom])
+        traffic_src = cap["source"]
+    except (OSError, KeyError, ValueError):
+        pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",
-                "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                "frac": kernels[dom]["frac"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "pipeline_alg_bytes": int(algorithmic_bytes(w, nnz, P, plan.K)),
                 "pipeline_frac": round(algorithmic_bytes(w, nnz, P, plan.K) / (ms_step * 1e-3) / 1e9 / (peak * world), 4)}
 
