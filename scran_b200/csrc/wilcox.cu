@@ -224,7 +224,8 @@ struct SortSmem {
     uint32_t* n;         // MAXB
     int64_t* vbase;      // MAXB
     int64_t* soff;       // MAXB: stream position of the segment's first entry
-    double* fmin;        // MAXB: value range of the segment -> bucket = (v - fmin) * scale
+    double* fmin;        // MAXB: value range of the segment (ValueMap)
+    double* fmax;        // MAXB
     double* scale;       // MAXB
     uint32_t* boff;      // 258: bucket offsets of the value partition
     unsigned long long* bmin;  // 2: smallest / largest key of a bucket that takes the radix fallback
@@ -237,7 +238,7 @@ struct SortSmem {
 constexpr int BUCKET_RANK_MAX = 32;  // buckets up to this size are ranked by all-pairs counting
 
 constexpr size_t sort_fixed_bytes(int cap, int segcap) {
-    return (size_t)(segcap + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 2 + (size_t)MAXB * 8 * 4 + 2 * 8 +
+    return (size_t)(segcap + MAXB + 8) * 4 + (size_t)(MAXB + 1) * 4 * 2 + (size_t)MAXB * 4 * 2 + (size_t)MAXB * 8 * 5 + 2 * 8 +
            258 * 4 + 256 * 4 + (size_t)(cap / BUCKET_RANK_MAX + 2) * 4 + 40 * 4 + 16 * 4 + 128;
 }
 
@@ -251,7 +252,8 @@ __device__ inline SortSmem carve_sort_smem(unsigned char* raw, int cap, int segc
     s.vbase = reinterpret_cast<int64_t*>(p);
     s.soff = s.vbase + MAXB;
     s.fmin = reinterpret_cast<double*>(s.soff + MAXB);
-    s.scale = s.fmin + MAXB;
+    s.fmax = s.fmin + MAXB;
+    s.scale = s.fmax + MAXB;
     s.bmin = reinterpret_cast<unsigned long long*>(s.scale + MAXB);
     s.seg = reinterpret_cast<uint32_t*>(s.bmin + 2);
     s.segptr = s.seg + (segcap + MAXB + 8);
@@ -288,10 +290,20 @@ __device__ inline void unit_key(const double* __restrict__ vals, int64_t vbase, 
 // Monotone in the value, so the buckets are ordered and equal values share a bucket; values outside
 // the range (the probes) clamp to the ends; dropped entries go to the last bucket, where their
 // all-ones key sorts them last.
-__device__ __forceinline__ unsigned value_bucket(uint64_t key, bool keep, double fmin, double scale, unsigned nbuckets) {
-    // the conversion saturates: below the range (and NaN) -> 0, far above -> 2^32 - 1
-    const unsigned b = __double2uint_rz((value_of(key) - fmin) * scale);
-    return keep ? min(b, nbuckets - 1u) : nbuckets - 1u;
+struct ValueMap {
+    double fmin, fmax;  // range of the stored non-zero values (both roles), probes excluded
+    double scale;       // (nbuckets - 2) / (fmax - fmin); 0 if there is one value only
+};
+// The first and the last bucket are kept for what lies outside the range: the probes (0, -lfc) and the
+// dropped entries. Otherwise a probe would share the bucket of the smallest values, and with
+// integer-valued data that bucket (thousands of copies of one value) would no longer be uniform.
+__device__ __forceinline__ unsigned value_bucket(uint64_t key, bool keep, const ValueMap& vm, unsigned nbuckets) {
+    if (!keep) return nbuckets - 1u;
+    if (nbuckets < 3u) return 0u;
+    const double v = value_of(key);
+    if (v < vm.fmin) return 0u;
+    if (v > vm.fmax) return nbuckets - 1u;
+    return 1u + min(__double2uint_rz((v - vm.fmin) * vm.scale), nbuckets - 3u);  // the conversion saturates
 }
 
 // Segment of compact element / bucket index p: last s with off[s] <= p.
@@ -362,19 +374,28 @@ struct ScratchRun {
     uint32_t start;  // position of the run inside the unit (= its first fine bucket)
     uint32_t lim;    // entries of the run that belong to the stream (the stored zeros at the very end do not)
     int64_t out;     // stream position of the run's first entry
-    double fmin, scale;  // the unit's coarse bucket map
+    ValueMap vm;     // the unit's coarse bucket map (256 buckets)
 };
 
 // Fine bucket of a key inside a large unit: coarse bucket d (256 of equal width over the unit's value
 // range, the same expression as the split used) is divided into as many fine buckets as it has
 // elements, so the fine buckets follow the density of the values and number exactly the unit's
 // elements: fine = boff[d] + floor(frac * count_d). Monotone in the value.
-__device__ __forceinline__ uint32_t fine_bucket(uint64_t key, const uint32_t* boff, double fmin, double scale) {
+__device__ __forceinline__ uint32_t fine_bucket(uint64_t key, const uint32_t* boff, const ValueMap& vm) {
     if (key == ~0ull) return boff[256] - 1u;  // stored zeros: the very last bucket
-    const double x = (value_of(key) - fmin) * scale;
-    const uint32_t d = min(__double2uint_rz(x), 255u);
+    const double v = value_of(key);
+    uint32_t d = 0;
+    double frac = 0.0;
+    if (v > vm.fmax) {
+        d = 255u;
+    } else if (!(v < vm.fmin)) {  // the same expression as value_bucket(..., 256)
+        const double x = (v - vm.fmin) * vm.scale;
+        const uint32_t di = min(__double2uint_rz(x), 253u);
+        d = 1u + di;
+        frac = x - (double)di;
+    }
     const uint32_t lo = boff[d], c = boff[d + 1] - lo;
-    return lo + min(__double2uint_rz((x - (double)d) * (double)c), c - 1u);
+    return lo + min(__double2uint_rz(frac * (double)c), c - 1u);
 }
 
 template <bool SCRATCH>
@@ -407,7 +428,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
-                    if (valid[q]) body(key[q], lab[q], key[q] != ~0ull, fine_bucket(key[q], S.boff, run.fmin, run.scale) - run.start, 0);
+                    if (valid[q]) body(key[q], lab[q], key[q] != ~0ull, fine_bucket(key[q], S.boff, run.vm) - run.start, 0);
             }
         } else {
             if (c_lo >= c_hi) return;
@@ -420,7 +441,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                 const double* vals = P.vals + S.vbase[s];
                 const uint32_t* segb = S.seg + S.segptr[s];
                 const uint32_t G = S.segptr[s + 1] - S.segptr[s] - 1u;
-                const double fmin = S.fmin[s], scale = S.scale[s];
+                const ValueMap vm = {S.fmin[s], S.fmax[s], S.scale[s]};
                 const uint32_t el_lo = pos - off_lo, el_hi = min(c_hi, off_hi) - off_lo;
                 for (int role = 0; role < (two_roles ? 2 : 1); ++role) {
                     // this role's part of the unit's list: n values, then the probe
@@ -448,14 +469,14 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                                 }
                                 const double vv = role ? v[q] - P.shift : v[q];
                                 const uint64_t key = keep ? key_of(vv) : ~0ull;
-                                body(key, lab | rolebit, keep, off_lo + value_bucket(key, keep, fmin, scale, cnt), s);
+                                body(key, lab | rolebit, keep, off_lo + value_bucket(key, keep, vm, cnt), s);
                             }
                         }
                     }
                     if (part_hi - base == n + 1u && lane == 0) {  // the probe: 0, or 0 - lfc in the L role
                         const double vv = role ? 0.0 - P.shift : 0.0;
                         const uint64_t key = key_of(vv);
-                        body(key, G | rolebit, true, off_lo + value_bucket(key, true, fmin, scale, cnt), s);
+                        body(key, G | rolebit, true, off_lo + value_bucket(key, true, vm, cnt), s);
                     }
                 }
                 pos = off_lo + el_hi;
@@ -559,7 +580,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     if constexpr (SCRATCH) {
         for (uint32_t p = c_lo + lane; p < c_hi; p += 32) {
             const uint64_t key = S.key[p];
-            rank_element(p, key, fine_bucket(key, S.boff, run.fmin, run.scale) - run.start, 0u, run.lim, run.out);
+            rank_element(p, key, fine_bucket(key, S.boff, run.vm) - run.start, 0u, run.lim, run.out);
         }
     } else if (c_lo < c_hi) {
         int s = find_segment(S.off, nb, c_lo);
@@ -567,13 +588,13 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
         while (pos < c_hi) {
             while (pos >= S.off[s + 1]) ++s;
             const uint32_t off_lo = S.off[s], off_hi = S.off[s + 1], cnt = off_hi - off_lo;
-            const double fmin = S.fmin[s], scale = S.scale[s];
+            const ValueMap vm = {S.fmin[s], S.fmax[s], S.scale[s]};
             const uint32_t lim = cnt - S.drop[s];
             const int64_t out = S.soff[s];
             const uint32_t hi = min(c_hi, off_hi);
             for (uint32_t p = pos + lane; p < hi; p += 32) {
                 const uint64_t key = S.key[p];
-                rank_element(p, key, off_lo + value_bucket(key, key != ~0ull, fmin, scale, cnt), off_lo, lim, out);
+                rank_element(p, key, off_lo + value_bucket(key, key != ~0ull, vm, cnt), off_lo, lim, out);
             }
             pos = hi;
         }
@@ -720,8 +741,10 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
             }
             if (lane == 0) {
                 const uint32_t cnt = S.off[s + 1] - S.off[s];
-                S.fmin[s] = fmax > fmin ? fmin : 0.0;
-                S.scale[s] = fmax > fmin ? (double)cnt / (fmax - fmin) : 0.0;
+                if (!(fmin <= fmax)) fmin = fmax = 0.0;  // no stored non-zero value at all
+                S.fmin[s] = fmin;
+                S.fmax[s] = fmax;
+                S.scale[s] = fmax > fmin && cnt >= 3u ? (double)(cnt - 2u) / (fmax - fmin) : 0.0;
                 if (nb == 1) {  // the plain range, for the 256-way split of a unit beyond the capacity
                     double* red = reinterpret_cast<double*>(S.scan);
                     red[0] = fmin;
@@ -750,7 +773,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         uint64_t* gb = P.g_kb + soff;
         uint32_t* gq = P.g_pb + soff;
         const double fmin = reinterpret_cast<double*>(S.scan)[0], fmax = reinterpret_cast<double*>(S.scan)[1];
-        const double scale = fmax > fmin ? 256.0 / (fmax - fmin) : 0.0;
+        const ValueMap vm256 = {fmin, fmax, fmax > fmin ? 254.0 / (fmax - fmin) : 0.0};
         if (tid == 0) S.misc[3] = 0;  // dropped (stored zero) entries, counted in pass 1
         __syncthreads();
 
@@ -775,7 +798,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     if (valid[q]) {
-                        const unsigned d = value_bucket(key[q], keep[q], fmin, scale, 256u);
+                        const unsigned d = value_bucket(key[q], keep[q], vm256, 256u);
                         atomicAdd(&S.gcur[d], 1u);
                         ndrop += keep[q] ? 0u : 1u;
                     }
@@ -850,7 +873,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         if (valid[q]) {
-                            const unsigned d = value_bucket(key[q], keep[q], fmin, scale, 256u);
+                            const unsigned d = value_bucket(key[q], keep[q], vm256, 256u);
                             const uint32_t dst = atomicAdd(&S.gcur[d], 1u);
                             ga[dst] = key[q];
                             gp[dst] = lab[q];
@@ -884,8 +907,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 run.start = start;
                 run.lim = m > start ? min(cnt, m - start) : 0u;
                 run.out = soff + start;
-                run.fmin = fmin;
-                run.scale = scale;
+                run.vm = vm256;
                 bucket_sort_job<true>(P, S, 1, cnt, ga + start, gp + start, run);
                 continue;
             }
