@@ -19,6 +19,8 @@ namespace {
 
 constexpr int K1_THREADS = 1024;
 constexpr int K1_R = 3;          // elements per thread held in registers per column (covers 3072 per column)
+constexpr int K1_SUB_SHIFT = 8;  // gene sub-ranges of 256: one scatter warp each
+constexpr int K1_SUB = 1 << K1_SUB_SHIFT;
 constexpr int K1_MAXCOLS = MAX_CHUNK_COLS;  // columns per chunk (their bounds are staged in shared memory)
 
 // A column's first K1_R * K1_THREADS entries, prefetched into registers while earlier columns
@@ -68,7 +70,7 @@ __device__ inline int stage_bounds(const int64_t* __restrict__ p, const int32_t*
 __global__ void __launch_bounds__(K1_THREADS)
 k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const int32_t* __restrict__ perm,
          const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen, uint32_t* __restrict__ table,
-         int* __restrict__ bad) {
+         int* __restrict__ bad, uint32_t* __restrict__ sub_split, int nsub) {
     extern __shared__ __align__(16) unsigned char k1_smem[];
     int64_t* s_lo = reinterpret_cast<int64_t*>(k1_smem);
     int* s_n = reinterpret_cast<int*>(s_lo + K1_MAXCOLS);
@@ -83,6 +85,13 @@ k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
     for (int j = warp; j < ncols; j += nwarps) {
         const int64_t lo = s_lo[j];
         const int n = s_n[j];
+        // sub_split (optional): for the column at permuted position c_lo + j, where the entries with
+        // gene >= r * K1_SUB start, r = 0 .. nsub: the rows are sorted, so the boundaries are where the
+        // sub-range of an entry differs from that of its left neighbour
+        uint32_t* srow = sub_split ? sub_split + (size_t)(c_lo + j) * (nsub + 1) : nullptr;
+        if (srow && n == 0) {
+            for (int r = lane; r <= nsub; r += 32) srow[r] = 0u;
+        }
         for (int k0 = 0; k0 < n; k0 += 128) {  // four loads in flight per lane
             int g[4];
 #pragma unroll
@@ -103,6 +112,13 @@ k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
                     } else {
                         const unsigned gl = (unsigned)(g[q] - g0);
                         if (gl < (unsigned)glen) atomicAdd(&cnt[gl], 1u);
+                        const int sub = g[q] >> K1_SUB_SHIFT, sub_prev = prev >> K1_SUB_SHIFT;  // (-1 >> s = -1)
+                        if (srow && (sub != sub_prev || k == n - 1)) {
+                            for (int r = sub_prev + 1; r <= sub; ++r) srow[r] = (uint32_t)k;
+                            if (k == n - 1) {
+                                for (int r = sub + 1; r <= nsub; ++r) srow[r] = (uint32_t)n;
+                            }
+                        }
                     }
                 }
             }
@@ -309,6 +325,111 @@ k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const
     }
 }
 
+// Pass B, one warp per (chunk, sub-range of K1_SUB genes). A gene's entries must be appended in
+// column order, but different gene ranges are independent of each other: with the positions where
+// every sub-range starts inside every column (sub_split, written by the counting pass) a warp can
+// walk the chunk's columns on its own, one short slice (its genes' entries of that column) a step,
+// with no barrier shared with other warps. The slices of the next columns are fetched while the
+// current one is applied (K1W_DEPTH in flight). Per gene the write cursor and the last up-to-4 values
+// are staged in shared memory, so that HBM sees whole 32-byte sectors, as in k1_scatter.
+constexpr int K1W_WARPS = 4;
+constexpr int K1W_DEPTH = 8;
+
+__global__ void __launch_bounds__(K1W_WARPS * 32)
+k1_scatter_warp(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
+                const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int nsub,
+                const uint32_t* __restrict__ sub_split, const uint32_t* __restrict__ table,
+                const int64_t* __restrict__ row_ptr, double* __restrict__ vals) {
+    __shared__ double s_stage[K1W_WARPS][K1_SUB * 4];
+    __shared__ uint32_t s_cursor[K1W_WARPS][K1_SUB], s_first[K1W_WARPS][K1_SUB];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int blocks_per_chunk = (nsub + K1W_WARPS - 1) / K1W_WARPS;
+    const int chunk = blockIdx.x / blocks_per_chunk, sr = (blockIdx.x % blocks_per_chunk) * K1W_WARPS + warp;
+    if (sr >= nsub) return;  // (no block-wide barrier anywhere in this kernel)
+    double* stage = s_stage[warp];
+    uint32_t* cursor = s_cursor[warp];
+    uint32_t* first = s_first[warp];
+    const int g0 = sr * K1_SUB, glen = min(K1_SUB, ngenes - g0);
+    for (int g = lane; g < glen; g += 32) {
+        const uint32_t at = (uint32_t)(row_ptr[g0 + g] + table[(size_t)chunk * ngenes + g0 + g]);
+        cursor[g] = at;
+        first[g] = at;
+    }
+    __syncwarp();
+    const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
+    const int ncols = c_hi - c_lo;
+
+    auto put = [&](int g, double v) {
+        const unsigned gl = (unsigned)(g - g0);
+        if (gl >= (unsigned)glen) return;  // only reachable with an invalid (unsorted) matrix, reported by pass A
+        const uint32_t at = cursor[gl];
+        cursor[gl] = at + 1;
+        double* sg = stage + (size_t)gl * 4;
+        sg[at & 3u] = v;
+        if ((at & 3u) == 3u) {
+            const uint32_t base = at - 3u, f = first[gl];
+            if (base >= f) {  // a whole 32-byte sector
+                double2* dst = reinterpret_cast<double2*>(vals + base);
+                dst[0] = make_double2(sg[0], sg[1]);
+                dst[1] = make_double2(sg[2], v);
+            } else {          // the sector started in an earlier chunk: write only our part
+                for (uint32_t s = f; s < at; ++s) vals[s] = sg[s & 3u];
+                vals[at] = v;
+            }
+        }
+    };
+    struct Slice {
+        int32_t g;
+        double v;
+        int64_t lo;
+        int n;
+    };
+    for (int j0 = 0; j0 < ncols; j0 += 32) {
+        // bounds of my sub-range inside the next 32 columns: one column per lane
+        int64_t my_lo = 0;
+        int my_n = 0;
+        if (j0 + lane < ncols) {
+            const int pos = c_lo + j0 + lane;
+            const uint32_t* srow = sub_split + (size_t)pos * (nsub + 1);
+            const uint32_t a = srow[sr], b = srow[sr + 1];
+            my_lo = p[perm[pos]] + a;
+            my_n = (int)(b - a);
+        }
+        const int nb = min(32, ncols - j0);
+        Slice ring[K1W_DEPTH];
+        auto load = [&](Slice& sl, int q) {
+            sl.lo = __shfl_sync(0xffffffffu, my_lo, q & 31);
+            sl.n = q < nb ? __shfl_sync(0xffffffffu, my_n, q & 31) : 0;
+            sl.g = -1;
+            if (lane < sl.n) {
+                sl.g = idx[sl.lo + lane];
+                sl.v = x[sl.lo + lane];
+            }
+        };
+#pragma unroll
+        for (int d = 0; d < K1W_DEPTH; ++d) load(ring[d], d);
+        for (int q0 = 0; q0 < nb; q0 += K1W_DEPTH) {
+#pragma unroll
+            for (int d = 0; d < K1W_DEPTH; ++d) {
+                Slice& sl = ring[d];
+                if (sl.g >= 0) put(sl.g, sl.v);
+                for (int k = 32 + lane; k < sl.n; k += 32) put(idx[sl.lo + k], x[sl.lo + k]);
+                __syncwarp();  // the next column may touch the same genes from other lanes
+                load(sl, q0 + d + K1W_DEPTH);
+            }
+        }
+    }
+    __syncwarp();
+    // flush the incomplete last sector of every gene
+    for (int g = lane; g < glen; g += 32) {
+        const uint32_t c = cursor[g], f = first[g];
+        if ((c & 3u) != 0u && c > f) {
+            const uint32_t from = max(f, c & ~3u);
+            for (uint32_t s = from; s < c; ++s) vals[s] = stage[(size_t)g * 4 + (s & 3u)];
+        }
+    }
+}
+
 }  // namespace
 
 void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayout& L, Transposed& T) {
@@ -337,11 +458,20 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
     const int glen_all = (int)ceil_div(ngenes, nranges);
     allow_smem(k1_count, (size_t)glen_all * 4 + bounds_bytes);
 
+    // the warp-per-sub-range scatter needs, per column, where every sub-range of K1_SUB genes starts
+    const char* old_env = getenv("SCRANB200_K1_BLOCK_SCATTER");  // "1": the older CTA-per-2048-genes scatter (kept for comparison)
+    const bool warp_scatter = !(old_env && old_env[0] == '1');
+    const int nsub = (int)ceil_div(ngenes, K1_SUB);
+    uint32_t* sub_split = nullptr;
+    if (warp_scatter && L.nchunks > 0 && ngenes > 0) {
+        ctx->split.reserve((size_t)(nsub + 1) * L.perm.size() * 4 + 64);
+        sub_split = ctx->split.as<uint32_t>();
+    }
     if (L.nchunks > 0 && ngenes > 0) {
         for (int r = 0; r < nranges; ++r) {
             const int g0 = r * glen_all, glen = std::min(glen_all, ngenes - g0);
             SB_LAUNCH(ctx, k1_count, L.nchunks, K1_THREADS, (size_t)glen * 4 + bounds_bytes, mat->d_p, mat->d_i, L.d_perm,
-                      L.d_chunk_start, ngenes, g0, glen, table, bad);
+                      L.d_chunk_start, ngenes, g0, glen, table, bad, r == 0 ? sub_split : nullptr, nsub);
         }
     }
     if (ngenes > 0) {
@@ -349,7 +479,12 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
                   ctx->seg_off.as<uint32_t>(), ctx->row_total.as<uint32_t>());
     }
     SB_LAUNCH(ctx, k1_scan_rows, 1, 1024, 0, ctx->row_total.as<uint32_t>(), ngenes, ctx->row_ptr.as<int64_t>());
-    if (L.nchunks > 0 && ngenes > 0) {
+    if (warp_scatter && L.nchunks > 0 && ngenes > 0) {
+        const int64_t grid = (int64_t)L.nchunks * ceil_div(nsub, K1W_WARPS);
+        if (grid > 2147483647ll) throw Error("too many transpose tiles");
+        SB_LAUNCH(ctx, k1_scatter_warp, (unsigned)grid, K1W_WARPS * 32, 0, mat->d_p, mat->d_i, mat->d_x, L.d_perm, L.d_chunk_start,
+                  ngenes, nsub, sub_split, table, T.row_ptr, T.vals);
+    } else if (L.nchunks > 0 && ngenes > 0) {
         // Scatter pass: (chunk) x (range of K1S_GR genes) CTAs.
         const int GR = K1S_GR;
         const int sranges = (int)ceil_div(ngenes, GR);
