@@ -347,3 +347,46 @@ def test_score_markers_one_cell_groups(sb):
     groups[0] = 3
     got, want = _score_both(sb, x, groups, full_stats=True)
     assert_tables_match(got, want)
+
+
+# ---------------------------------------------------------------------------------------------
+# pairwiseWilcox / pairwiseTTests (tests/testthat/test-pairwise-wilcox.R, test-pairwise-t.R): device
+# U / tie term / means / variances under the host p-value layer, against the oracle's restatement
+# ---------------------------------------------------------------------------------------------
+
+def _pair_lists_match(got, want, rtol=1e-10):
+    assert [(q["first"], q["second"]) for q in got] == [(q["first"], q["second"]) for q in want]
+    for a, b in zip(got, want):
+        for key in ("effect", "log_p", "log_fdr"):
+            x, y = np.asarray(a[key], np.float64), np.asarray(b[key], np.float64)
+            ok = np.isclose(x, y, rtol=rtol, atol=1e-12, equal_nan=True) | (x == y)
+            assert ok.all(), (a["first"], a["second"], key, np.nanmax(np.abs(x - y)))
+
+
+@pytest.mark.parametrize("direction", ["any", "up", "down"])
+@pytest.mark.parametrize("lfc", [0.0, 0.5])
+def test_pairwise_wilcox_layers(sb, port_lib, direction, lfc):
+    from oracle import rlevel
+    rng = np.random.default_rng(41)
+    x = make_matrix(70, 420, seed=141, rate=1.2)
+    groups = rng.integers(0, 4, 420)
+    block = rng.integers(0, 3, 420)
+    for blk in (None, block):
+        got = sb.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction)
+        want = rlevel.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, lib=port_lib)
+        _pair_lists_match(got, want)
+
+
+@pytest.mark.parametrize("direction", ["any", "up", "down"])
+@pytest.mark.parametrize("lfc", [0.0, 0.5])
+def test_pairwise_t_tests_layers(sb, port_lib, direction, lfc):
+    from oracle import rlevel
+    rng = np.random.default_rng(42)
+    x = make_matrix(70, 420, seed=142, rate=1.2)
+    groups = rng.integers(0, 4, 420)
+    block = rng.integers(0, 3, 420)
+    for blk in (None, block):
+        for std in (False, True):
+            got = sb.pairwise_t_tests(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, std_lfc=std)
+            want = rlevel.pairwise_ttests(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, std_lfc=std, lib=port_lib)
+            _pair_lists_match(got, want)
