@@ -486,14 +486,43 @@ def pairwise_wilcox(x, groups, block=None, lfc=0.0, direction="any"):
         if len(block) != m.shape[1]:
             raise ValueError("length of 'block' does not equal 'ncol(x)'")
         blocks = [np.flatnonzero(block == b) for b in sorted(set(block.tolist()))]
-    all_n, all_u, all_t = [], [], []
-    for chosen in blocks:  # R/pairwiseWilcox.R:221-243: one native call per block level
+    # R/pairwiseWilcox.R:221-243 makes one native call per block level; here all block levels go through
+    # ONE paired call (two with lfc != 0: the mirrored entries use -lfc, src/overlap_exprs.cpp:179-187),
+    # every (block, group) combination being a group of its own, and the results are laid out as the
+    # per-block overlap_exprs() matrices: entry (i, j) present for j < i (all i != j with lfc != 0).
+    all_n, combos, left, right, where = [], [], [], [], []
+    for b, chosen in enumerate(blocks):
         cg = codes[chosen]
         by_group = [chosen[cg == g].astype(np.int32) for g in range(G)]
         all_n.append(np.array([len(v) for v in by_group], np.float64))
-        U, T = overlap_exprs(m, by_group, lfc)
-        all_u.append(U)
-        all_t.append(T)
+        base = len(combos)
+        combos.extend(by_group)
+        for i in range(G):
+            if len(by_group[i]) == 0:
+                continue  # src/overlap_exprs.cpp:175,177: empty groups are skipped, their entries stay 0
+            for j in range(i):
+                if len(by_group[j]) == 0:
+                    continue
+                left.append(base + i + 1)
+                right.append(base + j + 1)
+                where.append((b, i, j))
+    ngenes = m.shape[0]
+    all_u = [np.full((G, G, ngenes), np.nan) for _ in blocks]
+    all_t = [np.full((G, G, ngenes), np.nan) for _ in blocks]
+    for b in range(len(blocks)):
+        for i in range(G):
+            for j in range(G):
+                if j < i or (lfc != 0 and i != j):
+                    all_u[b][i, j] = 0.0
+                    all_t[b][i, j] = 0.0
+    if left:
+        for sign in ((1.0,) if lfc == 0 else (1.0, -1.0)):
+            U, T = overlap_exprs_paired(m, np.array(left, np.int32), np.array(right, np.int32), combos, sign * lfc,
+                                        want_ties=True)
+            for k, (b, i, j) in enumerate(where):
+                a, c = (i, j) if sign > 0 else (j, i)
+                all_u[b][a, c] = U[:, k]
+                all_t[b][a, c] = T[:, k]
 
     def sigma(nh, nt, ties):  # .get_sigma, R/pairwiseWilcox.R:347-350
         s2 = (nh * nt / 12) * ((nh + nt + 1) - ties / ((nh + nt) * (nh + nt - 1)))

@@ -113,11 +113,12 @@ k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
                         const unsigned gl = (unsigned)(g[q] - g0);
                         if (gl < (unsigned)glen) atomicAdd(&cnt[gl], 1u);
                         const int sub = g[q] >> K1_SUB_SHIFT, sub_prev = prev >> K1_SUB_SHIFT;  // (-1 >> s = -1)
-                        if (srow && (sub != sub_prev || k == n - 1)) {
-                            for (int r = sub_prev + 1; r <= sub; ++r) srow[r] = (uint32_t)k;
-                            if (k == n - 1) {
-                                for (int r = sub + 1; r <= nsub; ++r) srow[r] = (uint32_t)n;
-                            }
+                        if (srow && sub != sub_prev) {
+                            srow[sub] = (uint32_t)k;  // usually the only sub-range that starts here
+                            for (int r = sub_prev + 1; r < sub; ++r) srow[r] = (uint32_t)k;
+                        }
+                        if (srow && k == n - 1) {
+                            for (int r = sub + 1; r <= nsub; ++r) srow[r] = (uint32_t)n;
                         }
                     }
                 }
