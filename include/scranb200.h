@@ -90,6 +90,22 @@ int scranb200_blocked_stats_transformed(scranb200_ctx* ctx, const scranb200_mat*
                                         int transform, const double* sf, double pseudo, double* mean_out,
                                         double* var_out);
 
+/* ---- pairwiseWilcox, statistics AND p-value layer: R/pairwiseWilcox.R:192-350 ----------------
+ *  The R function calls overlap_exprs once per block level
+ * (R/pairwiseWilcox.R:221-228) and then, in R closures per (block, host, target): AUC, the normal
+ * approximation with continuity and tie correction (:263-350), Stouffer's combination over the
+ * block levels with weights n_host n_target and the weighted mean of the AUCs
+ * (R/utils_markers.R:52-130), and .logBH over the genes (:184-190). This entry point does all of
+ * it on the device, log.p = TRUE.
+ * group: one code per cell, 0 .. ngroups-1 (negative = NA: the cell is ignored); block: one code
+ * per cell, 0 .. nblocks-1, or NULL (one block); direction: 0 "any", 1 "up", 2 "down".
+ * Outputs: host arrays [ngroups (ngroups - 1)][nrow]: ordered pair (first, second), first in level
+ * order, second in level order skipping first, the order of the reference's `pairs` DataFrame;
+ * effect = AUC (overlap proportion), logp, logfdr natural logs. Pairs without a valid block: NaN. */
+int scranb200_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int ngroups,
+                              const int32_t* block, int nblocks, double lfc, int direction, double* effect_out,
+                              double* logp_out, double* logfdr_out);
+
 /* ---- overlap_exprs_paired: src/overlap_exprs.cpp:196-220 ------------------------------------
  * groups: the reference's list of 0-based cell-index vectors, flattened: group g owns
  * group_cells[group_ptr[g] .. group_ptr[g+1]). A cell may belong to at most one group (the

@@ -472,9 +472,49 @@ def _blocked_template(levels, nblocks, direction, statfun):
     return ordered
 
 
-def pairwise_wilcox(x, groups, block=None, lfc=0.0, direction="any"):
+def pairwise_wilcox(x, groups, block=None, lfc=0.0, direction="any", host_layer=False):
     """pairwiseWilcox(x, groups, block=, lfc=, direction=, log.p=TRUE): list of dicts
-    (first, second, effect=AUC, log_p, log_fdr) in the reference's pair order."""
+    (first, second, effect=AUC, log_p, log_fdr) in the reference's pair order. The statistics and the
+    p-value layer (normal approximation, Stouffer over the block levels, log BH) run on the device;
+    host_layer=True keeps the p-value layer in numpy / scipy on top of the device U and tie terms."""
+    if host_layer:
+        return _pairwise_wilcox_host_layer(x, groups, block, lfc, direction)
+    if direction not in ("any", "up", "down"):
+        raise ValueError("'direction' should be one of 'any', 'up', 'down'")
+    m = _as_matrix(x)
+    levels, codes = _setup_groups(groups, m.shape[1])
+    G = len(levels)
+    if block is None:
+        bcodes, nb = None, 1
+    else:
+        block = np.asarray(list(block))
+        if len(block) != m.shape[1]:
+            raise ValueError("length of 'block' does not equal 'ncol(x)'")
+        blevels = sorted(set(block.tolist()))
+        bcodes = np.ascontiguousarray(np.searchsorted(np.array(blevels), block), np.int32)
+        nb = len(blevels)
+    gcodes = np.ascontiguousarray(codes, np.int32)
+    nout = G * (G - 1)
+    eff = np.zeros((max(1, nout), m.shape[0]), np.float64)
+    lp = np.zeros_like(eff)
+    lf = np.zeros_like(eff)
+    check(lib().scranb200_pairwise_wilcox(m.ctx.handle, m.handle, ptr(gcodes), G, ptr(bcodes), nb, float(lfc),
+                                          ("any", "up", "down").index(direction), ptr(eff), ptr(lp), ptr(lf)))
+    out, k = [], 0
+    for a in levels:
+        for b in levels:
+            if a == b:
+                continue
+            if np.all(np.isnan(lp[k])):
+                import warnings
+                if levels.index(b) < levels.index(a):
+                    warnings.warn("no within-block comparison between %s and %s" % (a, b))
+            out.append(dict(first=a, second=b, effect=eff[k].copy(), log_p=lp[k].copy(), log_fdr=lf[k].copy()))
+            k += 1
+    return out
+
+
+def _pairwise_wilcox_host_layer(x, groups, block=None, lfc=0.0, direction="any"):
     from scipy.special import log_ndtr
     m = _as_matrix(x)
     levels, codes = _setup_groups(groups, m.shape[1])

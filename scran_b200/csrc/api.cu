@@ -171,7 +171,10 @@ struct PairRun {
     Transposed T;
 };
 
+}  // namespace
+
 // transpose (+ optional stats) (+ optional U / ties) for one layout; results stay on the device.
+// (Also used by pvalues.cu.)
 void run_pairs(scranb200_ctx* ctx, const scranb200_mat* mat, PairLayout& L, DevBuf& lbuf, bool want_stats, double lfc,
                bool want_u, bool want_t) {
     Transposed T;
@@ -198,6 +201,8 @@ void run_pairs(scranb200_ctx* ctx, const scranb200_mat* mat, PairLayout& L, DevB
         run_wilcox(ctx, T, L, lfc, ctx->u_pairs.as<double>(), want_t ? ctx->t_pairs.as<double>() : nullptr);
     }
 }
+
+namespace {
 
 void score_stage1(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan, int64_t ld, int64_t row0,
                   double* d_eff, double* d_out) {
@@ -484,6 +489,19 @@ int scranb200_blocked_stats(scranb200_ctx* ctx, const scranb200_mat* mat, const 
         if (ndetected_out) SB_CUDA(cudaMemcpyAsync(ndetected_out, ctx->ndet.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     }
     SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
+    API_END
+}
+
+int scranb200_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int ngroups,
+                              const int32_t* block, int nblocks, double lfc, int direction, double* effect_out,
+                              double* logp_out, double* logfdr_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    if (ngroups < 0 || nblocks < 1) throw Error("bad number of groups or blocks");
+    if (direction < 0 || direction > 2) throw Error("direction must be 0 (any), 1 (up) or 2 (down)");
+    phase_begin(ctx);
+    run_pairwise_wilcox(ctx, mat, group, ngroups, block, nblocks, lfc, direction, effect_out, logp_out, logfdr_out);
     phase_collect(ctx);
     API_END
 }

@@ -29,4 +29,8 @@ void run_stats(scranb200_ctx* ctx, Transposed& T, const PairLayout& L, double* d
 // d_u / d_t: [ngenes][npairs] (pairs contiguous within a gene, caller's pair order).
 void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, double lfc, double* d_u, double* d_t);
 
+// pvalues.cu: pairwiseWilcox's p-value layer on the device; outputs are host arrays [G (G - 1)][ngenes].
+void run_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int G, const int32_t* block,
+                         int nblocks, double lfc, int direction, double* effect, double* logp, double* logfdr);
+
 }  // namespace sb

@@ -372,9 +372,33 @@ def test_pairwise_wilcox_layers(sb, port_lib, direction, lfc):
     groups = rng.integers(0, 4, 420)
     block = rng.integers(0, 3, 420)
     for blk in (None, block):
-        got = sb.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction)
         want = rlevel.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, lib=port_lib)
+        for host_layer in (False, True):  # p-value layer on the device (the default) / in numpy on the device statistics
+            got = sb.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, host_layer=host_layer)
+            _pair_lists_match(got, want)
+
+
+def test_pairwise_wilcox_extreme_tails_and_empty_combinations(sb, port_lib):
+    """Perfectly separated groups of thousands of cells (log p-values of -1e3 and below, where exp()
+    underflows: asymptotic tail and the Newton inverse), a gene without any variation, and a block
+    level in which one group is absent."""
+    from oracle import rlevel
+    rng = np.random.default_rng(43)
+    ncells = 6000
+    groups = rng.integers(0, 3, ncells)
+    block = rng.integers(0, 2, ncells)
+    block[groups == 2] = 0                      # group 2 is absent from block 1
+    x = np.zeros((6, ncells))
+    x[0] = groups * 10.0 + rng.random(ncells)   # perfectly separated
+    x[1] = np.where(groups == 1, rng.random(ncells) + 5, 0.0)
+    x[2] = 1.0                                  # no variation: every value ties
+    x[3] = rng.poisson(0.3, ncells)
+    x[4] = rng.normal(size=ncells)
+    for blk in (None, block):
+        want = rlevel.pairwise_wilcox(as_csc(x), groups, block=blk, lib=port_lib)
+        got = sb.pairwise_wilcox(as_csc(x), groups, block=blk)
         _pair_lists_match(got, want)
+        assert min(np.nanmin(q["log_p"]) for q in got) < -1000
 
 
 @pytest.mark.parametrize("direction", ["any", "up", "down"])
