@@ -140,16 +140,23 @@ __global__ void k1_scan_table(uint32_t* __restrict__ table, int nchunks, int nge
     uint32_t run = 0;
     int dc = 0;
     int next_first = first_chunk[0];
-    for (int k = 0; k < nchunks; ++k) {
-        while (dc <= C && next_first == k) {
-            seg_off[(size_t)dc * ngenes + g] = run;
-            ++dc;
-            next_first = dc <= C ? first_chunk[dc] : -1;
+    for (int k0 = 0; k0 < nchunks; k0 += 8) {  // eight loads in flight: one thread per gene is all the parallelism there is
+        uint32_t v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = k0 + q < nchunks ? table[(size_t)(k0 + q) * ngenes + g] : 0u;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int k = k0 + q;
+            if (k < nchunks) {
+                while (dc <= C && next_first == k) {
+                    seg_off[(size_t)dc * ngenes + g] = run;
+                    ++dc;
+                    next_first = dc <= C ? first_chunk[dc] : -1;
+                }
+                table[(size_t)k * ngenes + g] = run;
+                run += v[q];
+            }
         }
-        const size_t at = (size_t)k * ngenes + g;
-        const uint32_t v = table[at];
-        table[at] = run;
-        run += v;
     }
     while (dc <= C) {
         seg_off[(size_t)dc * ngenes + g] = run;
