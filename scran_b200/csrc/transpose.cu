@@ -117,11 +117,14 @@ k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
                             srow[sub] = (uint32_t)k;  // usually the only sub-range that starts here
                             for (int r = sub_prev + 1; r < sub; ++r) srow[r] = (uint32_t)k;
                         }
-                        if (srow && k == n - 1) {
-                            for (int r = sub + 1; r <= nsub; ++r) srow[r] = (uint32_t)n;
-                        }
                     }
                 }
+            }
+        }
+        if (srow && n > 0) {  // the sub-ranges behind the column's last entry: all lanes
+            const int last = idx[lo + n - 1];
+            if (last >= 0 && last < ngenes) {
+                for (int r = (last >> K1_SUB_SHIFT) + 1 + lane; r <= nsub; r += 32) srow[r] = (uint32_t)n;
             }
         }
     }
