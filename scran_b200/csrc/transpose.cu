@@ -115,7 +115,8 @@ k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
                         const int sub = g[q] >> K1_SUB_SHIFT, sub_prev = prev >> K1_SUB_SHIFT;  // (-1 >> s = -1)
                         if (srow && sub != sub_prev) {
                             srow[sub] = (uint32_t)k;  // usually the only sub-range that starts here
-                            for (int r = sub_prev + 1; r < sub; ++r) srow[r] = (uint32_t)k;
+#pragma unroll 1
+                            for (int r = sub_prev + 1; r < sub; ++r) srow[r] = (uint32_t)k;  // (sub-ranges without entries)
                         }
                     }
                 }
