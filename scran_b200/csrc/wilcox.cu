@@ -1201,51 +1201,77 @@ __device__ __forceinline__ void walk_range(const uint16_t* st, int i_lo, int i_h
         }
         deferred = false;
     };
-    // The next block's entries are requested before the current block is walked.
-    uint32_t ent_next = (i_lo + lane) < i_hi ? (uint32_t)st[i_lo + lane] : 0u;
-    for (int i0 = i_lo; i0 < i_hi; i0 += 32) {
-        const uint32_t ent = ent_next;
-        {
-            const int nxt = i0 + 32 + lane;
-            ent_next = nxt < i_hi ? (uint32_t)st[nxt] : 0u;
-        }
-        if (i_hi - i0 >= 32) {
-            const unsigned tied = __ballot_sync(0xffffffffu, (ent & TIE_BIT) != 0u);
-            if (can_defer && tied == 0xffffffffu) {
-                deferred = true;
-#pragma unroll 8
-                for (int k = 0; k < 32; ++k) {
-                    const int lab = (int)(__shfl_sync(0xffffffffu, ent, k) & LAB_MASK);
-#pragma unroll
-                    for (int j = 0; j < J; ++j) bump(cd[j], lab, Rj[j]);
-                }
-                continue;
-            }
-            if (deferred) flush();
-            if (!SHIFT && tied == 0u) {
-#pragma unroll
-                for (int k = 0; k < 28; k += QN) {
-                    uint32_t l[QN];
-#pragma unroll
-                    for (int a = 0; a < QN; ++a) l[a] = __shfl_sync(0xffffffffu, ent, k + a);
-                    multi_untied(l);
-                }
-                step_untied(__shfl_sync(0xffffffffu, ent, 28));
-                step_untied(__shfl_sync(0xffffffffu, ent, 29));
-                step_untied(__shfl_sync(0xffffffffu, ent, 30));
-#pragma unroll
-                for (int j = 0; j < J; ++j) cs[j] = c[j];  // the last entry's run starts here; the next block may tie with it
-                step_untied(__shfl_sync(0xffffffffu, ent, 31));
-            } else {
-#pragma unroll 8
-                for (int k = 0; k < 32; ++k) step(__shfl_sync(0xffffffffu, ent, k));
-            }
-        } else {
-            if (deferred) flush();
-            const int cnt = i_hi - i0;
-            for (int k = 0; k < cnt; ++k) step(__shfl_sync(0xffffffffu, ent, k));
+    // Up to 32 entries the slow way: one entry per lane, handed round with shuffles. Used for the few
+    // entries before the first 16-byte boundary of the stream and for the tail of the range.
+    auto shuffled_block = [&](int i0, int cnt) {
+        const uint32_t ent = lane < cnt ? (uint32_t)st[i0 + lane] : 0u;
+        if (deferred) flush();
+        for (int k = 0; k < cnt; ++k) step(__shfl_sync(0xffffffffu, ent, k));
+    };
+    int i = i_lo;
+    {
+        const int to_boundary = (int)(((16u - (unsigned)(reinterpret_cast<uintptr_t>(st + i) & 15u)) & 15u) >> 1);
+        const int cnt = min(to_boundary, i_hi - i);
+        if (cnt > 0) {
+            shuffled_block(i, cnt);
+            i += cnt;
         }
     }
+    // Whole blocks of 32 entries: EVERY lane loads all 64 bytes (four 16-byte loads from one address:
+    // a broadcast) and picks the entries out of its registers, instead of 32 shuffles a block: the
+    // walk is bound by the load/store pipe (two atomic adds per entry), which the shuffles share.
+    for (; i + 32 <= i_hi; i += 32) {
+        uint32_t u[16];
+        {
+            const uint4* src = reinterpret_cast<const uint4*>(st + i);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint4 w = src[q];
+                u[4 * q] = w.x;
+                u[4 * q + 1] = w.y;
+                u[4 * q + 2] = w.z;
+                u[4 * q + 3] = w.w;
+            }
+        }
+        uint32_t any = 0u, all = 0xffffffffu;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+            any |= u[q];
+            all &= u[q];
+        }
+        const uint32_t tie2 = TIE_BIT | (TIE_BIT << 16);
+        auto entry = [&](int k) { return (k & 1) ? u[k >> 1] >> 16 : u[k >> 1] & 0xffffu; };
+        if (can_defer && (all & tie2) == tie2) {  // wholly inside a run: count only
+            deferred = true;
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+                const int lab = (int)(entry(k) & LAB_MASK);
+#pragma unroll
+                for (int j = 0; j < J; ++j) bump(cd[j], lab, Rj[j]);
+            }
+            continue;
+        }
+        if (deferred) flush();
+        if (!SHIFT && (any & tie2) == 0u) {  // no tie, no role bit: the entry is its label
+#pragma unroll
+            for (int k = 0; k < 28; k += QN) {
+                uint32_t l[QN];
+#pragma unroll
+                for (int a2 = 0; a2 < QN; ++a2) l[a2] = entry(k + a2);
+                multi_untied(l);
+            }
+            step_untied(entry(28));
+            step_untied(entry(29));
+            step_untied(entry(30));
+#pragma unroll
+            for (int j = 0; j < J; ++j) cs[j] = c[j];  // the last entry's run starts here; the next block may tie with it
+            step_untied(entry(31));
+        } else {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) step(entry(k));
+        }
+    }
+    if (i < i_hi) shuffled_block(i, i_hi - i);
     if (deferred) flush();
 #pragma unroll
     for (int j = 0; j < J; ++j) {
