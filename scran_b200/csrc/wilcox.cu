@@ -556,6 +556,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
         bool tie = false;
         if (end - start > 1) {
             if (two_roles) {
+#pragma unroll 1
                 for (uint32_t j = start; j < end; ++j) {
                     const uint64_t kj = S.key[j];
                     const uint32_t lj = S.lab[j];
@@ -565,6 +566,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                     tie |= eq && before;
                 }
             } else {
+#pragma unroll 1
                 for (uint32_t j = start; j < end; ++j) {
                     const uint64_t kj = S.key[j];
                     const bool eq = kj == key;
