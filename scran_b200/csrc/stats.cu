@@ -50,14 +50,28 @@ k2_stats(const double* __restrict__ vals, const int64_t* __restrict__ row_ptr, c
             det += (v > 0.0) ? 1.0 : 0.0;
         };
         int64_t k = lo;
-        // The update chain is sequential by definition; the loads are not. Eight values are fetched
-        // ahead of the arithmetic so that every thread keeps several memory requests in flight.
-        for (; k + 8 <= hi; k += 8) {
-            double v[8];
+        // The update chain is sequential by definition (a division per value); the loads are not. The
+        // next eight values are requested before the current eight are folded in, so that a thread
+        // has memory requests in flight all the time and not only between two stretches of arithmetic.
+        double v[8];
+        bool have = k + 8 <= hi;
+        if (have) {
 #pragma unroll
             for (int q = 0; q < 8; ++q) v[q] = vals[k + q];
+        }
+        while (have) {
+            double w[8];
+            const bool more = k + 16 <= hi;
+            if (more) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) w[q] = vals[k + 8 + q];
+            }
 #pragma unroll
             for (int q = 0; q < 8; ++q) update(v[q]);
+            k += 8;
+            have = more;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = w[q];
         }
         for (; k < hi; ++k) update(vals[k]);
 
