@@ -61,7 +61,9 @@ struct EffParams {
     double* eff;  // [3][Q][ld]
 };
 
-__global__ void __launch_bounds__(256) k4_effects(EffParams P) {
+// (Five CTAs per SM: the kernel waits on loads, so residency beats the few spilled registers:
+// 2.0 -> 1.4 ms at the config-3 shard against the compiler's own 114 registers.)
+__global__ void __launch_bounds__(256, 5) k4_effects(EffParams P) {
     // 4 consecutive genes per comparison share a 32-byte sector of every [.][ngenes] array.
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t tiles = (P.ngenes + 3) / 4;
