@@ -352,7 +352,7 @@ k1_scatter_warp(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, 
                 const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int nsub,
                 const uint32_t* __restrict__ sub_split, const uint32_t* __restrict__ table,
                 const int64_t* __restrict__ row_ptr, double* __restrict__ vals) {
-    __shared__ double s_stage[K1W_WARPS][K1_SUB * 4];
+    __shared__ double s_stage[K1W_WARPS][K1_SUB * 3];  // the fourth value of a sector never waits: it completes the sector
     __shared__ uint32_t s_cursor[K1W_WARPS][K1_SUB], s_first[K1W_WARPS][K1_SUB];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int blocks_per_chunk = (nsub + K1W_WARPS - 1) / K1W_WARPS;
@@ -376,9 +376,10 @@ k1_scatter_warp(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, 
         if (gl >= (unsigned)glen) return;  // only reachable with an invalid (unsorted) matrix, reported by pass A
         const uint32_t at = cursor[gl];
         cursor[gl] = at + 1;
-        double* sg = stage + (size_t)gl * 4;
-        sg[at & 3u] = v;
-        if ((at & 3u) == 3u) {
+        double* sg = stage + (size_t)gl * 3;
+        if ((at & 3u) != 3u) {
+            sg[at & 3u] = v;
+        } else {
             const uint32_t base = at - 3u, f = first[gl];
             if (base >= f) {  // a whole 32-byte sector
                 double2* dst = reinterpret_cast<double2*>(vals + base);
@@ -437,7 +438,7 @@ k1_scatter_warp(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, 
         const uint32_t c = cursor[g], f = first[g];
         if ((c & 3u) != 0u && c > f) {
             const uint32_t from = max(f, c & ~3u);
-            for (uint32_t s = from; s < c; ++s) vals[s] = stage[(size_t)g * 4 + (s & 3u)];
+            for (uint32_t s = from; s < c; ++s) vals[s] = stage[(size_t)g * 3 + (s & 3u)];
         }
     }
 }
