@@ -1029,6 +1029,7 @@ struct WalkParams {
     int groups;           // solo mode: position chunks walked concurrently (private tables)
     int nslots;           // batch mode: warp groups (0 = batch mode unavailable: tables too large)
     int slot_tiles;       // batch mode: warps per slot = ceil((maxG + 1) / 32)
+    int slot_chunks;      // small-unit kernel: position chunks per unit (2 when one warp covers all labels)
     int pass;             // 0: everything with m <= 65536 (uint32 tables); 1: only m > 65536 (uint64 tables)
     const int32_t* nbig;  // number of large single-unit jobs at the head of `order`
     uint32_t big_total;   // a unit with more entries than this is "large": walked by a whole CTA
@@ -1292,29 +1293,34 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk_small(WalkParams P) {
     constexpr int W = 32 * J;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Gmax1 = P.maxG + 1;
-    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                  // [WALK_WARPS][Gmax1]
-    unsigned long long* slot_task = reinterpret_cast<unsigned long long*>(hist + (size_t)WALK_WARPS * Gmax1 + (Gmax1 & 1));
-    uint32_t* acc = reinterpret_cast<uint32_t*>(slot_task + WALK_WARPS);    // [nslots][Gmax1][stl * W]
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                  // [2][WALK_WARPS][Gmax1]: counted / adding role, per (slot, chunk)
+    unsigned long long* slot_task = reinterpret_cast<unsigned long long*>(hist + (size_t)2 * WALK_WARPS * Gmax1);
+    int* slot_mid = reinterpret_cast<int*>(slot_task + WALK_WARPS);         // [WALK_WARPS]
+    uint32_t* acc = reinterpret_cast<uint32_t*>(slot_mid + WALK_WARPS);     // [nslots][Gmax1][stl * W]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const UnitTables& ut = P.ut;
-    const int stl = P.slot_tiles;
-    const int slot = warp / stl, wtile = warp % stl;
+    // A slot = the warps of one unit: `stl` tiles of labels x `nch` position chunks (two when one warp
+    // covers all labels: the halves of the unit are walked at the same time into the slot's one
+    // table, with atomic adds, and combined through their label counts as in k3_walk).
+    const int stl = P.slot_tiles, nch = P.slot_chunks, swarps = stl * nch;
+    const int slot = warp / swarps, ws = warp % swarps, wtile = ws % stl, chunk = ws / stl;
     if (slot >= P.nslots) return;
     const size_t rpad = (size_t)stl * W;
     uint32_t* sacc = acc + (size_t)slot * Gmax1 * rpad;
-    uint32_t* shist = hist + (size_t)slot * Gmax1;
-    const int sthreads = stl * 32, stid = wtile * 32 + lane;
+    uint32_t* hist_r = hist + (size_t)(slot * nch) * Gmax1;                   // rows chunk 0 .. nch-1
+    uint32_t* hist_l = hist + (size_t)(WALK_WARPS + slot * nch) * Gmax1;
+    const int sthreads = swarps * 32, stid = ws * 32 + lane;
     const int64_t ntasks = (int64_t)ut.ngenes * ut.U;
     while (true) {
         unsigned long long t = 0;
-        if (stl == 1) {
+        if (swarps == 1) {
             if (lane == 0) t = atomicAdd(P.job_counter, 1ull);
             t = __shfl_sync(0xffffffffu, t, 0);
         } else {
             if (stid == 0) slot_task[slot] = atomicAdd(P.job_counter, 1ull);
-            slot_barrier(slot, stl);
+            slot_barrier(slot, swarps);
             t = slot_task[slot];
-            slot_barrier(slot, stl);
+            slot_barrier(slot, swarps);
         }
         if ((int64_t)t >= ntasks) break;
         const int64_t task = (int64_t)t;
@@ -1324,18 +1330,44 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk_small(WalkParams P) {
         const uint32_t m = P.unit_m[task];
         const uint16_t* st = P.stream + ui.soff;
         for (int k = stid; k < Gt * (int)rpad; k += sthreads) sacc[k] = 0;
-        slot_barrier(slot, stl);
+        if (nch == 2 && ws == 0) {  // second chunk: from the first run start at or after the middle
+            int b = m >= 512u ? (int)(m / 2) : (int)m;
+            while (b < (int)m) {
+                const bool stop = b + lane >= (int)m || !(st[b + lane] & TIE_BIT);
+                const unsigned found = __ballot_sync(0xffffffffu, stop);
+                if (found) {
+                    b += __ffs(found) - 1;
+                    break;
+                }
+                b += 32;
+            }
+            if (lane == 0) slot_mid[slot] = min(b, (int)m);
+        }
+        slot_barrier(slot, swarps);
+        const int mid = nch == 2 ? slot_mid[slot] : (int)m;
+        const int i_lo = chunk == 0 ? 0 : mid, i_hi = chunk == nch - 1 ? (int)m : mid;
         const int R0 = wtile * W + lane;
-        // shist: stored entries per label (counted role), left behind by the walk
-        walk_range<uint32_t, SHIFT, J>(st, 0, (int)m, R0, sacc + R0, rpad, shist, nullptr, Gt, lane);
-        slot_barrier(slot, stl);
+        // the label counts of the chunk (counted role / adding role) are left behind by the walk
+        walk_range<uint32_t, SHIFT, J>(st, i_lo, i_hi, R0, sacc + R0, rpad, hist_r + chunk * Gmax1,
+                                       SHIFT ? hist_l + chunk * Gmax1 : nullptr, Gt, lane);
+        slot_barrier(slot, swarps);
+        if (nch == 2) {  // what the first chunk's entries add to the second chunk's rows
+            const uint32_t* add_l = SHIFT ? hist_l + Gmax1 : hist_r + Gmax1;
+            for (int k = stid; k < Gt * Gt; k += sthreads) {
+                const int L = k / Gt, R = k % Gt;
+                const uint32_t extra = add_l[L] * hist_r[R];
+                if (extra) sacc[(size_t)L * rpad + R] += SHIFT ? 2u * extra : extra;
+            }
+            slot_barrier(slot, swarps);
+        }
         for (int pp = P.pair_ptr[ui.u] + stid; pp < P.pair_ptr[ui.u + 1]; pp += sthreads) {
             const int l = P.pair_l[pp], r = P.pair_r[pp];
             const long long nL = ut.ncells_dev[ui.first + l], nR = ut.ncells_dev[ui.first + r];
-            const long long zL = nL - (long long)shist[l], zR = nR - (long long)shist[r];
-            P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] = pair_u<uint32_t, SHIFT>(sacc, rpad, l, r, ui.G, nL, nR, zL, zR);
+            const long long sl = nch == 2 ? (long long)hist_r[l] + hist_r[Gmax1 + l] : (long long)hist_r[l];
+            const long long sr = nch == 2 ? (long long)hist_r[r] + hist_r[Gmax1 + r] : (long long)hist_r[r];
+            P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] = pair_u<uint32_t, SHIFT>(sacc, rpad, l, r, ui.G, nL, nR, nL - sl, nR - sr);
         }
-        slot_barrier(slot, stl);
+        slot_barrier(slot, swarps);
     }
 }
 
@@ -1749,12 +1781,15 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     // ---- units of up to big_total entries: one warp group per unit, no CTA-wide barriers ----
     {
         const size_t table = (size_t)Gt * W * 4 * ntiles;  // one unit's uint32 count table
-        const size_t fixed_small = ((size_t)WALK_WARPS * Gt + (Gt & 1)) * 4 + WALK_WARPS * 8 + 32;
+        const size_t fixed_small = ((size_t)2 * WALK_WARPS * Gt) * 4 + WALK_WARPS * 8 + WALK_WARPS * 4 + 32;
+        // halves of a unit walked at the same time, if shared memory holds fewer tables than the CTA has warps
+        const int nch = ntiles == 1 && fixed_small + table * WALK_WARPS > ctx->smem_optin ? 2 : 1;
         int ns = 0;
-        if (fixed_small + table <= ctx->smem_optin && ntiles <= WALK_WARPS) {
-            ns = (int)std::min<size_t>((ctx->smem_optin - fixed_small) / table, (size_t)(WALK_WARPS / ntiles));
-            if (ntiles > 1) ns = std::min(ns, 15);  // named barriers 1..15
+        if (fixed_small + table <= ctx->smem_optin && ntiles * nch <= WALK_WARPS) {
+            ns = (int)std::min<size_t>((ctx->smem_optin - fixed_small) / table, (size_t)(WALK_WARPS / (ntiles * nch)));
+            if (ntiles * nch > 1) ns = std::min(ns, 15);  // named barriers 1..15
         }
+        wp.slot_chunks = nch;
         wp.slot_tiles = ntiles;
         wp.nslots = ns;
         if (ns > 0) {
