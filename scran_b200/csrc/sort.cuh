@@ -13,10 +13,6 @@
 
 namespace sb {
 
-#ifdef SORT_PROBE
-__device__ long long g_probe[8];
-#endif
-
 constexpr int SORT_THREADS = 1024;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 #ifndef SORT_UNROLL
@@ -117,9 +113,6 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
         P* sp = cur ? pb : pa;
         uint64_t* dk = cur ? ka : kb;
         P* dp = cur ? pa : pb;
-#ifdef SORT_PROBE
-        long long pt0 = clock64();
-#endif
         for (int i = lane; i < 256; i += 32) mine[i] = 0;
         if (tid == 0) aux[32] = 0;
         __syncwarp();
@@ -151,17 +144,8 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
 #endif
         }
         __syncwarp();
-#ifdef SORT_PROBE
-        long long pt1 = clock64();
         __syncthreads();
-        long long pt1b = clock64();
-#else
-        __syncthreads();
-#endif
         scan_digit_histograms(whist, aux, dbase ? -1 : n, dbase, 0u);  // with dbase the pass is never skipped
-#ifdef SORT_PROBE
-        long long pt2 = clock64();
-#endif
         const bool skip = aux[32] != 0;
         if (!skip) {
             // ---- stable reorder: rank inside the 32 by lane order, base from the warp's counters ---
@@ -201,13 +185,7 @@ __device__ int block_radix_sort(uint64_t* ka, P* pa, uint64_t* kb, P* pb, int n,
             }
             cur ^= 1;
         }
-#ifdef SORT_PROBE
-        long long pt3 = clock64();
-#endif
         __syncthreads();
-#ifdef SORT_PROBE
-        if (tid == 0) { g_probe[0] += pt1 - pt0; g_probe[1] += pt1b - pt1; g_probe[2] += pt2 - pt1b; g_probe[3] += pt3 - pt2; g_probe[4] += clock64() - pt3; g_probe[5] += 1; }
-#endif
     }
     return cur;
 }

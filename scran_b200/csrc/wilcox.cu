@@ -35,14 +35,6 @@
 
 namespace sb {
 
-#ifdef SB_PHASE_PROBE
-__device__ unsigned long long g_phase[16];
-#define PHASE_T(v) const long long v = clock64()
-#define PHASE_ADD(k, a, b) do { if (threadIdx.x == 0) atomicAdd(&g_phase[k], (unsigned long long)((b) - (a))); } while (0)
-#else
-#define PHASE_T(v)
-#define PHASE_ADD(k, a, b)
-#endif
 
 namespace {
 
@@ -1634,18 +1626,6 @@ __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
 
 }  // namespace
 
-#ifdef SB_PHASE_PROBE
-void phase_probe_dump() {
-    unsigned long long h[16];
-    cudaMemcpyFromSymbol(h, g_phase, sizeof(h));
-    const char* names[11] = {"tables", "batch build", "batch sort", "batch slot pass", "batch emit", "big pass0 minmax", "big partition (all)", "big group load", "big group sort", "big group emit", "  of which unit hist"};
-    unsigned long long tot = 0;
-    for (int k = 0; k < 10; ++k) tot += h[k];
-    for (int k = 0; k < 11; ++k) fprintf(stderr, "  %-22s %6.2f%%  %8.3f Mcycles per CTA\n", names[k], 100.0 * h[k] / (double)tot, h[k] / 148.0 / 1e6);
-    unsigned long long z[16] = {0};
-    cudaMemcpyToSymbol(g_phase, z, sizeof(z));
-}
-#endif
 
 void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, double lfc, double* d_u, double* d_t) {
     if (L.U == 0 || T.ngenes == 0 || L.npairs == 0) return;
@@ -1740,10 +1720,6 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     SB_LAUNCH(ctx, k3_sort, (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count), SORT_THREADS,
               (size_t)cap_large * 12 + sort_fixed_bytes(cap_large, segcap), sp);
     phase_mark(ctx, PH_SORT);
-#ifdef SB_PHASE_PROBE
-    cudaStreamSynchronize(ctx->stream);
-    phase_probe_dump();
-#endif
 
     // ---- walk ----
     WalkParams wp;
