@@ -12,11 +12,14 @@
 //
 //  k3_plan  one CTA: cuts the (gene, unit) list into jobs: runs of consecutive small units that
 //           together fit the shared-memory sort, or one larger unit on its own.
-//  k3_sort  one CTA per job. Small units are sorted together in one shared-memory radix sort
-//           (key = value, then unit slot). A unit beyond the shared-memory capacity is first
-//           split by value into 256 ordered buckets (one stable pass through L2), then
-//           consecutive buckets are sorted in shared memory. With lfc != 0 every value enters
-//           twice: as b ("R role") and as a - lfc ("L role"), R before L inside a tie.
+//  k3_sort  one CTA per job, no radix passes on the main path: the values go to as many equal-width
+//           VALUE buckets as there are elements (count, scan, scatter in shared memory), after
+//           which an element ranks itself inside its small bucket by counting (which also yields
+//           the tie bit) and writes its label to its final stream position; large buckets (many
+//           equal values) are finished by one warp each. A unit beyond the shared-memory
+//           capacity is first split by value into 256 coarse buckets in global scratch; its fine
+//           buckets then follow the coarse counts. With lfc != 0 every value enters twice: as b
+//           ("R role") and as a - lfc ("L role"), R before L inside a tie.
 //  k3_walk  lane R keeps the running count c_R of label-R entries seen so far (cs_R = the count
 //           at the start of the current tie run) and adds it into row label(i) of a
 //           (G+1) x (G+1) table in shared memory while stepping through the stream: that yields
@@ -26,8 +29,9 @@
 //           2U = nL nR + Bfull[L][R] - Bfull[R][L] in int64, exact. (lfc != 0: the table
 //           accumulates cs_R + c_R at L-role entries and
 //           2U = B[L][R] + z_R B[L][p] + z_L B[p][R] + z_L z_R B[p][p].)
-//           Small units are walked several at a time (one warp group each); large ones by all
-//           warps over position chunks with private tables.
+//           Small units are walked several at a time (one warp group each, k3_walk_small);
+//           large ones by all warps of a CTA over position chunks into one shared table with
+//           atomic adds (k3_walk), the chunks being combined through their label counts.
 //  k3_ties  optional: sum over tie runs of t(t^2-1) per pair, accumulated in double in ascending
 //           value order like src/overlap_exprs.cpp:121-124.
 #include "kernels.h"
