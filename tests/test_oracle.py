@@ -200,3 +200,24 @@ def test_pairwise_layers_match_scipy(port_lib):
         ref = st.ttest_ind(x[:, g == 1], x[:, g == 0], axis=1, equal_var=False).pvalue
     ok = np.isfinite(ref) & (x.var(1) > 1e-6)
     assert np.allclose(np.exp(t["log_p"][ok]), ref[ok], rtol=1e-8)
+
+
+@pytest.mark.parametrize("sparse", [True, False])
+def test_transformed_blocked_stats_pin(port_lib, oracle_lib, sparse):
+    """compute_blocked_stats_lognorm / _norm (src/compute_blocked_stats.cpp:129-185): the port agrees bit
+    for bit with the reference's object code, and both with rowMeans / rowVars of the transformed
+    matrix (what tests/testthat/test-model-var.R checks through modelGeneVarByPoisson's callers)."""
+    rng = np.random.default_rng(23)
+    x = np.where(rng.random((40, 150)) < 0.35, rng.poisson(3.0, (40, 150)).astype(float), 0.0)
+    block = rng.integers(0, 3, 150).astype(np.int32)
+    sf = np.exp(rng.normal(0, 0.3, 150))
+    m = sp.csc_matrix(x) if sparse else x
+    for transform, pseudo in ((2, 1.0), (1, 1.0), (1, 0.5)):
+        pm, pv = port_lib.blocked_stats(m, block, 3, transform=transform, sf=sf, pseudo=pseudo)
+        om, ov = oracle_lib.blocked_stats(m, block, 3, transform=transform, sf=sf, pseudo=pseudo)
+        assert np.array_equal(pm, om, equal_nan=True) and np.array_equal(pv, ov, equal_nan=True)
+        y = x / sf if transform == 2 else np.log(x / sf + pseudo) / np.log(2.0)
+        for b in range(3):
+            keep = block == b
+            assert np.allclose(pm[:, b], y[:, keep].mean(1), rtol=1e-12, atol=1e-14)
+            assert np.allclose(pv[:, b], y[:, keep].var(1, ddof=1), rtol=1e-10, atol=1e-14)
