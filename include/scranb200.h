@@ -61,6 +61,11 @@ int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const
  * freed). Used by the multi-GPU harness and by bench.py's device-resident timing. */
 int scranb200_wrap_device_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, int64_t nnz, const int64_t* d_p,
                               const int32_t* d_i, const double* d_x, scranb200_mat** out);
+/* Frees the handle. The device arrays of an uploaded matrix are kept by its context (at most two
+ * matrices' worth) and reused by the next upload of a similar size, because allocating and freeing
+ * tens of gigabytes costs a tenth of the transfer; they are released by scranb200_ctx_destroy, or
+ * earlier when a device allocation of the library would otherwise fail. Free matrices before their
+ * context. */
 void scranb200_mat_free(scranb200_mat* mat);
 int64_t scranb200_mat_nnz(const scranb200_mat* mat);
 
