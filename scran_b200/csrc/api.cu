@@ -30,6 +30,12 @@ bool release_spares_current() {
     return true;
 }
 
+// A matrix handle is only good with the context that made it, and only while that context lives.
+static void mat_guard(scranb200_ctx* ctx, const scranb200_mat* mat) {
+    if (!mat) throw Error("null matrix");
+    if (mat->ctx != ctx) throw Error("matrix belongs to another context, or its context was destroyed");
+}
+
 void phase_collect(scranb200_ctx* ctx) {
     for (int k = 0; k < PH_N; ++k) ctx->timing[k] = 0.0;
     for (int i = 1; i <= ctx->nev; ++i) {
@@ -140,7 +146,47 @@ scranb200_mat* new_mat(scranb200_ctx* ctx, int64_t nrow, int64_t ncol) {
     m->nrow = nrow;
     m->ncol = ncol;
     m->owned = true;
+    ctx->live_mats.push_back(m);
     return m;
+}
+
+// Frees a half-built matrix when an upload throws (out of memory on a 25 GB array, a malformed `p`).
+struct MatGuard {
+    scranb200_mat* m;
+    explicit MatGuard(scranb200_mat* mm) : m(mm) {}
+    ~MatGuard() {
+        if (m) scranb200_mat_free(m);
+    }
+    scranb200_mat* release() {
+        scranb200_mat* r = m;
+        m = nullptr;
+        return r;
+    }
+};
+
+// Column pointers of a CSC matrix (dgCMatrix @p): p[0] == 0, non-decreasing, no column longer than
+// the matrix has rows, at most 2^32 - 1 stored entries. Everything downstream trusts p[c+1] - p[c]
+// as a length (k1_count, the copies), so a malformed @p is refused here with a message.
+template <typename PT>
+int64_t validate_colptr(const PT* p, int64_t nrow, int64_t ncol) {
+    if (p[0] != 0) throw Error("column pointers 'p' must start at 0");
+    for (int64_t c = 0; c < ncol; ++c) {
+        const int64_t d = (int64_t)p[c + 1] - (int64_t)p[c];
+        if (d < 0) throw Error("column pointers 'p' must be non-decreasing");
+        if (d > nrow) throw Error("a column has more stored entries than the matrix has rows");
+    }
+    const int64_t nnz = (int64_t)p[ncol];
+    if (nnz > 4294967295ll) throw Error("matrix has more than 2^32-1 stored entries; upload it in row blocks");
+    return nnz;
+}
+
+__global__ void check_colptr(const int64_t* __restrict__ p, int64_t nrow, int64_t ncol, int64_t nnz, int* bad) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c == 0 && (p[0] != 0 || p[ncol] != nnz)) *bad = 1;
+    if (c < ncol) {
+        const int64_t d = p[c + 1] - p[c];
+        if (d < 0 || d > nrow) *bad = 1;
+    }
 }
 
 void finish_upload(scranb200_ctx* ctx, scranb200_mat* m, const int32_t* i, const double* x) {
@@ -301,11 +347,28 @@ void scranb200_ctx_destroy(scranb200_ctx* ctx) {
         for (sb::DevBuf* b : bufs) b->release();
         for (auto& sp : ctx->spare) cudaFree(sp.p);
         ctx->spare.clear();
+        for (scranb200_mat* m : ctx->live_mats) {  // matrices that outlive their context keep nothing
+            if (m->owned) {
+                cudaFree(m->d_p);
+                cudaFree(m->d_i);
+                cudaFree(m->d_x);
+            }
+            m->d_p = nullptr;
+            m->d_i = nullptr;
+            m->d_x = nullptr;
+        }
+        for (scranb200_plan* pl : ctx->live_plans) {
+            pl->d_layout.release();
+            pl->d_ints.release();
+            pl->d_dbls.release();
+        }
         for (int k = 0; k < 16; ++k) {
             if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
         }
         cudaStreamDestroy(ctx->stream);
     }
+    for (scranb200_mat* m : ctx->live_mats) m->ctx = nullptr;
+    for (scranb200_plan* pl : ctx->live_plans) pl->ctx = nullptr;
     delete ctx;
 }
 
@@ -330,13 +393,13 @@ int scranb200_upload_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const i
                          const double* x, scranb200_mat** out) {
     API_BEGIN
     ctx_guard(ctx);
-    scranb200_mat* m = new_mat(ctx, nrow, ncol);
-    m->nnz = p[ncol];
-    if (m->nnz < 0) throw Error("negative number of stored entries");
+    MatGuard guard(new_mat(ctx, nrow, ncol));
+    scranb200_mat* m = guard.m;
+    m->nnz = validate_colptr(p, nrow, ncol);
     m->d_p = dev_alloc<int64_t>(ctx, ncol + 1, m->bytes_p);
     SB_CUDA(cudaMemcpyAsync(m->d_p, p, (size_t)(ncol + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
     finish_upload(ctx, m, i, x);
-    *out = m;
+    *out = guard.release();
     API_END
 }
 
@@ -344,22 +407,23 @@ int scranb200_upload_csc32(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const
                            const double* x, scranb200_mat** out) {
     API_BEGIN
     ctx_guard(ctx);
-    scranb200_mat* m = new_mat(ctx, nrow, ncol);
-    m->nnz = p[ncol];
-    if (m->nnz < 0) throw Error("negative number of stored entries");
+    MatGuard guard(new_mat(ctx, nrow, ncol));
+    scranb200_mat* m = guard.m;
+    m->nnz = validate_colptr(p, nrow, ncol);
     m->d_p = dev_alloc<int64_t>(ctx, ncol + 1, m->bytes_p);
     ctx->io_a.reserve((size_t)(ncol + 1) * 4);
     SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, p, (size_t)(ncol + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
     SB_LAUNCH(ctx, widen_i32, (unsigned)ceil_div(ncol + 1, 256), 256, 0, ctx->io_a.as<int32_t>(), ncol + 1, m->d_p);
     finish_upload(ctx, m, i, x);
-    *out = m;
+    *out = guard.release();
     API_END
 }
 
 int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const double* x, scranb200_mat** out) {
     API_BEGIN
     ctx_guard(ctx);
-    scranb200_mat* m = new_mat(ctx, nrow, ncol);
+    MatGuard guard(new_mat(ctx, nrow, ncol));
+    scranb200_mat* m = guard.m;
     const size_t cells = (size_t)nrow * ncol;
     ctx->io_a.reserve(std::max<size_t>(cells, 1) * 8);
     ctx->io_b.reserve((size_t)(ncol + 1) * 8);
@@ -379,7 +443,7 @@ int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const
                   m->d_i, m->d_x);
     }
     SB_CUDA(cudaStreamSynchronize(ctx->stream));
-    *out = m;
+    *out = guard.release();
     API_END
 }
 
@@ -387,18 +451,32 @@ int scranb200_wrap_device_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, in
                               const int32_t* d_i, const double* d_x, scranb200_mat** out) {
     API_BEGIN
     ctx_guard(ctx);
-    scranb200_mat* m = new_mat(ctx, nrow, ncol);
+    if (nnz < 0 || nnz > 4294967295ll) throw Error("matrix has more than 2^32-1 stored entries; wrap it in row blocks");
+    MatGuard guard(new_mat(ctx, nrow, ncol));
+    scranb200_mat* m = guard.m;
     m->owned = false;
     m->nnz = nnz;
     m->d_p = const_cast<int64_t*>(d_p);
     m->d_i = const_cast<int32_t*>(d_i);
     m->d_x = const_cast<double*>(d_x);
-    *out = m;
+    ctx->flags.reserve(64);
+    int* bad = ctx->flags.as<int>();
+    SB_CUDA(cudaMemsetAsync(bad, 0, 4, ctx->stream));
+    SB_LAUNCH(ctx, check_colptr, (unsigned)ceil_div(std::max<int64_t>(1, ncol), 256), 256, 0, d_p, nrow, ncol, nnz, bad);
+    int h_bad = 0;
+    SB_CUDA(cudaMemcpyAsync(&h_bad, bad, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (h_bad) throw Error("column pointers 'p' must start at 0, be non-decreasing, keep every column within nrow entries and end at nnz");
+    *out = guard.release();
     API_END
 }
 
 void scranb200_mat_free(scranb200_mat* mat) {
     if (!mat) return;
+    if (mat->ctx) {  // (null: the context went first and has already released what the matrix held)
+        auto& live = mat->ctx->live_mats;
+        live.erase(std::remove(live.begin(), live.end(), mat), live.end());
+    }
     if (mat->owned && mat->ctx && mat->ctx->owner == getpid()) {
         cudaSetDevice(mat->ctx->device);
         // kept for the next upload; at most two matrices' worth
@@ -419,6 +497,7 @@ int64_t scranb200_mat_nnz(const scranb200_mat* mat) { return mat ? mat->nnz : 0;
 int scranb200_download_csc(scranb200_ctx* ctx, const scranb200_mat* mat, int64_t* p, int32_t* i, double* x) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     SB_CUDA(cudaMemcpyAsync(p, mat->d_p, (size_t)(mat->ncol + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
     if (mat->nnz > 0) {
         SB_CUDA(cudaMemcpyAsync(i, mat->d_i, (size_t)mat->nnz * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -433,6 +512,7 @@ int scranb200_blocked_stats_transformed(scranb200_ctx* ctx, const scranb200_mat*
                                         double* var_out) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     if (transform != 1 && transform != 2) throw Error("transform must be 1 (lognorm) or 2 (norm)");
     if (nblocks < 0) throw Error("negative number of blocks");
     for (int64_t c = 0; c < mat->ncol; ++c) {
@@ -473,6 +553,7 @@ int scranb200_blocked_stats(scranb200_ctx* ctx, const scranb200_mat* mat, const 
                             double* mean_out, double* var_out, double* ndetected_out) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     if (nblocks < 0) throw Error("negative number of blocks");
     for (int64_t c = 0; c < mat->ncol; ++c) {
         if (block[c] >= nblocks) throw Error("block id out of range");
@@ -498,6 +579,7 @@ int scranb200_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, cons
                               double* logp_out, double* logfdr_out) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     if (ngroups < 0 || nblocks < 1) throw Error("bad number of groups or blocks");
     if (direction < 0 || direction > 2) throw Error("direction must be 0 (any), 1 (up) or 2 (down)");
     phase_begin(ctx);
@@ -511,6 +593,7 @@ int scranb200_overlap_exprs_paired(scranb200_ctx* ctx, const scranb200_mat* mat,
                                    const int32_t* group_cells, double lfc, double* u_out, double* ties_out) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     std::vector<int32_t> ids;
     groups_to_ids(mat->ncol, ngroups, group_ptr, group_cells, ids);
     std::vector<int32_t> l0(npairs), r0(npairs);
@@ -538,6 +621,7 @@ int scranb200_overlap_exprs(scranb200_ctx* ctx, const scranb200_mat* mat, int ng
                             const int32_t* group_cells, double lfc, double* u_out, double* ties_out) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     std::vector<int32_t> ids;
     groups_to_ids(mat->ncol, ngroups, group_ptr, group_cells, ids);
     std::vector<int32_t> l0, r0;
@@ -594,7 +678,10 @@ int scranb200_plan_create(scranb200_ctx* ctx, int64_t ncells, const int32_t* gro
     scranb200_plan* P = new scranb200_plan();
     try {
         build_plan(*P, ncells, groups, ngroups, block, des_left, des_right, ndesired, lfc);
-        if (ctx) upload_plan(ctx, *P);
+        if (ctx) {
+            upload_plan(ctx, *P);
+            ctx->live_plans.push_back(P);
+        }
     } catch (...) {
         delete P;
         throw;
@@ -605,6 +692,10 @@ int scranb200_plan_create(scranb200_ctx* ctx, int64_t ncells, const int32_t* gro
 
 void scranb200_plan_destroy(scranb200_plan* plan) {
     if (!plan) return;
+    if (plan->ctx) {
+        auto& live = plan->ctx->live_plans;
+        live.erase(std::remove(live.begin(), live.end(), plan), live.end());
+    }
     if (plan->ctx && plan->ctx->owner == getpid()) {
         cudaSetDevice(plan->ctx->device);
         plan->d_layout.release();
@@ -648,6 +739,7 @@ int scranb200_score_effects_dev(scranb200_ctx* ctx, const scranb200_mat* mat, co
                                 int64_t ld, int64_t row0, double* d_eff, double* d_out) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     phase_begin(ctx);
     score_stage1(ctx, mat, plan, ld, row0, d_eff, d_out);
     SB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -681,6 +773,7 @@ int scranb200_score_markers(scranb200_ctx* ctx, const scranb200_mat* mat, const 
                             double* full_out) {
     API_BEGIN
     ctx_guard(ctx);
+    mat_guard(ctx, mat);
     const int64_t ngenes = mat->nrow;
     const size_t n_eff = (size_t)3 * std::max(1, plan->Q) * std::max<int64_t>(1, ngenes);
     const size_t n_out = (size_t)std::max(1, plan->K) * SCRANB200_NCOLS * std::max<int64_t>(1, ngenes);

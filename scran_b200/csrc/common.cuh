@@ -65,6 +65,9 @@ enum Phase { PH_TRANSPOSE = 0, PH_STATS, PH_SORT, PH_COUNT, PH_EFFECTS, PH_SUMMA
 
 }  // namespace sb
 
+struct scranb200_mat;
+struct scranb200_plan;
+
 struct scranb200_ctx {
     int device = 0;
     pid_t owner = 0;
@@ -87,6 +90,10 @@ struct scranb200_ctx {
         size_t bytes;
     };
     std::vector<Spare> spare;
+    // live matrices and plans of this context: scranb200_ctx_destroy orphans them (frees their device
+    // memory, clears their back-pointer), so that a later mat_free / plan_destroy only deletes the handle
+    std::vector<scranb200_mat*> live_mats;
+    std::vector<scranb200_plan*> live_plans;
 };
 
 struct scranb200_mat {

@@ -190,6 +190,7 @@ extern "C" int scranb200_synth_csc(scranb200_ctx* ctx, int64_t ngenes_total, int
         m->nrow = n;
         m->ncol = ncells;
         m->owned = true;
+        ctx->live_mats.push_back(m);
         void* pp = nullptr;
         SB_CUDA(cudaMalloc(&pp, (size_t)(ncells + 1) * 8));
         m->d_p = (int64_t*)pp;

@@ -3,14 +3,16 @@
 // (src/overlap_exprs.cpp:171,211 and :37-47) and the column walk of
 // src/compute_blocked_stats.cpp:53-56 with one O(nnz) counting sort.
 //
-// Why it is stable without atomics: the cells are visited in (combination, cell) order, one
-// chunk of columns per CTA, one column at a time. Inside one column every gene occurs at most
-// once (dgCMatrix invariant, validated in the counting pass), so the threads of a CTA can bump
-// the per-gene cursor in shared memory with plain loads and stores; the barrier between two
-// columns orders the cursor updates of consecutive cells. The per-chunk gene histograms are
-// scanned in (gene, chunk) order, which yields for every (gene, combination) a contiguous
-// segment holding that gene's stored values of that combination in ascending cell order:
-// exactly the sequence the reference's running mean/variance update consumes.
+// Why it is stable without global atomics: the cells are visited in (combination, cell) order,
+// cut into chunks of columns. The counting pass (k1_count) gives, per chunk, every gene's number
+// of stored entries; scanned in (gene, chunk) order that is where each chunk's part of every
+// (gene, combination) segment starts. The scatter (k1_scatter_warp) gives every warp one chunk
+// and one sub-range of 256 genes: it walks the chunk's columns in order, and inside one column
+// every gene occurs at most once (dgCMatrix invariant, validated in the counting pass), so the
+// per-gene write cursors in shared memory are bumped with plain loads and stores; a __syncwarp
+// between two columns orders the updates of consecutive cells. Every segment therefore holds its
+// gene's stored values of that combination in ascending cell order: exactly the sequence the
+// reference's running mean / variance update consumes.
 #include "kernels.h"
 
 namespace sb {
@@ -18,38 +20,9 @@ namespace sb {
 namespace {
 
 constexpr int K1_THREADS = 1024;
-constexpr int K1_R = 3;          // elements per thread held in registers per column (covers 3072 per column)
 constexpr int K1_SUB_SHIFT = 8;  // gene sub-ranges of 256: one scatter warp each
 constexpr int K1_SUB = 1 << K1_SUB_SHIFT;
 constexpr int K1_MAXCOLS = MAX_CHUNK_COLS;  // columns per chunk (their bounds are staged in shared memory)
-
-// A column's first K1_R * K1_THREADS entries, prefetched into registers while earlier columns
-// are being applied; three of these rotate so that three columns are in flight per CTA.
-template <bool WITH_VALUES>
-struct ColStage {
-    int32_t g[K1_R];
-    double v[K1_R];
-    int64_t lo;
-    int n;
-    __device__ __forceinline__ void load(const int64_t* s_lo, const int* s_n, int j, int ncols,
-                                         const int32_t* __restrict__ idx, const double* __restrict__ x) {
-        n = 0;
-        lo = 0;
-        if (j < ncols) {
-            lo = s_lo[j];
-            n = s_n[j];
-        }
-#pragma unroll
-        for (int r = 0; r < K1_R; ++r) {
-            const int k = r * K1_THREADS + (int)threadIdx.x;
-            g[r] = -1;
-            if (k < n) {
-                g[r] = idx[lo + k];
-                if (WITH_VALUES) v[r] = x[lo + k];
-            }
-        }
-    }
-};
 
 // Stages the bounds of the chunk's columns in shared memory. Returns the number of columns.
 __device__ inline int stage_bounds(const int64_t* __restrict__ p, const int32_t* __restrict__ perm, int c_lo, int c_hi,
@@ -194,156 +167,13 @@ __global__ void __launch_bounds__(1024) k1_scan_rows(const uint32_t* __restrict_
     if (t == 1023) row_ptr[ngenes] = part[1023];
 }
 
-// For every used column (in permuted order) and every gene range r: where the entries with
-// gene >= r * GR start inside the column. split: [nranges + 1][ncols] offsets relative to p[c].
-__global__ void __launch_bounds__(256)
-k1_split(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const int32_t* __restrict__ perm, int ncols,
-         int GR, int nranges, uint32_t* __restrict__ split) {
-    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pos >= ncols) return;
-    const int c = perm[pos];
-    const int64_t lo = p[c];
-    const uint32_t len = (uint32_t)(p[c + 1] - lo);
-    split[pos] = 0;
-    uint32_t from = 0;
-    for (int r = 1; r < nranges; ++r) {
-        const int target = r * GR;
-        uint32_t a = from, b = len;  // first entry with gene >= target
-        while (a < b) {
-            const uint32_t mid = (a + b) >> 1;
-            if (idx[lo + mid] < target) a = mid + 1; else b = mid;
-        }
-        split[(size_t)r * ncols + pos] = a;
-        from = a;
-    }
-    split[(size_t)nranges * ncols + pos] = len;
-}
-
-constexpr int K1S_THREADS = 256;
-constexpr int K1S_GR = 2048;  // genes per scatter CTA: cursor + start + 4 staged values = 40 B per gene
-
-// Register stage of one column slice: R entries per thread (R * 256 entries in all; longer
-// slices finish through direct loads). D of these rotate, so D column slices are in flight.
-template <int R>
-struct SliceStage {
-    int32_t g[R];
-    double v[R];
-    int64_t lo;
-    int n;
-    __device__ __forceinline__ void load(const int64_t* s_lo, const int* s_n, int j, int ncols,
-                                         const int32_t* __restrict__ idx, const double* __restrict__ x) {
-        n = 0;
-        lo = 0;
-        if (j < ncols) {
-            lo = s_lo[j];
-            n = s_n[j];
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int k = r * K1S_THREADS + (int)threadIdx.x;
-            g[r] = -1;
-            if (k < n) {
-                g[r] = idx[lo + k];
-                v[r] = x[lo + k];
-            }
-        }
-    }
-};
-
-// Pass B: scatter the values. One CTA owns (chunk of columns) x (range of GR genes). Per gene it
-// keeps the write cursor and the last up-to-4 values in shared memory, and writes a 32-byte
-// sector to HBM only when the sector is complete (or at the end of the chunk), so that the
-// gene-major array is written in whole sectors instead of one scattered 8-byte store per entry.
-template <int R, int D>
-__global__ void __launch_bounds__(K1S_THREADS)
-k1_scatter(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
-           const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int GR, int nranges,
-           int ncols_all, const uint32_t* __restrict__ split, const uint32_t* __restrict__ table,
-           const int64_t* __restrict__ row_ptr, double* __restrict__ vals) {
-    extern __shared__ __align__(16) unsigned char k1_smem[];
-    int64_t* s_lo = reinterpret_cast<int64_t*>(k1_smem);
-    double* stage = reinterpret_cast<double*>(s_lo + K1_MAXCOLS);       // [GR][4]
-    int* s_n = reinterpret_cast<int*>(stage + (size_t)GR * 4);
-    uint32_t* cursor = reinterpret_cast<uint32_t*>(s_n + K1_MAXCOLS);   // [GR]
-    uint32_t* first = cursor + GR;                                      // [GR]
-    const int chunk = blockIdx.x / nranges, r = blockIdx.x % nranges;
-    const int g0 = r * GR, glen = min(GR, ngenes - g0);
-    for (int g = threadIdx.x; g < glen; g += blockDim.x) {
-        const uint32_t at = (uint32_t)(row_ptr[g0 + g] + table[(size_t)chunk * ngenes + g0 + g]);
-        cursor[g] = at;
-        first[g] = at;
-    }
-    const int c_lo = chunk_start[chunk], c_hi = chunk_start[chunk + 1];
-    const int ncols = c_hi - c_lo;
-    for (int j = threadIdx.x; j < ncols; j += blockDim.x) {
-        const int c = perm[c_lo + j];
-        uint32_t a = 0, b;
-        if (nranges > 1) {
-            a = split[(size_t)r * ncols_all + c_lo + j];
-            b = split[(size_t)(r + 1) * ncols_all + c_lo + j];
-        } else {
-            b = (uint32_t)(p[c + 1] - p[c]);
-        }
-        s_lo[j] = p[c] + a;
-        s_n[j] = (int)(b - a);
-    }
-    __syncthreads();
-
-    auto put = [&](int g, double v) {
-        const unsigned gl = (unsigned)(g - g0);
-        if (gl >= (unsigned)glen) return;  // only reachable with an invalid (unsorted) matrix, reported by pass A
-        const uint32_t at = cursor[gl];
-        cursor[gl] = at + 1;
-        double* sg = stage + (size_t)gl * 4;
-        sg[at & 3u] = v;
-        if ((at & 3u) == 3u) {
-            const uint32_t base = at - 3u, f = first[gl];
-            if (base >= f) {  // a whole 32-byte sector
-                double2* dst = reinterpret_cast<double2*>(vals + base);
-                dst[0] = make_double2(sg[0], sg[1]);
-                dst[1] = make_double2(sg[2], v);
-            } else {          // the sector started in an earlier chunk: write only our part
-                for (uint32_t s = f; s < at; ++s) vals[s] = sg[s & 3u];
-                vals[at] = v;
-            }
-        }
-    };
-    auto apply = [&](SliceStage<R>& st) {
-#pragma unroll
-        for (int q = 0; q < R; ++q) {
-            if (st.g[q] >= 0) put(st.g[q], st.v[q]);
-        }
-        for (int k = R * K1S_THREADS + (int)threadIdx.x; k < st.n; k += K1S_THREADS) put(idx[st.lo + k], x[st.lo + k]);
-    };
-
-    SliceStage<R> ring[D];
-#pragma unroll
-    for (int q = 0; q < D; ++q) ring[q].load(s_lo, s_n, q, ncols, idx, x);
-    for (int j = 0; j < ncols; j += D) {
-#pragma unroll
-        for (int q = 0; q < D; ++q) {
-            if (j + q < ncols) apply(ring[q]);
-            __syncthreads();
-            ring[q].load(s_lo, s_n, j + q + D, ncols, idx, x);
-        }
-    }
-    // flush the incomplete last sector of every gene
-    for (int g = threadIdx.x; g < glen; g += blockDim.x) {
-        const uint32_t c = cursor[g], f = first[g];
-        if ((c & 3u) != 0u && c > f) {
-            const uint32_t from = max(f, c & ~3u);
-            for (uint32_t s = from; s < c; ++s) vals[s] = stage[(size_t)g * 4 + (s & 3u)];
-        }
-    }
-}
-
 // Pass B, one warp per (chunk, sub-range of K1_SUB genes). A gene's entries must be appended in
 // column order, but different gene ranges are independent of each other: with the positions where
 // every sub-range starts inside every column (sub_split, written by the counting pass) a warp can
 // walk the chunk's columns on its own, one short slice (its genes' entries of that column) a step,
 // with no barrier shared with other warps. The slices of the next columns are fetched while the
 // current one is applied (K1W_DEPTH in flight). Per gene the write cursor and the last up-to-4 values
-// are staged in shared memory, so that HBM sees whole 32-byte sectors, as in k1_scatter.
+// are staged in shared memory, so that HBM sees whole 32-byte sectors.
 constexpr int K1W_WARPS = 4;
 constexpr int K1W_DEPTH = 8;
 
@@ -471,16 +301,12 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
     const int glen_all = (int)ceil_div(ngenes, nranges);
     allow_smem(k1_count, (size_t)glen_all * 4 + bounds_bytes);
 
-    // the warp-per-sub-range scatter needs, per column, where every sub-range of K1_SUB genes starts
-    const char* old_env = getenv("SCRANB200_K1_BLOCK_SCATTER");  // "1": the older CTA-per-2048-genes scatter (kept for comparison)
-    const bool warp_scatter = !(old_env && old_env[0] == '1');
+    // the scatter needs, per column, where every sub-range of K1_SUB genes starts
     const int nsub = (int)ceil_div(ngenes, K1_SUB);
     uint32_t* sub_split = nullptr;
-    if (warp_scatter && L.nchunks > 0 && ngenes > 0) {
+    if (L.nchunks > 0 && ngenes > 0) {
         ctx->split.reserve((size_t)(nsub + 1) * L.perm.size() * 4 + 64);
         sub_split = ctx->split.as<uint32_t>();
-    }
-    if (L.nchunks > 0 && ngenes > 0) {
         for (int r = 0; r < nranges; ++r) {
             const int g0 = r * glen_all, glen = std::min(glen_all, ngenes - g0);
             SB_LAUNCH(ctx, k1_count, L.nchunks, K1_THREADS, (size_t)glen * 4 + bounds_bytes, mat->d_p, mat->d_i, L.d_perm,
@@ -492,38 +318,11 @@ void run_transpose(scranb200_ctx* ctx, const scranb200_mat* mat, const PairLayou
                   ctx->seg_off.as<uint32_t>(), ctx->row_total.as<uint32_t>());
     }
     SB_LAUNCH(ctx, k1_scan_rows, 1, 1024, 0, ctx->row_total.as<uint32_t>(), ngenes, ctx->row_ptr.as<int64_t>());
-    if (warp_scatter && L.nchunks > 0 && ngenes > 0) {
+    if (L.nchunks > 0 && ngenes > 0) {
         const int64_t grid = (int64_t)L.nchunks * ceil_div(nsub, K1W_WARPS);
         if (grid > 2147483647ll) throw Error("too many transpose tiles");
         SB_LAUNCH(ctx, k1_scatter_warp, (unsigned)grid, K1W_WARPS * 32, 0, mat->d_p, mat->d_i, mat->d_x, L.d_perm, L.d_chunk_start,
                   ngenes, nsub, sub_split, table, T.row_ptr, T.vals);
-    } else if (L.nchunks > 0 && ngenes > 0) {
-        // Scatter pass: (chunk) x (range of K1S_GR genes) CTAs.
-        const int GR = K1S_GR;
-        const int sranges = (int)ceil_div(ngenes, GR);
-        const int ncols = (int)L.perm.size();
-        const uint32_t* split = nullptr;
-        if (sranges > 1) {
-            ctx->split.reserve((size_t)(sranges + 1) * ncols * 4);
-            SB_LAUNCH(ctx, k1_split, (unsigned)ceil_div(ncols, 256), 256, 0, mat->d_p, mat->d_i, L.d_perm, ncols, GR, sranges,
-                      ctx->split.as<uint32_t>());
-            split = ctx->split.as<uint32_t>();
-        }
-        const size_t smem = (size_t)K1_MAXCOLS * 12 + (size_t)GR * 40;
-        const int64_t grid = (int64_t)L.nchunks * sranges;
-        if (grid > 2147483647ll) throw Error("too many transpose tiles");
-        // entries of one column that fall into one gene range, on average
-        const double slice = (double)mat->nnz / std::max(1, (int)mat->ncol) / sranges;
-#define SB_SCATTER(RR, DD)                                                                                          \
-    do {                                                                                                            \
-        allow_smem(k1_scatter<RR, DD>, smem);                                                                       \
-        SB_LAUNCH(ctx, (k1_scatter<RR, DD>), (unsigned)grid, K1S_THREADS, smem, mat->d_p, mat->d_i, mat->d_x, L.d_perm, \
-                  L.d_chunk_start, ngenes, GR, sranges, ncols, split, table, T.row_ptr, T.vals);                    \
-    } while (0)
-        if (slice <= 200.0) SB_SCATTER(1, 8);
-        else if (slice <= 450.0) SB_SCATTER(2, 4);
-        else SB_SCATTER(4, 2);
-#undef SB_SCATTER
     }
     int h_bad = 0;
     SB_CUDA(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
