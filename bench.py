@@ -191,6 +191,54 @@ def run_reference(args, w):
     print(json.dumps(line))
 
 
+def shard_starts(w, world):
+    """Gene ranges of equal expected nnz (housekeeping genes are ten times heavier
+    than the average, so equal gene counts leave the ranks unbalanced): int64[world + 1]."""
+    from scran_b200._lib import check, lib, ptr
+    from scran_b200.distributed import balanced_row_starts
+    wts = np.zeros(w["ngenes"], np.float64)
+    check(lib().scranb200_synth_row_weights(w["ngenes"], w["ncells"], float(w["density"]), int(w["seed"]), ptr(wts)))
+    return balanced_row_starts(wts, world)
+
+
+def multi_gpu_check(scran_b200, ctx, rank, world, dist):
+    """Before anything is timed at N > 1: a config-2-sized matrix (33,538 x 100,000, 20 groups, 4 batches)
+    is scored sharded over all ranks and, on rank 0, whole through the fused single-GPU call; the two
+    [K][19][ngenes] tables must be bit-identical (the reference's multi-worker == serial check,
+    tests/testthat/test-pairwise-wilcox.R:287-296). Exits non-zero otherwise."""
+    from scran_b200.distributed import ShardedScorer
+    w = dict(WORKLOADS["config2"])
+    groups, block = labels_for(w)
+    starts = shard_starts(w, world)
+    plan = scran_b200.ScorePlan(groups.tolist(), block.tolist(), None, 0.0, ctx=ctx)
+    scorer = ShardedScorer(ctx, plan, w["ngenes"], rank, world, dist, row_starts=starts, root=0)
+    part = scran_b200.DeviceMatrix.synthetic(ctx, w["ngenes"], int(starts[rank]), int(starts[rank + 1]), w["ncells"], groups,
+                                             w["G"], w["density"], w["seed"])
+    got = np.zeros((plan.K, 19, w["ngenes"]), np.float64) if rank == 0 else None
+    scorer.step(part, got)
+    part.free()
+    note = None
+    if rank == 0:
+        from scran_b200._lib import check, lib, ptr
+        whole = scran_b200.DeviceMatrix.synthetic(ctx, w["ngenes"], 0, w["ngenes"], w["ncells"], groups, w["G"], w["density"],
+                                                  w["seed"])
+        want = np.zeros_like(got)
+        check(lib().scranb200_score_markers(ctx.handle, whole.handle, plan.handle, ptr(want), None))
+        whole.free()
+        same = np.array_equal(got, want, equal_nan=True)
+        note = "bit-identical" if same else "MISMATCH"
+        if not same:
+            bad = np.argwhere(~((got == want) | (np.isnan(got) & np.isnan(want))))
+            print(json.dumps({"multi_gpu_check": "MISMATCH", "n_gpus": world, "first_bad": bad[:5].tolist()}), flush=True)
+    flag = [note]
+    dist.broadcast_object_list(flag, 0)
+    plan.free()
+    if flag[0] != "bit-identical":
+        dist.destroy_process_group()
+        sys.exit(3)
+    return "bit-identical: config2 (33538 x 100000, 20 groups, 4 batches) sharded over %d ranks == fused single-GPU call" % world
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -213,7 +261,7 @@ def main():
 
     import scran_b200
     from scran_b200._lib import check, lib, ptr
-    from scran_b200.distributed import ShardedScorer, shard_ranges
+    from scran_b200.distributed import ShardedScorer
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -232,19 +280,24 @@ def main():
 
     ctx = scran_b200.Context(local)
     groups, block = labels_for(w)
-    granges, per = shard_ranges(w["ngenes"], world)
-    g0, g1 = granges[rank]
+    row_starts = shard_starts(w, world)
+    g0, g1 = int(row_starts[rank]), int(row_starts[rank + 1])
+    check_note = multi_gpu_check(scran_b200, ctx, rank, world, dist) if world > 1 else None
     t_gen = time.perf_counter()
     mat = scran_b200.DeviceMatrix.synthetic(ctx, w["ngenes"], g0, g1, w["ncells"], groups, w["G"], w["density"], w["seed"])
     t_gen = time.perf_counter() - t_gen
     nnz_local = mat.nnz
     nnz_t = torch.tensor([nnz_local], dtype=torch.int64, device="cuda")
+    nnz_all = [torch.zeros_like(nnz_t) for _ in range(world)]
     if world > 1:
-        dist.all_reduce(nnz_t)
-    nnz = int(nnz_t.item())
+        dist.all_gather(nnz_all, nnz_t)
+    else:
+        nnz_all = [nnz_t]
+    nnz_ranks = [int(t.item()) for t in nnz_all]
+    nnz = sum(nnz_ranks)
 
     plan = scran_b200.ScorePlan(groups.tolist(), None if block is None else block.tolist(), None, 0.0, ctx=ctx)
-    scorer = ShardedScorer(ctx, plan, w["ngenes"], rank, world, dist)
+    scorer = ShardedScorer(ctx, plan, w["ngenes"], rank, world, dist, row_starts=row_starts, root=0)
     P = w["G"] * (w["G"] - 1) // 2
     gene_pairs = w["ngenes"] * P
     ext = torch.cuda.ExternalStream(lib().scranb200_ctx_stream(ctx.handle), device=torch.device("cuda", local))
@@ -276,17 +329,20 @@ def main():
         phase_ms[k] /= args.steps
     value = gene_pairs / (ms_step * 1e-3)
 
-    # ---- end to end through the host-buffer C-ABI call --------------------------------------
+    # ---- end to end through the host-buffer C-ABI calls --------------------------------------
+    # N = 1: scranb200_upload_csc + scranb200_score_markers. N > 1: every rank uploads its row block and
+    # all ranks run scranb200_score_markers_sharded; the complete [K][19][ngenes] table (min-ranks over
+    # ALL genes) lands in the root's host buffer. Timed with the host clock around barriers.
     e2e = None
     if not args.no_e2e:
         p_h, i_h, x_h = mat.download()
         mat.free()
-        del scorer
         torch.cuda.empty_cache()
         pin = [torch.from_numpy(a).pin_memory() for a in (p_h, i_h, x_h)]
         del p_h, i_h, x_h
         nrow = g1 - g0
-        out_h = torch.empty((max(1, plan.K), 19, nrow), dtype=torch.float64).pin_memory()
+        out_rows = w["ngenes"] if (world > 1 and rank == 0) else nrow
+        out_h = torch.empty((max(1, plan.K), 19, max(1, out_rows)), dtype=torch.float64).pin_memory()
         L = lib()
 
         def e2e_step():
@@ -294,7 +350,11 @@ def main():
             h = C.c_void_p()
             check(L.scranb200_upload_csc(ctx.handle, nrow, w["ncells"], ptr(pin[0]), ptr(pin[1]), ptr(pin[2]), C.byref(h)))
             try:
-                check(L.scranb200_score_markers(ctx.handle, h, plan.handle, ptr(out_h), None))
+                if world == 1:
+                    check(L.scranb200_score_markers(ctx.handle, h, plan.handle, ptr(out_h), None))
+                else:
+                    check(L.scranb200_score_markers_sharded(ctx.handle, h, plan.handle, w["ngenes"], ptr(scorer.row_starts), 0,
+                                                            ptr(out_h) if rank == 0 else None, None))
             finally:
                 L.scranb200_mat_free(h)
 
@@ -307,15 +367,16 @@ def main():
         barrier()
         dt = (time.perf_counter() - t0) / n_e2e
         t_e = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        h2d_t = torch.tensor([sum(int(a.numel() * a.element_size()) for a in pin)], dtype=torch.int64, device="cuda")
         if world > 1:
             dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-        h2d = sum(int(a.numel() * a.element_size()) for a in pin)
-        d2h = int(out_h.numel() * 8)
-        # N > 1: every rank scores its own gene shard end to end; ranks are local (min-rank over the shard),
-        # so the multi-GPU e2e figure is the per-shard pipeline, stated here rather than hidden.
-        e2e = {"value": gene_pairs / float(t_e.item()), "unit": "gene·pairs/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "ms_per_step": float(t_e.item()) * 1e3,
-               "call": "scranb200_upload_csc + scranb200_score_markers (host buffers, pinned)"}
+            dist.all_reduce(h2d_t)
+        d2h = int(max(1, plan.K) * 19 * w["ngenes"] * 8)
+        e2e = {"value": gene_pairs / float(t_e.item()), "unit": "gene·pairs/s", "h2d_bytes_per_step": int(h2d_t.item()),
+               "d2h_bytes_per_step": d2h, "ms_per_step": float(t_e.item()) * 1e3, "host_memory": "pinned",
+               "call": "scranb200_upload_csc + scranb200_score_markers (host buffers)" if world == 1 else
+                       "per rank scranb200_upload_csc of its row block + scranb200_score_markers_sharded; complete table "
+                       "(min-ranks over all genes) to the root's host buffer"}
 
     if rank != 0:
         if world > 1:
@@ -363,11 +424,14 @@ def main():
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, **{k: w[k] for k in ("ngenes", "ncells", "G", "B", "density")},
-                   "nnz": nnz, "pairs": P, "block_level_pairs": plan.npairs, "sharding": "genes x%d" % world,
+                   "nnz": nnz, "pairs": P, "block_level_pairs": plan.npairs,
+                   "sharding": "genes x%d, ranges of equal expected nnz" % world, "nnz_per_rank": nnz_ranks,
                    "l2": "inputs (%.1f GB) larger than L2" % (nnz * 12 / 1e9)},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "cpu_baseline": cpu, "synth_seconds": round(t_gen, 2),
     }
+    if check_note:
+        line["multi_gpu_check"] = check_note
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -191,6 +191,36 @@ int scranb200_score_finish_dev(scranb200_ctx* ctx, const scranb200_plan* plan, i
                                const int32_t* d_minrank, double* d_out);
 int scranb200_fill_i32(scranb200_ctx* ctx, int32_t* d_ptr, int64_t n, int32_t value);
 
+/* ---- gene-sharded scoreMarkers across the GPUs of one box -------------------------------------
+ * Replaces what beachmat::rowBlockApply + BiocParallel do for the reference (R/scoreMarkers.R:
+ * 234-248: one worker per row block, results rbind-ed) together with the min-rank over ALL genes
+ * after the join (:251-256). A rank is one context (one GPU) holding the rows
+ * [row_starts[r], row_starts[r+1]) of the matrix for all cells; ranks are either processes (one
+ * context each) or the contexts of one process (one host thread per context while scoring).
+ * The exchange (effect columns from gene shards to comparison shards, MIN-combination of the
+ * per-table ranks, gather of the result rows) runs inside the library over NCCL, which is loaded
+ * at run time (libnccl.so.2) on the first of these calls.
+ *
+ * scranb200_comm_unique_id: rank 0 makes the 128-byte id and hands it to the others by any means.
+ * scranb200_ctx_comm_init:  collective over the world ranks. world == 1 needs no NCCL.
+ * scranb200_ctx_comm_init_all: the same for n contexts of THIS process (ncclCommInitAll).
+ * scranb200_balance_rows: contiguous row ranges of equal total weight (weight = stored entries per
+ *   gene; housekeeping genes are ten times heavier than the average): row_starts[world + 1].
+ * scranb200_score_markers_sharded: collective. mat = this rank's row block (row_starts[rank+1] -
+ *   row_starts[rank] rows), plan = the same plan on every rank. root >= 0: only that rank
+ *   receives the result; root < 0: every rank. out (nullable, host): [K][19][ngenes_total] as
+ *   scranb200_score_markers writes it; d_out (nullable): receives the DEVICE address of the same
+ *   table inside the context's scratch (valid until the context's next call; null on ranks that
+ *   do not receive the result). */
+#define SCRANB200_COMM_ID_BYTES 128
+int scranb200_comm_unique_id(char* id_out);
+int scranb200_ctx_comm_init(scranb200_ctx* ctx, int world, int rank, const char* id_in);
+int scranb200_ctx_comm_init_all(scranb200_ctx** ctxs, int n);
+int scranb200_balance_rows(const double* weight, int64_t nrow, int world, int64_t* row_starts);
+int scranb200_score_markers_sharded(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan,
+                                    int64_t ngenes_total, const int64_t* row_starts, int root, double* out,
+                                    double** d_out);
+
 /* ---- computeMinRank: R/computeMinRank.R:45-50 (ties.method="min", decreasing=TRUE) ----------
  * x: nrow x ncol column-major; out[nrow]: min over columns of (1 + number of non-NaN entries of
  * the column strictly greater), NaN entries ignored; INT32_MAX if a row has none. */
@@ -224,6 +254,8 @@ int scranb200_compute_min_rank_static(scranb200_ctx* ctx, const double* d_x, int
  * returned matrix. density < 0: natural Poisson density (config 1). */
 int scranb200_synth_csc(scranb200_ctx* ctx, int64_t ngenes_total, int64_t g0, int64_t g1, int64_t ncells,
                         const int32_t* groups, int ngroups, double density, uint64_t seed, scranb200_mat** out);
+/* Expected stored entries per gene of that matrix (weights for scranb200_balance_rows). */
+int scranb200_synth_row_weights(int64_t ngenes_total, int64_t ncells, double density, uint64_t seed, double* weight);
 /* Copy a device matrix's CSC arrays to host buffers (sizes from nrow/ncol/scranb200_mat_nnz). */
 int scranb200_download_csc(scranb200_ctx* ctx, const scranb200_mat* mat, int64_t* p, int32_t* i, double* x);
 

@@ -248,7 +248,7 @@ void run_pairs(scranb200_ctx* ctx, const scranb200_mat* mat, PairLayout& L, DevB
     }
 }
 
-namespace {
+void comm_release(scranb200_ctx* ctx);  // dist.cu
 
 void score_stage1(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan, int64_t ld, int64_t row0,
                   double* d_eff, double* d_out) {
@@ -262,6 +262,8 @@ void score_stage1(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_
     run_summaries(ctx, *plan, (int)mat->nrow, ld, row0, d_eff, d_out);
     phase_mark(ctx, PH_SUMMARY);
 }
+
+namespace {
 
 // The transformers of src/compute_blocked_stats.cpp:129-177 applied to the stored values: one warp per
 // column (the size factor belongs to the column). lognorm: log(x / sf + pseudo) / M_LN2 (:136), the
@@ -343,7 +345,9 @@ void scranb200_ctx_destroy(scranb200_ctx* ctx) {
                               &ctx->unit_m, &ctx->sort_keys, &ctx->sort_labs, &ctx->flags, &ctx->mean, &ctx->var,
                               &ctx->ndet, &ctx->u_pairs, &ctx->t_pairs, &ctx->layout_i32, &ctx->layout_f64, &ctx->eff,
                               &ctx->out, &ctx->minrank, &ctx->rank_keys, &ctx->rank_idx, &ctx->plan_tmp, &ctx->io_a,
-                              &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit, &ctx->jobs, &ctx->split, &ctx->vmin, &ctx->vmax};
+                              &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit, &ctx->jobs, &ctx->split, &ctx->vmin, &ctx->vmax,
+                              &ctx->xchg_part, &ctx->xchg_recv, &ctx->xchg_cols};
+        sb::comm_release(ctx);
         for (sb::DevBuf* b : bufs) b->release();
         for (auto& sp : ctx->spare) cudaFree(sp.p);
         ctx->spare.clear();

@@ -82,6 +82,10 @@ struct scranb200_ctx {
     // scratch, named by role (sizes at config 3 in DESIGN.md)
     sb::DevBuf table, seg_off, row_total, row_ptr, vals, stream_lab, unit_m, sort_keys, sort_labs, flags;
     sb::DevBuf mean, var, ndet, u_pairs, t_pairs, layout_i32, layout_f64;
+    // gene-sharded runs (dist.cu): the NCCL communicator (an ncclComm_t, null for world == 1) and the exchange buffers
+    void* comm = nullptr;
+    int world = 1, rank = 0;
+    sb::DevBuf xchg_part, xchg_recv, xchg_cols;
     sb::DevBuf eff, out, minrank, rank_keys, rank_idx, plan_tmp, io_a, io_b, io_c, grp_avg, logit, jobs, split, vmin, vmax;
     // device arrays of freed matrices, kept for the next upload of a similar size (cudaMalloc / cudaFree of
     // tens of gigabytes costs as much as a tenth of the transfer itself)

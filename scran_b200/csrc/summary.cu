@@ -595,13 +595,14 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
     }
 }
 
-__global__ void k5_finish(const int32_t* minrank, int64_t ngenes, int64_t ld, int K, double* out) {
+// minrank: [K][3][ngenes]; rows [row0, row0 + nrows) go to rows [0, nrows) of out [K][19][ld].
+__global__ void k5_finish(const int32_t* minrank, int64_t ngenes, int64_t row0, int64_t nrows, int64_t ld, int K, double* out) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= ngenes * K * 3) return;
-    const int64_t g = t % ngenes;
-    const int ke = (int)(t / ngenes);
+    if (t >= nrows * K * 3) return;
+    const int64_t g = t % nrows;
+    const int ke = (int)(t / nrows);
     const int k = ke / 3, e = ke % 3;
-    const int32_t r = minrank[t];
+    const int32_t r = minrank[(size_t)ke * ngenes + row0 + g];
     const double inf = __longlong_as_double(0x7ff0000000000000ll);
     out[((size_t)k * SCRANB200_NCOLS + 4 + 5 * e + 4) * ld + g] = r == INT32_MAX ? inf : (double)r;
 }
@@ -719,14 +720,16 @@ void run_summaries(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int6
     SB_LAUNCH(ctx, k5_summaries, (unsigned)ceil_div((int64_t)ngenes * P.K, SUM_WARPS), SUM_WARPS * 32, smem, sp);
 }
 
-void run_minrank(scranb200_ctx* ctx, const scranb200_plan& P, int64_t ngenes, int64_t ld, const double* d_eff, int64_t q0,
-                 int64_t q1, int32_t* d_minrank) {
+// d_eff holds the comparison columns [eff_q0, eff_q0 + eff_nq) of every effect: [3][eff_nq][ld].
+void run_minrank_cols(scranb200_ctx* ctx, const scranb200_plan& P, int64_t ngenes, int64_t ld, const double* d_eff, int64_t q0,
+                      int64_t q1, int64_t eff_q0, int64_t eff_nq, int32_t* d_minrank) {
+    if (q0 < eff_q0 || q1 > eff_q0 + eff_nq) throw Error("internal: comparison columns outside the effect buffer");
     std::vector<int32_t> src, td, tf, auc;
     for (int e = 0; e < 3; ++e) {
         for (int64_t q = q0; q < q1; ++q) {
             const int need = P.q_need[q];
             if (!need) continue;
-            src.push_back((int32_t)(e * P.Q + q));
+            src.push_back((int32_t)(e * eff_nq + (q - eff_q0)));
             td.push_back((need & 1) ? P.group_table[P.avg_left[q]] * 3 + e : -1);
             tf.push_back((need & 2) ? P.group_table[P.avg_right[q]] * 3 + e : -1);
             auc.push_back(e == 1);
@@ -735,14 +738,24 @@ void run_minrank(scranb200_ctx* ctx, const scranb200_plan& P, int64_t ngenes, in
     launch_rank(ctx, d_eff, ld, ngenes, src, td, tf, auc, d_minrank);
 }
 
+void run_minrank(scranb200_ctx* ctx, const scranb200_plan& P, int64_t ngenes, int64_t ld, const double* d_eff, int64_t q0,
+                 int64_t q1, int32_t* d_minrank) {
+    run_minrank_cols(ctx, P, ngenes, ld, d_eff, q0, q1, 0, P.Q, d_minrank);
+}
+
 void run_fill_i32(scranb200_ctx* ctx, int32_t* d, int64_t n, int32_t v) {
     if (n > 0) SB_LAUNCH(ctx, k5_fill_i32, (unsigned)ceil_div(n, 256), 256, 0, d, n, v);
 }
 
+void run_finish_rows(scranb200_ctx* ctx, const scranb200_plan& P, int64_t ngenes_total, int64_t row0, int64_t nrows,
+                     int64_t ld, const int32_t* d_minrank, double* d_out) {
+    const int64_t n = nrows * P.K * 3;
+    if (n > 0) SB_LAUNCH(ctx, k5_finish, (unsigned)ceil_div(n, 256), 256, 0, d_minrank, ngenes_total, row0, nrows, ld, P.K, d_out);
+}
+
 void run_finish(scranb200_ctx* ctx, const scranb200_plan& P, int64_t ngenes, int64_t ld, const int32_t* d_minrank,
                 double* d_out) {
-    const int64_t n = ngenes * P.K * 3;
-    if (n > 0) SB_LAUNCH(ctx, k5_finish, (unsigned)ceil_div(n, 256), 256, 0, d_minrank, ngenes, ld, P.K, d_out);
+    run_finish_rows(ctx, P, ngenes, 0, ngenes, ld, d_minrank, d_out);
 }
 
 void run_min_rank_matrix(scranb200_ctx* ctx, const double* d_x, int64_t nrow, int64_t ncol, int32_t* d_out) {

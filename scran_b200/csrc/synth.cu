@@ -128,6 +128,42 @@ __global__ void __launch_bounds__(1024) synth_scan(const int64_t* counts, int64_
 
 using namespace sb;
 
+// Expected number of stored entries per gene of the synthetic matrix (the same rates as
+// scranb200_synth_csc uses), for cutting gene shards of equal weight before anything is generated.
+extern "C" int scranb200_synth_row_weights(int64_t ngenes_total, int64_t ncells, double density, uint64_t seed, double* weight) {
+    try {
+        if (density <= 0.0 || density >= 1.0) density = 0.63;
+        std::vector<double> base(ngenes_total);
+        std::vector<uint8_t> kind(ngenes_total);
+        for (int64_t g = 0; g < ngenes_total; ++g) {
+            base[g] = std::exp2(-6.0 + 9.0 * unit(hash3(seed, 0x7a7e, (uint64_t)g)));
+            kind[g] = (uint8_t)gene_kind(seed, g);
+        }
+        auto frac = [&](double alpha) {
+            double s = 0;
+            for (int64_t g = 0; g < ngenes_total; ++g) {
+                if (kind[g] == G_ZERO) continue;
+                s += kind[g] == G_ALWAYS ? 1.0 : 1.0 - std::exp(-alpha * base[g]);
+            }
+            return s / (double)std::max<int64_t>(1, ngenes_total);
+        };
+        double lo = 1e-6, hi = 1e6;
+        for (int it = 0; it < 200; ++it) {
+            const double mid = std::sqrt(lo * hi);
+            if (frac(mid) < density) lo = mid; else hi = mid;
+        }
+        const double alpha = std::sqrt(lo * hi);
+        for (int64_t g = 0; g < ngenes_total; ++g) {
+            const double d = kind[g] == G_ZERO ? 0.0 : kind[g] == G_ALWAYS ? 1.0 : 1.0 - std::exp(-alpha * base[g]);
+            weight[g] = d * (double)ncells;
+        }
+    } catch (const std::exception& e) {
+        sb::set_last_error(e.what());
+        return 1;
+    }
+    return 0;
+}
+
 extern "C" int scranb200_synth_csc(scranb200_ctx* ctx, int64_t ngenes_total, int64_t g0, int64_t g1, int64_t ncells,
                                     const int32_t* groups, int ngroups, double density, uint64_t seed,
                                     scranb200_mat** out) {

@@ -197,8 +197,9 @@ struct SortParams {
     int cap, segcap, maxG;
     uint16_t* stream;
     uint32_t* unit_m;
-    uint64_t *g_ka, *g_kb;   // global scratch, indexed like the stream (units beyond cap only)
-    uint32_t *g_pa, *g_pb;
+    uint64_t *g_ka, *g_kb;   // global scratch of the units beyond cap: one region of `scratch_len` entries per CTA,
+    uint32_t *g_pa, *g_pb;   // reused unit after unit (it stays in L2 instead of streaming through HBM)
+    int64_t scratch_len;
     const int32_t* jobs;
     const int32_t* njobs;
     const int32_t* order;
@@ -766,10 +767,10 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         const int64_t vbase = S.vbase[0], soff = S.soff[0];
         const uint32_t n = S.n[0];
         const int G = (int)nseg - 1;
-        uint64_t* ga = P.g_ka + soff;
-        uint32_t* gp = P.g_pa + soff;
-        uint64_t* gb = P.g_kb + soff;
-        uint32_t* gq = P.g_pb + soff;
+        uint64_t* ga = P.g_ka + (size_t)blockIdx.x * P.scratch_len;
+        uint32_t* gp = P.g_pa + (size_t)blockIdx.x * P.scratch_len;
+        uint64_t* gb = P.g_kb + (size_t)blockIdx.x * P.scratch_len;
+        uint32_t* gq = P.g_pb + (size_t)blockIdx.x * P.scratch_len;
         const double fmin = reinterpret_cast<double*>(S.scan)[0], fmax = reinterpret_cast<double*>(S.scan)[1];
         const ValueMap vm256 = {fmin, fmax, fmax > fmin ? 254.0 / (fmax - fmin) : 0.0};
         if (tid == 0) S.misc[3] = 0;  // dropped (stored zero) entries, counted in pass 1
@@ -1706,13 +1707,16 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     sp.unit_m = ctx->unit_m.as<uint32_t>();
     sp.g_ka = sp.g_kb = nullptr;
     sp.g_pa = sp.g_pb = nullptr;
-    if (max_m > cap_large) {  // some unit may not fit shared memory: scratch laid out like the stream
-        ctx->sort_keys.reserve((size_t)stream_len * 16 + 64);
-        ctx->sort_labs.reserve((size_t)stream_len * 8 + 64);
+    const int sort_grid = (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count);
+    sp.scratch_len = (max_m + 63) & ~int64_t(63);
+    if (max_m > cap_large) {  // some unit may not fit shared memory: a scratch region per CTA, sized for the largest unit
+        const size_t all = (size_t)sort_grid * (size_t)sp.scratch_len;
+        ctx->sort_keys.reserve(all * 16 + 64);
+        ctx->sort_labs.reserve(all * 8 + 64);
         sp.g_ka = ctx->sort_keys.as<uint64_t>();
-        sp.g_kb = sp.g_ka + stream_len;
+        sp.g_kb = sp.g_ka + all;
         sp.g_pa = ctx->sort_labs.as<uint32_t>();
-        sp.g_pb = sp.g_pa + stream_len;
+        sp.g_pb = sp.g_pa + all;
     }
     sp.jobs = jobs;
     sp.njobs = njobs;
@@ -1721,8 +1725,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     allow_smem(k3_sort, (size_t)cap_large * 12 + sort_fixed_bytes(cap_large, segcap));
     sp.cap = cap_large;
     SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
-    SB_LAUNCH(ctx, k3_sort, (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count), SORT_THREADS,
-              (size_t)cap_large * 12 + sort_fixed_bytes(cap_large, segcap), sp);
+    SB_LAUNCH(ctx, k3_sort, sort_grid, SORT_THREADS, (size_t)cap_large * 12 + sort_fixed_bytes(cap_large, segcap), sp);
     phase_mark(ctx, PH_SORT);
 
     // ---- walk ----

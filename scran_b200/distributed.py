@@ -10,8 +10,11 @@ gene shards to comparison shards (all-to-all over NVLink), every rank ranks its 
 columns over all genes, the per-table minima are combined with an all-reduce(MIN), and the
 result columns are gathered on rank 0.
 
-The three collective helpers below work on CPU tensors with the gloo backend too, which is how
-tests/test_distributed_cpu.py checks the plumbing without a GPU.
+On the GPU the exchange runs inside the library (csrc/dist.cu, NCCL on the context's stream;
+ShardedScorer below only passes the row ranges). The three collective helpers in this file restate
+that exchange plan on torch tensors; they work with the gloo backend on CPU tensors, which is how
+tests/test_distributed_cpu.py checks the plan (who sends which block where, how the min-ranks
+combine, how the rows are gathered) without a GPU.
 """
 import numpy as np
 
@@ -79,45 +82,60 @@ def gather_tables(out_local, ngenes, dist, world):
     return full
 
 
-class ShardedScorer:
-    """scoreMarkers over a gene shard per rank, all numerics in libscranb200 on this rank's GPU."""
+def balanced_row_starts(weights, world):
+    """Contiguous row ranges of equal total weight (scranb200_balance_rows): int64[world + 1]."""
+    from ._lib import check, lib, ptr
+    w = np.ascontiguousarray(weights, np.float64)
+    starts = np.zeros(world + 1, np.int64)
+    check(lib().scranb200_balance_rows(ptr(w), len(w), int(world), ptr(starts)))
+    return starts
 
-    def __init__(self, ctx, plan, ngenes_total, rank=0, world=1, dist=None):
+
+def init_comm(ctx, rank=0, world=1, dist=None):
+    """Gives the context its NCCL communicator. The 128-byte unique id is made on rank 0 and travels
+    over the process group the caller already has (any backend)."""
+    from ._lib import check, lib, ptr
+    if getattr(ctx, "_comm", None) == (world, rank):
+        return  # this context already has the communicator of this world
+    ident = np.zeros(128, np.uint8)
+    if world > 1:
         import torch
-        self.torch = torch
-        self.ctx, self.plan = ctx, plan
-        self.ngenes, self.rank, self.world, self.dist = int(ngenes_total), rank, world, dist
-        self.granges, self.per = shard_ranges(self.ngenes, world)
-        self.g0, self.g1 = self.granges[rank]
-        dev = torch.device("cuda", ctx.device)
-        K, Q = max(1, plan.K), max(1, plan.Q)
-        self.eff_local = torch.zeros((3, Q, self.per), dtype=torch.float64, device=dev)
-        self.out_local = torch.zeros((K, 19, self.per), dtype=torch.float64, device=dev)
-        self.minrank = torch.empty((K, 3, self.ngenes), dtype=torch.int32, device=dev)
-        torch.cuda.synchronize(dev)
-
-    def step(self, mat):
-        """One full pass; returns the [K, 19, ngenes] result tensor (complete on every rank)."""
-        from ._lib import check, lib, ptr
-        torch, plan, ctx = self.torch, self.plan, self.ctx
-        L = lib()
-        check(L.scranb200_score_effects_dev(ctx.handle, mat.handle, plan.handle, self.per, 0, ptr(self.eff_local),
-                                            ptr(self.out_local)))
-        self.last_timing = ctx.last_timing()
-        if self.world > 1:
-            full, (q0, q1) = exchange_effects(self.eff_local, self.g1 - self.g0, self.ngenes, plan.Q, self.dist,
-                                              self.world, self.rank)
-            torch.cuda.current_stream().synchronize()
-            eff, ld = full, self.ngenes
+        if rank == 0:
+            check(lib().scranb200_comm_unique_id(ptr(ident)))
+        t = torch.from_numpy(ident)
+        if dist.get_backend() == "nccl":
+            t = t.cuda()
+            dist.broadcast(t, 0)
+            ident = t.cpu().numpy()
         else:
-            eff, ld, q0, q1 = self.eff_local, self.per, 0, plan.Q
-        check(L.scranb200_fill_i32(ctx.handle, ptr(self.minrank), self.minrank.numel(), INT32_MAX))
-        check(L.scranb200_score_minrank_dev(ctx.handle, plan.handle, self.ngenes, ld, ptr(eff), q0, q1,
-                                            ptr(self.minrank)))
-        self.last_timing["minrank"] = ctx.last_timing()["minrank"]
-        combine_minrank(self.minrank, self.dist, self.world)
-        out = gather_tables(self.out_local, self.ngenes, self.dist, self.world)
-        torch.cuda.current_stream().synchronize()
-        check(L.scranb200_score_finish_dev(ctx.handle, plan.handle, self.ngenes, self.ngenes, ptr(self.minrank),
-                                           ptr(out)))
-        return out
+            dist.broadcast(t, 0)
+    check(lib().scranb200_ctx_comm_init(ctx.handle, int(world), int(rank), ptr(ident)))
+    ctx._comm = (world, rank)
+
+
+class ShardedScorer:
+    """scoreMarkers over one gene shard per rank: scranb200_score_markers_sharded, i.e. all numerics AND
+    the exchange (NCCL) inside libscranb200 on this rank's GPU and stream. row_starts: int64[world + 1]
+    (default: equally many genes per rank)."""
+
+    def __init__(self, ctx, plan, ngenes_total, rank=0, world=1, dist=None, row_starts=None, root=0):
+        self.ctx, self.plan = ctx, plan
+        self.ngenes, self.rank, self.world, self.root = int(ngenes_total), rank, world, root
+        if row_starts is None:
+            granges, _ = shard_ranges(self.ngenes, world)
+            row_starts = [g[0] for g in granges] + [self.ngenes]
+        self.row_starts = np.ascontiguousarray(row_starts, np.int64)
+        self.g0, self.g1 = int(self.row_starts[rank]), int(self.row_starts[rank + 1])
+        init_comm(ctx, rank, world, dist)
+
+    def step(self, mat, out=None):
+        """One full pass. out (optional): host array [K, 19, ngenes] filled on the ranks that receive the
+        result (root, or all if root < 0). Returns the device address of the result table (0 elsewhere)."""
+        import ctypes as C
+
+        from ._lib import check, lib, ptr
+        d_out = C.c_void_p()
+        check(lib().scranb200_score_markers_sharded(self.ctx.handle, mat.handle, self.plan.handle, self.ngenes,
+                                                    ptr(self.row_starts), int(self.root), ptr(out), C.byref(d_out)))
+        self.last_timing = self.ctx.last_timing()
+        return d_out.value or 0
