@@ -176,6 +176,41 @@ def test_overlap_many_groups_large_units(sb, port_lib):
     assert np.array_equal(t, pt)
 
 
+def test_overlap_medium_units(sb, port_lib):
+    """Units of 18,000 - 65,535 entries: beyond the shared-memory sort, within 16-bit positions, i.e. the
+    path that scatters into bucket order in global scratch and ranks window by window. Continuous values,
+    a skewed distribution (large buckets that are not uniform), integer values (large uniform buckets),
+    negative values, stored zeros; lfc != 0 doubles every entry (two roles)."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(83)
+    ncells = 64000
+    x = np.zeros((9, ncells))
+    x[0] = np.where(rng.random(ncells) < 0.45, np.log2(1 + rng.poisson(1.2, ncells) + rng.random(ncells)), 0)
+    x[1] = np.where(rng.random(ncells) < 0.99, rng.random(ncells) + 0.25, 0)           # ~63,400 entries
+    x[2] = np.where(rng.random(ncells) < 0.6, rng.poisson(2, ncells), 0)                # long tie runs
+    x[3] = np.where(rng.random(ncells) < 0.8, np.exp(8 * rng.random(ncells)), 0)        # heavy skew: a few huge buckets
+    x[3, :40] = 1e6
+    x[4] = np.where(rng.random(ncells) < 0.5, rng.normal(size=ncells), 0)               # both sides of zero
+    x[5] = np.where(rng.random(ncells) < 0.7, np.round(rng.normal(size=ncells), 2), 0)  # thousands of short runs
+    x[6] = np.where(rng.random(ncells) < 0.35, 1.0 + 1e-9 * rng.integers(0, 50, ncells), 0)  # 50 values a hair apart
+    x[7] = np.where(rng.random(ncells) < 0.4, rng.random(ncells), 0)
+    x[8] = np.where(rng.random(ncells) < 0.3, rng.random(ncells) * 100, 0)
+    m = as_csc(x)
+    data = m.data.copy()
+    rows = np.repeat(np.arange(m.shape[1]), np.diff(m.indptr))  # (column of each entry; unused, keeps the intent clear)
+    data[(m.indices == 7) & (rng.random(len(data)) < 0.1)] = 0.0  # stored zeros in gene 7
+    m = sp.csc_matrix((data, m.indices, m.indptr), shape=m.shape)
+    for ngroups in (7, 40):
+        g = rng.integers(0, ngroups, ncells)
+        groups = [np.flatnonzero(g == k).astype(np.int32) for k in range(ngroups)]
+        left, right = all_pairs(ngroups)
+        for lfc in (0.0, 0.5):
+            u, t = sb.overlap_exprs_paired(m, left, right, groups, lfc, want_ties=True)
+            pu, pt = port_lib.overlap_paired(m, left, right, groups, lfc, want_ties=True)
+            assert np.array_equal(u, pu), (ngroups, lfc, np.argwhere(u != pu)[:5])
+            assert np.array_equal(t, pt), (ngroups, lfc)
+
+
 def test_overlap_long_tie_runs(sb, port_lib):
     """Integer-valued data: runs of equal values much longer than a warp's block of 32 entries, in
     units small enough for the warp-group walk, with 3 and with 40 groups (one and two labels a lane)."""
