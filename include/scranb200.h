@@ -111,6 +111,18 @@ int scranb200_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, cons
                               const int32_t* block, int nblocks, double lfc, int direction, double* effect_out,
                               double* logp_out, double* logfdr_out);
 
+/* ---- pairwiseTTests (block= branch), statistics AND p-value layer: R/pairwiseTTests.R:226-332, 439-461
+ *  The R function takes the per-(block, group) means and variances
+ * from compute_blocked_stats_none (ids group + block * ngroups, :242) and then, in R closures per
+ * (block, host, target): Welch's t-test (.get_t_test_stats, :311-332), stats::pt(log.p = TRUE) for both
+ * tails (.run_t_test, :439-461; against -|lfc| / +|lfc| when lfc != 0), the log-fold change or with
+ * std_lfc Cohen's d (:283-289), Stouffer over the block levels with weights 1 / (1/nh + 1/nt)
+ * (R/utils_markers.R:52-130), and .logBH over the genes (:184-190). All of it runs on the device here.
+ * Arguments and outputs as for scranb200_pairwise_wilcox; effect = logFC (host - target). */
+int scranb200_pairwise_t_tests(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int ngroups,
+                               const int32_t* block, int nblocks, double lfc, int direction, int std_lfc,
+                               double* effect_out, double* logp_out, double* logfdr_out);
+
 /* ---- overlap_exprs_paired: src/overlap_exprs.cpp:196-220 ------------------------------------
  * groups: the reference's list of 0-based cell-index vectors, flattened: group g owns
  * group_cells[group_ptr[g] .. group_ptr[g+1]). A cell may belong to at most one group (the

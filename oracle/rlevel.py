@@ -478,9 +478,43 @@ def pairwise_wilcox(x, groups, block=None, lfc=0.0, direction="any", lib=None):
     return _blocked_template(levels, len(blocks), direction, statfun)
 
 
+def log_pt(t, df, lower=True):
+    """stats::pt(t, df, lower.tail=lower, log.p=TRUE). scipy's t.logcdf / logsf are log(cdf): exact enough
+    until the tail underflows (log p < ~ -700); beyond that the tail is the regularised incomplete beta
+    function in 50-digit arithmetic (mpmath), elementwise - only a handful of entries ever get there."""
+    from scipy.stats import t as tdist
+    t = np.asarray(t, np.float64)
+    df = np.broadcast_to(np.asarray(df, np.float64), t.shape)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        out = np.array(tdist.logcdf(t, df) if lower else tdist.logsf(t, df), np.float64)
+    deep = np.isfinite(t) & np.isfinite(df) & ((out < -650) | np.isneginf(out))
+    if deep.any():
+        import mpmath as mp
+        with mp.workdps(50):
+            for k in np.flatnonzero(deep.ravel()):
+                tt, dd = mp.mpf(float(t.ravel()[k])), mp.mpf(float(df.ravel()[k]))
+                a, b, x = dd / 2, mp.mpf(1) / 2, dd / (dd + tt * tt)
+                try:
+                    tail = mp.betainc(a, b, 0, x, regularized=True) / 2
+                except ValueError:  # the hypergeometric series gives up on a few (t, df): Lentz's continued fraction
+                    c, d = mp.mpf(1), 1 / (1 - (a + b) * x / (a + 1))
+                    h = d
+                    for m in range(1, 100000):
+                        aa = m * (b - m) * x / ((a - 1 + 2 * m) * (a + 2 * m))
+                        d, c = 1 / (1 + aa * d), 1 + aa / c
+                        h *= d * c
+                        aa = -(a + m) * (a + b + m) * x / ((a + 2 * m) * (a + 1 + 2 * m))
+                        d, c = 1 / (1 + aa * d), 1 + aa / c
+                        h *= d * c
+                        if abs(d * c - 1) < mp.mpf(10) ** -45:
+                            break
+                    tail = mp.exp(a * mp.log(x) + b * mp.log(1 - x) - (mp.loggamma(a) + mp.loggamma(b) - mp.loggamma(a + b))) * h / a / 2
+                out.ravel()[k] = float(mp.log(tail))  # the requested tail is the far one, else log p would be ~ 0
+    return out
+
+
 def pairwise_ttests(x, groups, block=None, lfc=0.0, direction="any", std_lfc=False, lib=None):
     """R/pairwiseTTests.R:226-332, 439-461 on group codes 0..G-1 (negative = NA)."""
-    from scipy.stats import t as tdist
     lib = lib or native.load("best")
     groups = np.asarray(groups)
     G = int(groups.max()) + 1
@@ -513,11 +547,11 @@ def pairwise_ttests(x, groups, block=None, lfc=0.0, direction="any", std_lfc=Fal
         with np.errstate(invalid="ignore", divide="ignore"):
             if thr == 0:
                 tt = cur / np.sqrt(err)
-                left = tdist.logcdf(tt, df)
-                right = tdist.logsf(tt, df)
+                left = log_pt(tt, df, True)
+                right = log_pt(tt, df, False)
             else:
-                left = tdist.logcdf((cur + thr) / np.sqrt(err), df)
-                right = tdist.logsf((cur - thr) / np.sqrt(err), df)
+                left = log_pt((cur + thr) / np.sqrt(err), df, True)
+                right = log_pt((cur - thr) / np.sqrt(err), df, False)
             eff = cur.copy()
             if std_lfc:
                 pooled = ((hn - 1) * varis[:, b * G + host] + (tn - 1) * varis[:, b * G + target]) / (tn + hn - 2)

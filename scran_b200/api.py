@@ -10,9 +10,9 @@ that the parity tests read like the reference's own tests:
     overlap_exprs / overlap_exprs_paired             R/RcppExports.R:48-54
     compute_min_rank       computeMinRank()          R/computeMinRank.R:45-50
 
-All numerics run in libscranb200.so on the GPU through the C ABI; this module only converts
-arguments (what the R closures do before .Call) and reshapes results. The p-value layers of
-pairwiseWilcox / pairwiseTTests stay on the host exactly as they stay in R.
+All numerics run in libscranb200.so on the GPU through the C ABI, the p-value layers of
+pairwiseWilcox / pairwiseTTests included; this module only converts
+arguments (what the R closures do before .Call) and reshapes results.
 """
 import ctypes as C
 from collections import OrderedDict
@@ -397,7 +397,7 @@ def score_markers(x, groups, block=None, pairings=None, lfc=0.0, full_stats=Fals
 
 
 # ---------------------------------------------------------------------------------------------
-# pairwiseWilcox / pairwiseTTests: native statistics on the GPU, p-value layer on the host
+# pairwiseWilcox / pairwiseTTests: statistics and p-value layers on the GPU
 # ---------------------------------------------------------------------------------------------
 
 def _setup_groups(groups, ncells):
@@ -412,87 +412,44 @@ def _setup_groups(groups, ncells):
     return levels, np.array([code[g] if g is not None else -1 for g in groups], np.int64)
 
 
-def _stouffer_log(logps, weights):
-    from scipy.special import log_ndtr, ndtri_exp
-    z = np.stack([ndtri_exp(lp) for lp in logps], axis=0)
-    w = np.asarray(weights, np.float64)[:, None]
-    return log_ndtr((z * w).sum(axis=0) / np.sqrt((w ** 2).sum()))
+def _block_codes(block, ncells, keep):
+    """Block levels in sorted order -> int32 codes; cells with keep == False do not define a level
+    (R/pairwiseTTests.R:238: block[is.na(groups)] <- NA)."""
+    if block is None:
+        return None, 1
+    block = np.asarray(list(block))
+    if len(block) != ncells:
+        raise ValueError("length of 'block' does not equal 'ncol(x)'")
+    blevels = sorted(set(block[keep].tolist()))
+    codes = np.searchsorted(np.array(blevels), block) if blevels else np.zeros(ncells, np.int64)
+    codes = np.where(keep, np.minimum(codes, max(0, len(blevels) - 1)), 0)
+    return np.ascontiguousarray(codes, np.int32), max(1, len(blevels))
 
 
-def log_bh(logp):
-    """.logBH (R/utils_markers.R:184-190)."""
-    logp = np.asarray(logp, np.float64)
-    o = np.argsort(logp, kind="stable")
-    n = len(o)
-    rep = logp[o] + np.log(n / np.arange(1, n + 1))
-    rep = np.minimum.accumulate(rep[::-1])[::-1]
-    out = np.empty(n)
-    out[o] = rep
+def _pair_list(levels, eff, lp, lf):
+    import warnings
+    out, k = [], 0
+    for a in levels:
+        for b in levels:
+            if a == b:
+                continue
+            if np.all(np.isnan(lp[k])) and levels.index(b) < levels.index(a):
+                warnings.warn("no within-block comparison between %s and %s" % (a, b))
+            out.append(dict(first=a, second=b, effect=eff[k].copy(), log_p=lp[k].copy(), log_fdr=lf[k].copy()))
+            k += 1
     return out
 
 
-def _choose(left, right, direction):
-    if direction == "up":
-        return right
-    if direction == "down":
-        return left
-    return np.minimum(0, np.minimum(left, right) + np.log(2))
-
-
-def _blocked_template(levels, nblocks, direction, statfun):
-    """.pairwise_blocked_template (R/utils_markers.R:52-130)."""
-    import warnings
-    res = {}
-    for i, host in enumerate(levels):
-        for target in levels[:i]:
-            outs = [statfun(b, i, levels.index(target)) for b in range(nblocks)]
-            valid = [k for k, o in enumerate(outs) if o["valid"]]
-            if valid:
-                w = np.array([outs[k]["weight"] for k in valid], np.float64)
-                cl = _stouffer_log([outs[k]["left"] for k in valid], w)
-                cr = _stouffer_log([outs[k]["right"] for k in valid], w)
-                hp, tp = _choose(cl, cr, direction), _choose(cr, cl, direction)
-                fwd = np.stack([outs[k]["forward"] for k in valid], 1)
-                rvs = np.stack([outs[k]["reverse"] for k in valid], 1)
-                fe = (fwd * w[None, :]).sum(1) / w.sum()
-                re_ = (rvs * w[None, :]).sum(1) / w.sum()
-            else:
-                n = len(outs[0]["left"])
-                hp = tp = fe = re_ = np.full(n, np.nan)
-                warnings.warn("no within-block comparison between %s and %s" % (host, target))
-            res[(host, target)] = (fe, hp)
-            res[(target, host)] = (re_, tp)
-    ordered = []
-    for a in levels:
-        for b in levels:
-            if (a, b) in res:
-                eff, lp = res[(a, b)]
-                ordered.append(dict(first=a, second=b, effect=eff, log_p=lp,
-                                    log_fdr=log_bh(lp) if not np.all(np.isnan(lp)) else lp))
-    return ordered
-
-
-def pairwise_wilcox(x, groups, block=None, lfc=0.0, direction="any", host_layer=False):
+def pairwise_wilcox(x, groups, block=None, lfc=0.0, direction="any"):
     """pairwiseWilcox(x, groups, block=, lfc=, direction=, log.p=TRUE): list of dicts
     (first, second, effect=AUC, log_p, log_fdr) in the reference's pair order. The statistics and the
-    p-value layer (normal approximation, Stouffer over the block levels, log BH) run on the device;
-    host_layer=True keeps the p-value layer in numpy / scipy on top of the device U and tie terms."""
-    if host_layer:
-        return _pairwise_wilcox_host_layer(x, groups, block, lfc, direction)
+    p-value layer (normal approximation, Stouffer over the block levels, log BH) run on the device."""
     if direction not in ("any", "up", "down"):
         raise ValueError("'direction' should be one of 'any', 'up', 'down'")
     m = _as_matrix(x)
     levels, codes = _setup_groups(groups, m.shape[1])
     G = len(levels)
-    if block is None:
-        bcodes, nb = None, 1
-    else:
-        block = np.asarray(list(block))
-        if len(block) != m.shape[1]:
-            raise ValueError("length of 'block' does not equal 'ncol(x)'")
-        blevels = sorted(set(block.tolist()))
-        bcodes = np.ascontiguousarray(np.searchsorted(np.array(blevels), block), np.int32)
-        nb = len(blevels)
+    bcodes, nb = _block_codes(block, m.shape[1], np.ones(m.shape[1], bool))
     gcodes = np.ascontiguousarray(codes, np.int32)
     nout = G * (G - 1)
     eff = np.zeros((max(1, nout), m.shape[0]), np.float64)
@@ -500,155 +457,26 @@ def pairwise_wilcox(x, groups, block=None, lfc=0.0, direction="any", host_layer=
     lf = np.zeros_like(eff)
     check(lib().scranb200_pairwise_wilcox(m.ctx.handle, m.handle, ptr(gcodes), G, ptr(bcodes), nb, float(lfc),
                                           ("any", "up", "down").index(direction), ptr(eff), ptr(lp), ptr(lf)))
-    out, k = [], 0
-    for a in levels:
-        for b in levels:
-            if a == b:
-                continue
-            if np.all(np.isnan(lp[k])):
-                import warnings
-                if levels.index(b) < levels.index(a):
-                    warnings.warn("no within-block comparison between %s and %s" % (a, b))
-            out.append(dict(first=a, second=b, effect=eff[k].copy(), log_p=lp[k].copy(), log_fdr=lf[k].copy()))
-            k += 1
-    return out
-
-
-def _pairwise_wilcox_host_layer(x, groups, block=None, lfc=0.0, direction="any"):
-    from scipy.special import log_ndtr
-    m = _as_matrix(x)
-    levels, codes = _setup_groups(groups, m.shape[1])
-    G = len(levels)
-    if block is None:
-        blocks = [np.arange(m.shape[1])]
-    else:
-        block = np.asarray(list(block))
-        if len(block) != m.shape[1]:
-            raise ValueError("length of 'block' does not equal 'ncol(x)'")
-        blocks = [np.flatnonzero(block == b) for b in sorted(set(block.tolist()))]
-    # R/pairwiseWilcox.R:221-243 makes one native call per block level; here all block levels go through
-    # ONE paired call (two with lfc != 0: the mirrored entries use -lfc, src/overlap_exprs.cpp:179-187),
-    # every (block, group) combination being a group of its own, and the results are laid out as the
-    # per-block overlap_exprs() matrices: entry (i, j) present for j < i (all i != j with lfc != 0).
-    all_n, combos, left, right, where = [], [], [], [], []
-    for b, chosen in enumerate(blocks):
-        cg = codes[chosen]
-        by_group = [chosen[cg == g].astype(np.int32) for g in range(G)]
-        all_n.append(np.array([len(v) for v in by_group], np.float64))
-        base = len(combos)
-        combos.extend(by_group)
-        for i in range(G):
-            if len(by_group[i]) == 0:
-                continue  # src/overlap_exprs.cpp:175,177: empty groups are skipped, their entries stay 0
-            for j in range(i):
-                if len(by_group[j]) == 0:
-                    continue
-                left.append(base + i + 1)
-                right.append(base + j + 1)
-                where.append((b, i, j))
-    ngenes = m.shape[0]
-    all_u = [np.full((G, G, ngenes), np.nan) for _ in blocks]
-    all_t = [np.full((G, G, ngenes), np.nan) for _ in blocks]
-    for b in range(len(blocks)):
-        for i in range(G):
-            for j in range(G):
-                if j < i or (lfc != 0 and i != j):
-                    all_u[b][i, j] = 0.0
-                    all_t[b][i, j] = 0.0
-    if left:
-        for sign in ((1.0,) if lfc == 0 else (1.0, -1.0)):
-            U, T = overlap_exprs_paired(m, np.array(left, np.int32), np.array(right, np.int32), combos, sign * lfc,
-                                        want_ties=True)
-            for k, (b, i, j) in enumerate(where):
-                a, c = (i, j) if sign > 0 else (j, i)
-                all_u[b][a, c] = U[:, k]
-                all_t[b][a, c] = T[:, k]
-
-    def sigma(nh, nt, ties):  # .get_sigma, R/pairwiseWilcox.R:347-350
-        s2 = (nh * nt / 12) * ((nh + nt + 1) - ties / ((nh + nt) * (nh + nt - 1)))
-        with np.errstate(invalid="ignore"):
-            return np.maximum(np.sqrt(s2), 1e-8)
-
-    def statfun(b, host, target):  # R/pairwiseWilcox.R:263-345
-        hn, tn = all_n[b][host], all_n[b][target]
-        prod = hn * tn
-        with np.errstate(invalid="ignore", divide="ignore"):
-            if lfc == 0:
-                eff = all_u[b][host, target]
-                auc = eff / prod
-                out = dict(forward=auc, reverse=1 - auc)
-                z = eff - prod / 2
-                sig = sigma(hn, tn, all_t[b][host, target])
-                out["left"] = log_ndtr((z + 0.5) / sig)
-                out["right"] = log_ndtr(-(z - 0.5) / sig)
-            else:
-                minus, added = all_u[b][host, target], all_u[b][target, host]
-                if direction == "any":
-                    auc = (minus / 2 + added / 2) / prod
-                    out = dict(forward=auc, reverse=1 - auc)
-                elif direction == "up":
-                    out = dict(forward=minus / prod, reverse=1 - added / prod)
-                else:
-                    out = dict(forward=added / prod, reverse=1 - minus / prod)
-                msig = sigma(hn, tn, all_t[b][host, target])
-                asig = sigma(hn, tn, all_t[b][target, host])
-                out["left"] = log_ndtr(((added - prod / 2) + 0.5) / asig)
-                out["right"] = log_ndtr(-((minus - prod / 2) - 0.5) / msig)
-        out["weight"] = prod
-        out["valid"] = prod > 1.5
-        return out
-
-    return _blocked_template(levels, len(blocks), direction, statfun)
+    return _pair_list(levels, eff, lp, lf)
 
 
 def pairwise_t_tests(x, groups, block=None, lfc=0.0, direction="any", std_lfc=False):
-    """pairwiseTTests(x, groups, block=, lfc=, direction=, std.lfc=) for the block= branch."""
-    from scipy.stats import t as tdist
+    """pairwiseTTests(x, groups, block=, lfc=, direction=, std.lfc=, log.p=TRUE) for the block= branch:
+    list of dicts (first, second, effect=logFC, log_p, log_fdr) in the reference's pair order. Blocked
+    means / variances, Welch's t-test, the log tails of the t distribution, Stouffer over the block
+    levels and log BH all run on the device (scranb200_pairwise_t_tests)."""
+    if direction not in ("any", "up", "down"):
+        raise ValueError("'direction' should be one of 'any', 'up', 'down'")
     m = _as_matrix(x)
     levels, codes = _setup_groups(groups, m.shape[1])
     G = len(levels)
-    if block is None:
-        bcode = np.zeros(len(codes), np.int64)
-        nb = 1
-    else:
-        block = list(block)
-        if len(block) != m.shape[1]:
-            raise ValueError("length of 'block' does not equal 'ncol(x)'")
-        blv = sorted(set(b for b, g in zip(block, codes) if g >= 0))
-        bcode = np.array([blv.index(b) if g >= 0 else 0 for b, g in zip(block, codes)])
-        nb = len(blv)
-    ids = np.where(codes >= 0, codes + bcode * G, NA_INT).astype(np.int32)  # R/pairwiseTTests.R:242
-    means, varis = compute_blocked_stats_none(m, ids, nb * G)
-    ncells = np.bincount(ids[ids >= 0], minlength=nb * G).astype(np.float64)
-    thr = abs(lfc)
-
-    def statfun(b, host, target):  # R/pairwiseTTests.R:270-302, 311-332, 439-461
-        hn, tn = ncells[b * G + host], ncells[b * G + target]
-        hv, tv = varis[:, b * G + host], varis[:, b * G + target]
-        hs2, ts2 = np.maximum(hv, 1e-8), np.maximum(tv, 1e-8)
-        hdf, tdf = max(0.0, hn - 1), max(0.0, tn - 1)
-        n = means.shape[0]
-        if hdf > 0 and tdf > 0:
-            herr, terr = hs2 / hn, ts2 / tn
-            err = herr + terr
-            df = err ** 2 / (herr ** 2 / hdf + terr ** 2 / tdf)
-        else:
-            err = df = np.full(n, np.nan)
-        cur = means[:, b * G + host] - means[:, b * G + target]
-        with np.errstate(invalid="ignore", divide="ignore"):
-            if thr == 0:
-                tt = cur / np.sqrt(err)
-                left, right = tdist.logcdf(tt, df), tdist.logsf(tt, df)
-            else:
-                left = tdist.logcdf((cur + thr) / np.sqrt(err), df)
-                right = tdist.logsf((cur - thr) / np.sqrt(err), df)
-            eff = cur.copy()
-            if std_lfc:
-                pooled = ((hn - 1) * hv + (tn - 1) * tv) / (tn + hn - 2)
-                zero = eff == 0
-                eff = eff / np.sqrt(pooled)
-                eff[zero] = 0
-            wgt = 1 / (1 / hn + 1 / tn) if hn > 0 and tn > 0 else 0.0
-        return dict(forward=eff, reverse=-eff, left=left, right=right, weight=wgt, valid=bool(np.all(~np.isnan(df))))
-
-    return _blocked_template(levels, nb, direction, statfun)
+    bcodes, nb = _block_codes(block, m.shape[1], codes >= 0)
+    gcodes = np.ascontiguousarray(codes, np.int32)
+    nout = G * (G - 1)
+    eff = np.zeros((max(1, nout), m.shape[0]), np.float64)
+    lp = np.zeros_like(eff)
+    lf = np.zeros_like(eff)
+    check(lib().scranb200_pairwise_t_tests(m.ctx.handle, m.handle, ptr(gcodes), G, ptr(bcodes), nb, float(lfc),
+                                           ("any", "up", "down").index(direction), int(bool(std_lfc)), ptr(eff), ptr(lp),
+                                           ptr(lf)))
+    return _pair_list(levels, eff, lp, lf)

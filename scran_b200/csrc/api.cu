@@ -592,6 +592,20 @@ int scranb200_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, cons
     API_END
 }
 
+int scranb200_pairwise_t_tests(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int ngroups,
+                               const int32_t* block, int nblocks, double lfc, int direction, int std_lfc,
+                               double* effect_out, double* logp_out, double* logfdr_out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    mat_guard(ctx, mat);
+    if (ngroups < 0 || nblocks < 1) throw Error("bad number of groups or blocks");
+    if (direction < 0 || direction > 2) throw Error("direction must be 0 (any), 1 (up) or 2 (down)");
+    phase_begin(ctx);
+    run_pairwise_ttests(ctx, mat, group, ngroups, block, nblocks, lfc, direction, std_lfc, effect_out, logp_out, logfdr_out);
+    phase_collect(ctx);
+    API_END
+}
+
 int scranb200_overlap_exprs_paired(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* left,
                                    const int32_t* right, int64_t npairs, int ngroups, const int64_t* group_ptr,
                                    const int32_t* group_cells, double lfc, double* u_out, double* ties_out) {

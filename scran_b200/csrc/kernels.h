@@ -33,4 +33,8 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
 void run_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int G, const int32_t* block,
                          int nblocks, double lfc, int direction, double* effect, double* logp, double* logfdr);
 
+// pvalues.cu: pairwiseTTests (block= branch) with its p-value layer on the device.
+void run_pairwise_ttests(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int G, const int32_t* block,
+                         int nblocks, double lfc, int direction, int std_lfc, double* effect, double* logp, double* logfdr);
+
 }  // namespace sb

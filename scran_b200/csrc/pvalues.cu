@@ -12,6 +12,7 @@
 // sorts every ordered pair's column with the radix sort of sort.cuh.
 #include "kernels.h"
 #include "sort.cuh"
+#include "tdist.cuh"
 
 namespace sb {
 
@@ -47,6 +48,29 @@ __device__ inline double ndtri_exp(double y) {
     }
     return z;
 }
+
+// Stouffer's method on log p-values (metapod::combineParallelPValues(method = "stouffer", log.p = TRUE),
+// called at R/utils_markers.R:96-97): z = sum w_b qnorm(p_b) / sqrt(sum w_b^2). A block with p = 1 (z = +Inf)
+// and one with p = 0 (z = -Inf) would add up to NaN; they are kept out of the sum and resolved by weight:
+// the heavier side wins, equal weights give p = 1/2. (metapod's source is not in the reference tree: this
+// edge is restated from its documented behaviour, parity unpinned.)
+struct StoufferAcc {
+    double z = 0.0, w_zero = 0.0, w_one = 0.0;
+    __device__ void add(double logp, double w) {
+        if (logp == 0.0) w_one += w;
+        else if (isinf(logp) && logp < 0.0) w_zero += w;
+        else z += ndtri_exp(logp) * w;
+    }
+    __device__ double log_p(double sw2) const {
+        if (w_zero > 0.0 || w_one > 0.0) {
+            if (isnan(z)) return z;
+            if (w_zero > w_one) return -__longlong_as_double(0x7ff0000000000000ll);
+            if (w_zero < w_one) return 0.0;
+            return -0.693147180559945309417232121458176568;
+        }
+        return log_ndtr(z / sqrt(sw2));
+    }
+};
 
 struct WilcoxLayerParams {
     int ngenes, G, nblocks, npairs;  // npairs: block-level pairs (columns of u / t)
@@ -88,7 +112,8 @@ __global__ void __launch_bounds__(256) k6_wilcox_layer(WilcoxLayerParams P) {
     }
     const int target = rem;
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
-    double sw = 0.0, sw2 = 0.0, zl = 0.0, zr = 0.0, fwd = 0.0, rev = 0.0;
+    double sw = 0.0, sw2 = 0.0, fwd = 0.0, rev = 0.0;
+    StoufferAcc zl, zr;
     bool any = false;
     for (int b = 0; b < P.nblocks; ++b) {
         const double nh = P.sizes[b * P.G + host], nt = P.sizes[b * P.G + target];
@@ -129,14 +154,14 @@ __global__ void __launch_bounds__(256) k6_wilcox_layer(WilcoxLayerParams P) {
         any = true;
         sw += prod;
         sw2 += prod * prod;
-        zl += ndtri_exp(left) * prod;
-        zr += ndtri_exp(right) * prod;
+        zl.add(left, prod);
+        zr.add(right, prod);
         fwd += f * prod;
         rev += r * prod;
     }
     double fe = nan, re = nan, hp = nan, tp = nan;
     if (any) {
-        const double cl = log_ndtr(zl / sqrt(sw2)), cr = log_ndtr(zr / sqrt(sw2));
+        const double cl = zl.log_p(sw2), cr = zr.log_p(sw2);
         hp = choose_p(cl, cr, P.direction);
         tp = choose_p(cr, cl, P.direction);
         fe = fwd / sw;
@@ -147,6 +172,85 @@ __global__ void __launch_bounds__(256) k6_wilcox_layer(WilcoxLayerParams P) {
     P.effect[o1] = fe;
     P.logp[o1] = hp;
     P.effect[o2] = re;
+    P.logp[o2] = tp;
+}
+
+// The same fold for pairwiseTTests (R/pairwiseTTests.R:270-302): per block Welch's t-test from the block's
+// means and variances (.get_t_test_stats, :311-332: variances floored at 1e-8, Welch's degrees of freedom),
+// log p-values of both tails from the t distribution (.run_t_test, :439-461; with lfc != 0 the two tails are
+// tested against -|lfc| and +|lfc|), effect = log-fold change or, with std.lfc, Cohen's d with the
+// df-pooled variance (:283-289); blocks weighted by 1 / (1/nh + 1/nt) (:296); a block is valid when both
+// groups have two or more cells (:299).
+struct TTestLayerParams {
+    int ngenes, G, nblocks;
+    int direction, std_lfc;
+    double thr;                 // |lfc|
+    const double *mean, *var;   // [nblocks * G][ngenes]
+    const double* sizes;        // [nblocks][G]
+    double *effect, *logp;      // [G * (G - 1)][ngenes]
+};
+
+__global__ void __launch_bounds__(256) k6_ttest_layer(TTestLayerParams P) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int upairs = P.G * (P.G - 1) / 2;
+    if (t >= (int64_t)P.ngenes * upairs) return;
+    const int g = (int)(t % P.ngenes);
+    int rem = (int)(t / P.ngenes), host = 1;
+    while (rem >= host) {
+        rem -= host;
+        ++host;
+    }
+    const int target = rem;
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    double sw = 0.0, sw2 = 0.0, fwd = 0.0;
+    StoufferAcc zl, zr;
+    bool any = false;
+    for (int b = 0; b < P.nblocks; ++b) {
+        const double nh = P.sizes[b * P.G + host], nt = P.sizes[b * P.G + target];
+        const double hdf = fmax(0.0, nh - 1.0), tdf = fmax(0.0, nt - 1.0);
+        if (!(hdf > 0.0 && tdf > 0.0)) continue;  // df would be NA: no valid test in this block
+        const size_t ch = ((size_t)b * P.G + host) * P.ngenes + g, ct = ((size_t)b * P.G + target) * P.ngenes + g;
+        const double hv = P.var[ch], tv = P.var[ct];
+        const double hs2 = fmax(hv, 1e-8), ts2 = fmax(tv, 1e-8);
+        const double herr = hs2 / nh, terr = ts2 / nt;
+        const double err = herr + terr;
+        const double df = err * err / (herr * herr / hdf + terr * terr / tdf);
+        const double cur = P.mean[ch] - P.mean[ct];
+        const double se = sqrt(err);
+        double left, right;
+        if (P.thr == 0.0) {
+            const double tt = cur / se;
+            left = log_pt(tt, df, true);
+            right = log_pt(tt, df, false);
+        } else {
+            left = log_pt((cur + P.thr) / se, df, true);
+            right = log_pt((cur - P.thr) / se, df, false);
+        }
+        double eff = cur;
+        if (P.std_lfc) {
+            const double pooled = ((nh - 1.0) * hv + (nt - 1.0) * tv) / (nt + nh - 2.0);
+            eff = cur == 0.0 ? 0.0 : cur / sqrt(pooled);
+        }
+        const double w = 1.0 / (1.0 / nh + 1.0 / nt);
+        any = true;
+        sw += w;
+        sw2 += w * w;
+        zl.add(left, w);
+        zr.add(right, w);
+        fwd += eff * w;
+    }
+    double fe = nan, hp = nan, tp = nan;
+    if (any) {
+        const double cl = zl.log_p(sw2), cr = zr.log_p(sw2);
+        hp = choose_p(cl, cr, P.direction);
+        tp = choose_p(cr, cl, P.direction);
+        fe = fwd / sw;
+    }
+    const size_t o1 = (size_t)ordered_index(host, target, P.G) * P.ngenes + g;
+    const size_t o2 = (size_t)ordered_index(target, host, P.G) * P.ngenes + g;
+    P.effect[o1] = fe;
+    P.logp[o1] = hp;
+    P.effect[o2] = -fe;
     P.logp[o2] = tp;
 }
 
@@ -232,6 +336,35 @@ __global__ void __launch_bounds__(SORT_THREADS) k6_log_bh(LogBhParams P) {
 void run_pairs(scranb200_ctx* ctx, const scranb200_mat* mat, PairLayout& L, DevBuf& lbuf, bool want_stats, double lfc,
                bool want_u, bool want_t);  // api.cu
 
+namespace {
+
+// .logBH over the genes for every ordered pair, then the three result arrays to the host.
+void finish_layer(scranb200_ctx* ctx, int64_t ngenes, int nout, double* d_effect, double* d_logp, double* d_logfdr,
+                  double* effect, double* logp, double* logfdr) {
+    const size_t out_bytes = (size_t)nout * ngenes * 8;
+    LogBhParams bp;
+    bp.n = (int)ngenes;
+    bp.ncols = nout;
+    bp.logp = d_logp;
+    bp.logfdr = d_logfdr;
+    const int grid = std::min(nout, ctx->sm_count);
+    ctx->rank_keys.reserve((size_t)grid * ngenes * 16);
+    ctx->rank_idx.reserve((size_t)grid * ngenes * 8);
+    bp.g_ka = ctx->rank_keys.as<uint64_t>();
+    bp.g_kb = bp.g_ka + (size_t)grid * ngenes;
+    bp.g_pa = ctx->rank_idx.as<uint32_t>();
+    bp.g_pb = bp.g_pa + (size_t)grid * ngenes;
+    const size_t smem = (size_t)(SORT_HIST_WORDS + 1) * 4 + (size_t)SORT_THREADS * 8 + 64;
+    allow_smem(k6_log_bh, smem);
+    SB_LAUNCH(ctx, k6_log_bh, grid, SORT_THREADS, smem, bp);
+    SB_CUDA(cudaMemcpyAsync(effect, d_effect, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    SB_CUDA(cudaMemcpyAsync(logp, d_logp, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    SB_CUDA(cudaMemcpyAsync(logfdr, d_logfdr, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+}
+
+}  // namespace
+
 // effect / logp / logfdr: host arrays [G (G - 1)][ngenes].
 void run_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int G, const int32_t* block,
                          int nblocks, double lfc, int direction, double* effect, double* logp, double* logfdr) {
@@ -303,25 +436,51 @@ void run_pairwise_wilcox(scranb200_ctx* ctx, const scranb200_mat* mat, const int
     wp.logp = d_logp;
     const int64_t items = ngenes * (int64_t)(G * (G - 1) / 2);
     SB_LAUNCH(ctx, k6_wilcox_layer, (unsigned)ceil_div(items, 256), 256, 0, wp);
-    LogBhParams bp;
-    bp.n = (int)ngenes;
-    bp.ncols = nout;
-    bp.logp = d_logp;
-    bp.logfdr = d_logfdr;
-    const int grid = std::min(nout, ctx->sm_count);
-    ctx->rank_keys.reserve((size_t)grid * ngenes * 16);
-    ctx->rank_idx.reserve((size_t)grid * ngenes * 8);
-    bp.g_ka = ctx->rank_keys.as<uint64_t>();
-    bp.g_kb = bp.g_ka + (size_t)grid * ngenes;
-    bp.g_pa = ctx->rank_idx.as<uint32_t>();
-    bp.g_pb = bp.g_pa + (size_t)grid * ngenes;
-    const size_t smem = (size_t)(SORT_HIST_WORDS + 1) * 4 + (size_t)SORT_THREADS * 8 + 64;
-    allow_smem(k6_log_bh, smem);
-    SB_LAUNCH(ctx, k6_log_bh, grid, SORT_THREADS, smem, bp);
-    SB_CUDA(cudaMemcpyAsync(effect, d_effect, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    SB_CUDA(cudaMemcpyAsync(logp, d_logp, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    SB_CUDA(cudaMemcpyAsync(logfdr, d_logfdr, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    finish_layer(ctx, ngenes, nout, d_effect, d_logp, d_logfdr, effect, logp, logfdr);
+}
+
+// pairwiseTTests (block= branch): blocked statistics on the device (K1 + K2 with the reference's own ids,
+// group + block * ngroups: R/pairwiseTTests.R:242), then the t-test layer and .logBH.
+void run_pairwise_ttests(scranb200_ctx* ctx, const scranb200_mat* mat, const int32_t* group, int G, const int32_t* block,
+                         int nblocks, double lfc, int direction, int std_lfc, double* effect, double* logp, double* logfdr) {
+    const int64_t ncells = mat->ncol, ngenes = mat->nrow;
+    if (G < 2 || ngenes == 0) return;
+    std::vector<int32_t> ids(ncells);
+    std::vector<double> sizes((size_t)nblocks * G, 0.0);
+    for (int64_t c = 0; c < ncells; ++c) {
+        const int b = block ? block[c] : 0;
+        if (group[c] >= G || (block && b >= nblocks)) throw Error("group or block code out of range");
+        ids[c] = group[c] < 0 || b < 0 ? -1 : b * G + group[c];
+        if (ids[c] >= 0) sizes[ids[c]] += 1.0;
+    }
+    PairLayout L;
+    build_layout(ids.data(), ncells, nblocks * G, nullptr, nullptr, 0, ctx->sm_count * 4, L);
+    upload_layout(ctx, L, ctx->layout_i32);
+    run_pairs(ctx, mat, L, ctx->layout_i32, true, 0.0, false, false);
+    const int nout = G * (G - 1);
+    const size_t out_bytes = (size_t)nout * ngenes * 8;
+    ctx->eff.reserve(out_bytes * 3);
+    double* d_effect = ctx->eff.as<double>();
+    double* d_logp = d_effect + (size_t)nout * ngenes;
+    double* d_logfdr = d_logp + (size_t)nout * ngenes;
+    ctx->io_c.reserve(sizes.size() * 8 + 64);
+    SB_CUDA(cudaMemcpyAsync(ctx->io_c.p, sizes.data(), sizes.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
     SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    TTestLayerParams tp;
+    tp.ngenes = (int)ngenes;
+    tp.G = G;
+    tp.nblocks = nblocks;
+    tp.direction = direction;
+    tp.std_lfc = std_lfc;
+    tp.thr = std::fabs(lfc);
+    tp.mean = ctx->mean.as<double>();
+    tp.var = ctx->var.as<double>();
+    tp.sizes = ctx->io_c.as<double>();
+    tp.effect = d_effect;
+    tp.logp = d_logp;
+    const int64_t items = ngenes * (int64_t)(G * (G - 1) / 2);
+    SB_LAUNCH(ctx, k6_ttest_layer, (unsigned)ceil_div(items, 256), 256, 0, tp);
+    finish_layer(ctx, ngenes, nout, d_effect, d_logp, d_logfdr, effect, logp, logfdr);
 }
 
 }  // namespace sb

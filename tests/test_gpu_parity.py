@@ -408,9 +408,8 @@ def test_pairwise_wilcox_layers(sb, port_lib, direction, lfc):
     block = rng.integers(0, 3, 420)
     for blk in (None, block):
         want = rlevel.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, lib=port_lib)
-        for host_layer in (False, True):  # p-value layer on the device (the default) / in numpy on the device statistics
-            got = sb.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, host_layer=host_layer)
-            _pair_lists_match(got, want)
+        got = sb.pairwise_wilcox(as_csc(x), groups, block=blk, lfc=lfc, direction=direction)
+        _pair_lists_match(got, want)
 
 
 def test_pairwise_wilcox_extreme_tails_and_empty_combinations(sb, port_lib):
@@ -449,3 +448,47 @@ def test_pairwise_t_tests_layers(sb, port_lib, direction, lfc):
             got = sb.pairwise_t_tests(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, std_lfc=std)
             want = rlevel.pairwise_ttests(as_csc(x), groups, block=blk, lfc=lfc, direction=direction, std_lfc=std, lib=port_lib)
             _pair_lists_match(got, want)
+
+
+def test_pairwise_t_tests_equal_welch_t_test(sb):
+    """The reference's own check (tests/testthat/test-pairwise-t.R:52-95): without blocking, every pair's
+    p-value is stats::t.test's (Welch), here scipy.stats.ttest_ind(equal_var=False); one-sided directions too."""
+    import scipy.stats as st
+    rng = np.random.default_rng(44)
+    x = make_matrix(60, 300, seed=144, rate=1.5, integer_rows=False)
+    x[1, ::3] = 2.5                                   # the all-equal row gets some variation
+    groups = rng.integers(0, 3, 300)
+    for direction, alt in (("any", "two-sided"), ("up", "greater"), ("down", "less")):
+        got = sb.pairwise_t_tests(x, groups, direction=direction)
+        for q in got:
+            a, b = x[:, groups == q["first"]], x[:, groups == q["second"]]
+            ref = st.ttest_ind(a, b, axis=1, equal_var=False, alternative=alt)
+            ok = np.isfinite(ref.pvalue) & (a.var(1) > 1e-8) & (b.var(1) > 1e-8)  # (the reference floors tiny variances)
+            np.testing.assert_allclose(q["log_p"][ok], np.log(ref.pvalue[ok]), rtol=1e-9, atol=1e-12)
+            np.testing.assert_allclose(q["effect"], a.mean(1) - b.mean(1), rtol=1e-12, atol=1e-13)
+
+
+def test_pairwise_t_tests_extreme_tails(sb, port_lib):
+    """Thousands of cells per group and well separated means: log p-values far below the smallest double
+    (the continued fraction of the incomplete beta function in log space), large Welch degrees of freedom,
+    a group with a single cell in one block (that block is not a valid test), a constant gene."""
+    from oracle import rlevel
+    rng = np.random.default_rng(45)
+    ncells = 9000
+    groups = rng.integers(0, 3, ncells)
+    block = rng.integers(0, 2, ncells)
+    one = np.flatnonzero((groups == 2) & (block == 1))
+    block[one[1:]] = 0                               # group 2 keeps ONE cell in block 1
+    x = np.zeros((6, ncells))
+    x[0] = groups * 4.0 + rng.normal(size=ncells)    # |t| ~ 150
+    x[1] = groups * 0.05 + rng.normal(size=ncells)
+    x[2] = 1.0
+    x[3] = rng.poisson(0.3, ncells)
+    x[4] = groups * 30.0 + rng.random(ncells)        # |t| in the thousands
+    x[5] = np.where(groups == 1, 1e-3 * rng.random(ncells), 0.0)
+    for blk in (None, block):
+        for lfc in (0.0, 1.0):
+            got = sb.pairwise_t_tests(x, groups, block=blk, lfc=lfc)
+            want = rlevel.pairwise_ttests(x, groups, block=blk, lfc=lfc, lib=port_lib)
+            _pair_lists_match(got, want)
+    assert min(np.nanmin(q["log_p"]) for q in got) < -1000
