@@ -123,6 +123,22 @@ int scranb200_pairwise_t_tests(scranb200_ctx* ctx, const scranb200_mat* mat, con
                                const int32_t* block, int nblocks, double lfc, int direction, int std_lfc,
                                double* effect_out, double* logp_out, double* logfdr_out);
 
+/* ---- combineMarkers: R/combineMarkers.R:182-330 with src/choose_effect_size.cpp:35-97 ----------
+ *  What .combine_markers_internal does for the contrasts of ONE first group,
+ * on log p-values (log.p.in = log.p.out = TRUE), including the two native helpers it calls
+ * (.Call symbols _scran_compute_Top_statistic_from_ranks, src/RcppExports.cpp, and
+ * _scran_choose_middle_effect_size). logp, effect: host [ncon][ngenes], NaN = NA; effect nullable.
+ * pval_type: 0 "any" (Simes; Top = the ceiling(n min_prop)-th smallest rank over the contrasts, ranks by
+ * rank(ties.method = "first") across the genes), 1 "some" (the ceiling(n min_prop)-th Holm-adjusted
+ * p-value), 2 "all" (the largest). The reference's defaults: min_prop = 0 for "any", 0.5 otherwise.
+ * Outputs, host arrays of ngenes in the ORIGINAL gene order, any of them nullable: top_out (int32,
+ * SCRANB200_NA_INT = NA; written for "any" only), logp_out, logfdr_out (.logBH), summary_out
+ * (.choose_effect_size), and order_out: the 0-based row order the reference applies last
+ * (order(Top) for "any", order(p) otherwise; ties by position, NA last). */
+int scranb200_combine_markers(scranb200_ctx* ctx, int64_t ngenes, int ncon, const double* logp, const double* effect,
+                              int pval_type, double min_prop, int32_t* top_out, double* logp_out, double* logfdr_out,
+                              double* summary_out, int32_t* order_out);
+
 /* ---- overlap_exprs_paired: src/overlap_exprs.cpp:196-220 ------------------------------------
  * groups: the reference's list of 0-based cell-index vectors, flattened: group g owns
  * group_cells[group_ptr[g] .. group_ptr[g+1]). A cell may belong to at most one group (the

@@ -97,6 +97,12 @@ class Checker:
         f = getattr(self.lib, prefix + "overlap")
         f.restype = C.c_int
         f.argtypes = mat + [C.c_int, _i64p, _i32p, C.c_double, _f64p, _f64p]
+        f = getattr(self.lib, prefix + "top_from_ranks")
+        f.restype = C.c_int
+        f.argtypes = [C.c_int, C.c_int64, _i32p, C.c_double, _i32p]
+        f = getattr(self.lib, prefix + "choose_middle")
+        f.restype = C.c_int
+        f.argtypes = [C.c_int, C.c_int64, _f64p, _f64p, C.c_double, _f64p]
 
     def _check(self, rc):
         if rc != 0:
@@ -168,6 +174,25 @@ class Checker:
         self._check(getattr(self.lib, self.prefix + "overlap")(*m.args(), G, gptr, cells, float(lfc), U.reshape(-1),
                                                       T.reshape(-1)))
         return U, T
+
+
+    def top_from_ranks(self, ranks, prop):
+        """compute_Top_statistic_from_ranks(Ranks, prop): ranks [ncon, ngenes] int (NA_INT = NA) -> int[ngenes]."""
+        ranks = np.ascontiguousarray(ranks, dtype=np.int32)
+        out = np.zeros(max(1, ranks.shape[1]), np.int32)
+        self._check(getattr(self.lib, self.prefix + "top_from_ranks")(ranks.shape[0], ranks.shape[1],
+                                                              ranks.reshape(-1) if ranks.size else np.zeros(1, np.int32),
+                                                              float(prop), out))
+        return out[:ranks.shape[1]]
+
+    def choose_middle(self, pvals, effects, prop):
+        """choose_middle_effect_size(Pvals, Effects, prop): [ncon, ngenes] doubles (NaN = NA) -> double[ngenes]."""
+        pvals = np.ascontiguousarray(pvals, dtype=np.float64)
+        effects = np.ascontiguousarray(effects, dtype=np.float64)
+        out = np.zeros(max(1, pvals.shape[1]), np.float64)
+        self._check(getattr(self.lib, self.prefix + "choose_middle")(pvals.shape[0], pvals.shape[1], pvals.reshape(-1),
+                                                             effects.reshape(-1), float(prop), out))
+        return out[:pvals.shape[1]]
 
 
 def load(kind="best"):

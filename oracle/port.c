@@ -20,6 +20,7 @@
  * Matrices are CSC (p: int64[ncol+1], i: int32 rows ascending in a column, x: double) or
  * dense column-major; outputs are caller-allocated.
  */
+#include <limits.h>
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -402,5 +403,70 @@ int oracle_port_overlap(int64_t nrow, int64_t ncol, const int64_t* p, const int3
     free(row);
     row_source_free(&rs);
     ranker_free(&r);
+    return 0;
+}
+
+/* ---- combineMarkers' native helpers: src/choose_effect_size.cpp:26-97 ---------------------------
+ * define_jump (:26-33): index of the (prop * n)-th smallest of n values, 0-based, 0 when prop == 0. */
+static size_t port_define_jump(size_t n, double prop) {
+    size_t jump = (size_t)ceil((double)n * prop);
+    if (jump) --jump;
+    return jump;
+}
+
+static int port_cmp_int(const void* a, const void* b) {
+    const int x = *(const int*)a, y = *(const int*)b;
+    return (x > y) - (x < y);
+}
+
+/* compute_Top_statistic_from_ranks (:35-61). ranks: [ncon][ngenes], INT_MIN = NA. */
+int oracle_port_top_from_ranks(int ncon, int64_t ngenes, const int* ranks, double prop, int* out) {
+    int* col = (int*)malloc((size_t)(ncon > 0 ? ncon : 1) * sizeof(int));
+    for (int64_t g = 0; g < ngenes; ++g) {
+        size_t nonna = 0;
+        for (int c = 0; c < ncon; ++c) {
+            const int r = ranks[(size_t)c * ngenes + g];
+            if (r != INT_MIN) col[nonna++] = r;
+        }
+        out[g] = INT_MIN;
+        if (nonna) {
+            qsort(col, nonna, sizeof(int), port_cmp_int);  /* the element nth_element would put at `jump` */
+            out[g] = col[port_define_jump(nonna, prop)];
+        }
+    }
+    free(col);
+    return 0;
+}
+
+typedef struct {
+    double p, e;
+} port_pe;
+static int port_cmp_pe(const void* a, const void* b) { /* std::pair's operator<: first, then second */
+    const port_pe *x = (const port_pe*)a, *y = (const port_pe*)b;
+    if (x->p < y->p) return -1;
+    if (y->p < x->p) return 1;
+    return (x->e > y->e) - (x->e < y->e);
+}
+
+/* choose_middle_effect_size (:64-97). pvals / effects: [ncon][ngenes], NaN = NA. */
+int oracle_port_choose_middle(int ncon, int64_t ngenes, const double* pvals, const double* effects, double prop, double* out) {
+    port_pe* col = (port_pe*)malloc((size_t)(ncon > 0 ? ncon : 1) * sizeof(port_pe));
+    for (int64_t g = 0; g < ngenes; ++g) {
+        size_t nonna = 0;
+        for (int c = 0; c < ncon; ++c) {
+            const double p = pvals[(size_t)c * ngenes + g], e = effects[(size_t)c * ngenes + g];
+            if (!isnan(p) && !isnan(e)) {
+                col[nonna].p = p;
+                col[nonna].e = e;
+                ++nonna;
+            }
+        }
+        out[g] = NAN;
+        if (nonna) {
+            qsort(col, nonna, sizeof(port_pe), port_cmp_pe);
+            out[g] = col[port_define_jump(nonna, prop)].e;
+        }
+    }
+    free(col);
     return 0;
 }

@@ -1,6 +1,6 @@
 // TEST INFRASTRUCTURE ONLY. extern "C" driver around the reference's own object code.
 //
-// Links against /root/reference/src/overlap_exprs.cpp and compute_blocked_stats.cpp,
+// Links against /root/reference/src/overlap_exprs.cpp, compute_blocked_stats.cpp and choose_effect_size.cpp,
 // compiled unmodified against oracle/stubs (see oracle/Makefile), and exposes flat-array
 // entry points so that Python (ctypes) can run the reference arithmetic on CSC / dense
 // inputs. Output goes to oracle/_ref/liboracle_ref.so, which is git-ignored.
@@ -21,6 +21,10 @@ Rcpp::List compute_blocked_stats_norm(Rcpp::RObject mat, Rcpp::IntegerVector blo
 Rcpp::List overlap_exprs(Rcpp::RObject exprs, Rcpp::List groups, double lfc);
 Rcpp::NumericMatrix overlap_exprs_paired(Rcpp::RObject exprs, Rcpp::IntegerVector left,
                                          Rcpp::IntegerVector right, Rcpp::List groups, double lfc);
+
+// src/choose_effect_size.cpp:35, 64 (the native helpers of combineMarkers)
+Rcpp::IntegerVector compute_Top_statistic_from_ranks(Rcpp::List Ranks, double prop);
+Rcpp::NumericVector choose_middle_effect_size(Rcpp::List Pvals, Rcpp::List Effects, double prop);
 
 namespace {
 thread_local std::string g_err;
@@ -115,6 +119,37 @@ int oracle_ref_overlap(int64_t nrow, int64_t ncol, const int64_t* p, const int* 
                 }
             }
         }
+        return 0;
+    } catch (std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+// ranks: [ncon][ngenes] integers (NA_INTEGER = NA), one rank vector per contrast. out: ngenes.
+int oracle_ref_top_from_ranks(int ncon, int64_t ngenes, const int* ranks, double prop, int* out) {
+    try {
+        Rcpp::List lst(ncon);
+        for (int c = 0; c < ncon; ++c) lst[c].ivec = std::make_shared<std::vector<int>>(ranks + c * ngenes, ranks + (c + 1) * ngenes);
+        Rcpp::IntegerVector res = compute_Top_statistic_from_ranks(lst, prop);
+        std::memcpy(out, res.begin(), static_cast<size_t>(ngenes) * sizeof(int));
+        return 0;
+    } catch (std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+// pvals / effects: [ncon][ngenes] doubles (NaN = NA). out: ngenes.
+int oracle_ref_choose_middle(int ncon, int64_t ngenes, const double* pvals, const double* effects, double prop, double* out) {
+    try {
+        Rcpp::List lp(ncon), le(ncon);
+        for (int c = 0; c < ncon; ++c) {
+            lp[c].nvec = std::make_shared<std::vector<double>>(pvals + c * ngenes, pvals + (c + 1) * ngenes);
+            le[c].nvec = std::make_shared<std::vector<double>>(effects + c * ngenes, effects + (c + 1) * ngenes);
+        }
+        Rcpp::NumericVector res = choose_middle_effect_size(lp, le, prop);
+        std::memcpy(out, res.begin(), static_cast<size_t>(ngenes) * sizeof(double));
         return 0;
     } catch (std::exception& e) {
         g_err = e.what();

@@ -563,3 +563,96 @@ def pairwise_ttests(x, groups, block=None, lfc=0.0, direction="any", std_lfc=Fal
                     valid=bool(np.all(~np.isnan(df))))
 
     return _blocked_template(levels, nb, direction, statfun)
+
+
+# ----------------------------------------------------------------------------------------------
+# combineMarkers (R/combineMarkers.R:182-330) on log p-values
+# ----------------------------------------------------------------------------------------------
+
+def combine_parallel_log_p(logp, method, min_prop):
+    """metapod::combineParallelPValues(list, method=, log.p=TRUE, min.prop=) restated from what the reference's
+    tests pin (tests/testthat/test-combine-markers.R:19-137): "simes" = min over the contrasts of the BH-adjusted
+    p-values; "berger" = the largest; "holm-min" = the ceiling(n min.prop)-th smallest Holm-adjusted one, n = the
+    gene's number of non-NA p-values. logp: [ncon, ngenes], NaN = NA. All NA -> NA."""
+    logp = np.asarray(logp, np.float64)
+    ncon, ngenes = logp.shape
+    out = np.full(ngenes, np.nan)
+    for g in range(ngenes):
+        p = np.sort(logp[~np.isnan(logp[:, g]), g])
+        n = len(p)
+        if n == 0:
+            continue
+        k = np.arange(1, n + 1)
+        if method == "simes":
+            out[g] = min(0.0, np.min(p + np.log(n / k)))
+        elif method == "berger":
+            out[g] = p[-1]
+        elif method == "holm-min":
+            adj = np.maximum.accumulate(np.minimum(0.0, p + np.log(n - k + 1)))
+            jump = max(int(np.ceil(n * min_prop)), 1) - 1
+            out[g] = adj[jump]
+        else:
+            raise ValueError(method)
+    return out
+
+
+def rank_first(v):
+    """rank(v, ties.method="first", na.last="keep") -> int32 with NA_INT for NA."""
+    v = np.asarray(v, np.float64)
+    out = np.full(len(v), native.NA_INT, np.int32)
+    ok = np.flatnonzero(~np.isnan(v))
+    o = ok[np.argsort(v[ok], kind="stable")]
+    out[o] = np.arange(1, len(o) + 1)
+    return out
+
+
+def order_na_last(v):
+    """order(v): ascending, ties by position, NA last."""
+    v = np.asarray(v, np.float64)
+    ok = np.flatnonzero(~np.isnan(v))
+    na = np.flatnonzero(np.isnan(v))
+    return np.concatenate([ok[np.argsort(v[ok], kind="stable")], na])
+
+
+def combine_markers_one(logp, effects, pval_type="any", min_prop=None, lib=None):
+    """.combine_markers_internal (R/combineMarkers.R:232-300) for the contrasts of one first group, log.p.in =
+    log.p.out = TRUE, sorted = TRUE. logp / effects: [ncon, ngenes]. Returns dict(Top (any only), log_p, log_fdr,
+    summary, order): everything in the ORIGINAL gene order plus the ordering the reference applies last. Top and
+    the "some" summary effect come from the reference's own native helpers (lib)."""
+    lib = lib or native.load("best")
+    logp = np.asarray(logp, np.float64)
+    method = {"any": "simes", "some": "holm-min", "all": "berger"}[pval_type]
+    if min_prop is None:
+        min_prop = 0.0 if pval_type == "any" else 0.5
+    pval = combine_parallel_log_p(logp, method, min_prop)
+    res = {}
+    if pval_type == "any":
+        ranked = np.stack([rank_first(logp[c]) for c in range(logp.shape[0])], 0)
+        top = lib.top_from_ranks(ranked, min_prop)
+        res["Top"] = top
+        order = order_na_last(np.where(top == native.NA_INT, np.nan, top.astype(np.float64)))
+    else:
+        order = order_na_last(pval)
+    res["log_p"] = pval
+    res["log_fdr"] = log_bh(pval) if not np.any(np.isnan(pval)) else np.full(len(pval), np.nan)
+    if effects is not None:
+        effects = np.asarray(effects, np.float64)
+        ngenes = logp.shape[1]
+        chosen = np.full(ngenes, np.nan)
+        if pval_type == "all":      # .choose_effect_size (:302-330): the effect of the largest p-value
+            worst = np.full(ngenes, -np.inf)
+            for c in range(logp.shape[0]):
+                worse = (logp[c] > worst) & ~np.isnan(logp[c])
+                chosen[worse] = effects[c][worse]
+                worst[worse] = logp[c][worse]
+        elif pval_type == "any":
+            best = np.full(ngenes, np.inf)
+            for c in range(logp.shape[0]):
+                better = (logp[c] < best) & ~np.isnan(logp[c])
+                chosen[better] = effects[c][better]
+                best[better] = logp[c][better]
+        else:
+            chosen = lib.choose_middle(logp, effects, min_prop)
+        res["summary"] = chosen
+    res["order"] = order
+    return res

@@ -1,7 +1,7 @@
 // TEST INFRASTRUCTURE ONLY — not product code, never linked into libscranb200.
 //
-// A minimal stand-in for the parts of Rcpp that the reference's two hot-path translation
-// units (src/overlap_exprs.cpp, src/compute_blocked_stats.cpp) touch, so that those files
+// A minimal stand-in for the parts of Rcpp that the reference's hot-path translation
+// units (src/overlap_exprs.cpp, src/compute_blocked_stats.cpp, src/choose_effect_size.cpp) touch, so that those files
 // can be compiled UNMODIFIED, from where they lie under /root/reference, into
 // oracle/_ref/liboracle_ref.so (see oracle/Makefile). Rcpp and R are not installed in
 // this image. Surface listed in SURVEY.md Appendix B. Everything here is plain
@@ -54,6 +54,7 @@ class StubVector {
 public:
     StubVector() : store(std::make_shared<std::vector<T>>()) {}
     explicit StubVector(size_t n) : store(std::make_shared<std::vector<T>>(n)) {}
+    StubVector(size_t n, T fill) : store(std::make_shared<std::vector<T>>(n, fill)) {}
     StubVector(const T* b, const T* e) : store(std::make_shared<std::vector<T>>(b, e)) {}
     size_t size() const { return store->size(); }
     T* begin() { return store->data(); }
@@ -92,6 +93,7 @@ class IntegerVector;
 // One slot of a List: may hold an integer vector, a numeric matrix or a nested list.
 struct ListSlot {
     std::shared_ptr<std::vector<int>> ivec;
+    std::shared_ptr<std::vector<double>> nvec;
     std::shared_ptr<NumericMatrix> nmat;
     std::shared_ptr<List> sub;
     ListSlot& operator=(const NumericMatrix& m) {
@@ -105,6 +107,7 @@ class IntegerVector : public StubVector<int> {
 public:
     IntegerVector() {}
     explicit IntegerVector(size_t n) : StubVector<int>(n) {}
+    IntegerVector(size_t n, int fill) : StubVector<int>(n, fill) {}
     IntegerVector(const int* b, const int* e) : StubVector<int>(b, e) {}
     IntegerVector(const ListSlot& s) {
         if (!s.ivec) throw std::runtime_error("stub: list slot holds no integer vector");
@@ -116,7 +119,12 @@ class NumericVector : public StubVector<double> {
 public:
     NumericVector() {}
     explicit NumericVector(size_t n) : StubVector<double>(n) {}
+    NumericVector(size_t n, double fill) : StubVector<double>(n, fill) {}
     NumericVector(const double* b, const double* e) : StubVector<double>(b, e) {}
+    NumericVector(const ListSlot& s) {
+        if (!s.nvec) throw std::runtime_error("stub: list slot holds no numeric vector");
+        store = s.nvec;
+    }
 };
 
 class List {

@@ -49,6 +49,7 @@ def _signatures():
         "scranb200_blocked_stats": (C.c_int, [c_ctx, c_mat, _p, C.c_int, _p, _p, _p]),
         "scranb200_pairwise_wilcox": (C.c_int, [c_ctx, c_mat, _p, C.c_int, _p, C.c_int, C.c_double, C.c_int, _p, _p, _p]),
         "scranb200_pairwise_t_tests": (C.c_int, [c_ctx, c_mat, _p, C.c_int, _p, C.c_int, C.c_double, C.c_int, C.c_int, _p, _p, _p]),
+        "scranb200_combine_markers": (C.c_int, [c_ctx, i64, C.c_int, _p, _p, C.c_int, C.c_double, _p, _p, _p, _p, _p]),
         "scranb200_blocked_stats_transformed": (C.c_int, [c_ctx, c_mat, _p, C.c_int, C.c_int, _p, C.c_double, _p, _p]),
         "scranb200_overlap_exprs_paired": (C.c_int, [c_ctx, c_mat, _p, _p, i64, C.c_int, _p, _p, dbl, _p, _p]),
         "scranb200_overlap_exprs": (C.c_int, [c_ctx, c_mat, C.c_int, _p, _p, dbl, _p, _p]),

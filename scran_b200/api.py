@@ -480,3 +480,57 @@ def pairwise_t_tests(x, groups, block=None, lfc=0.0, direction="any", std_lfc=Fa
                                            ("any", "up", "down").index(direction), int(bool(std_lfc)), ptr(eff), ptr(lp),
                                            ptr(lf)))
     return _pair_list(levels, eff, lp, lf)
+
+
+# ---------------------------------------------------------------------------------------------
+# combineMarkers / findMarkers
+# ---------------------------------------------------------------------------------------------
+
+def combine_markers(de_lists, pval_type="any", min_prop=None, effect_field="effect", sorted_rows=True, ctx=None):
+    """combineMarkers(de.lists, pairs, pval.type=, min.prop=, log.p.in=TRUE, log.p.out=TRUE, sorted=)
+    (R/combineMarkers.R:182-300) on the list pairwise_wilcox / pairwise_t_tests return (every element carries
+    its own `first` / `second`, the reference's `pairs`). Returns an OrderedDict first -> OrderedDict with
+    "Top" (pval_type "any" only), "log.p.value", "log.FDR", "summary.<effect>", one "<effect>.<second>" column
+    per contrast, and "order" (the row order the reference sorts by; applied to every column if sorted_rows)."""
+    if pval_type not in ("any", "some", "all"):
+        raise ValueError("'pval.type' should be one of 'any', 'some', 'all'")
+    if min_prop is None:
+        min_prop = 0.0 if pval_type == "any" else 0.5
+    ctx = ctx or default_context()
+    firsts = []
+    for q in de_lists:
+        if q["first"] not in firsts:
+            firsts.append(q["first"])
+    out = OrderedDict()
+    for f in firsts:
+        cur = [q for q in de_lists if q["first"] == f]
+        logp = np.ascontiguousarray(np.stack([q["log_p"] for q in cur], 0), np.float64)
+        eff = np.ascontiguousarray(np.stack([q[effect_field] for q in cur], 0), np.float64)
+        ncon, ngenes = logp.shape
+        top = np.zeros(ngenes, np.int32)
+        p = np.zeros(ngenes, np.float64)
+        fdr = np.zeros(ngenes, np.float64)
+        summ = np.zeros(ngenes, np.float64)
+        order = np.zeros(ngenes, np.int32)
+        check(lib().scranb200_combine_markers(ctx.handle, ngenes, ncon, ptr(logp), ptr(eff), ("any", "some", "all").index(pval_type),
+                                              float(min_prop), ptr(top), ptr(p), ptr(fdr), ptr(summ), ptr(order)))
+        cols = OrderedDict()
+        if pval_type == "any":
+            cols["Top"] = top
+        cols["log.p.value"] = p
+        cols["log.FDR"] = fdr
+        cols["summary." + effect_field] = summ
+        for k, q in enumerate(cur):
+            cols["%s.%s" % (effect_field, q["second"])] = eff[k]
+        if sorted_rows:
+            for name in list(cols):
+                cols[name] = cols[name][order]
+        cols["order"] = order
+        out[f] = cols
+    return out
+
+
+def find_markers_wilcox(x, groups, block=None, lfc=0.0, direction="any", pval_type="any", min_prop=None):
+    """findMarkers(x, groups, test.type="wilcox", block=, lfc=, direction=, pval.type=, min.prop=, log.p=TRUE)
+    (R/findMarkers.R:123-156): pairwiseWilcox followed by combineMarkers, both on the device."""
+    return combine_markers(pairwise_wilcox(x, groups, block=block, lfc=lfc, direction=direction), pval_type, min_prop)

@@ -221,3 +221,35 @@ def test_transformed_blocked_stats_pin(port_lib, oracle_lib, sparse):
             keep = block == b
             assert np.allclose(pm[:, b], y[:, keep].mean(1), rtol=1e-12, atol=1e-14)
             assert np.allclose(pv[:, b], y[:, keep].var(1, ddof=1), rtol=1e-10, atol=1e-14)
+
+
+def test_combine_markers_helpers_port_equals_reference_object_code(port_lib):
+    """compute_Top_statistic_from_ranks / choose_middle_effect_size (src/choose_effect_size.cpp:35-97): the C
+    restatement against the reference's own object code, and the R-level restatement of combineMarkers against
+    the definitions the reference's tests use (tests/testthat/test-combine-markers.R:19-137)."""
+    from oracle import native, rlevel
+    from scipy.stats import false_discovery_control
+    rng = np.random.default_rng(23)
+    lp = np.log(rng.random((9, 200)))
+    lp[2, 5] = np.nan
+    lp[:, 7] = np.nan
+    lp[:, 50:60] = np.round(lp[:, 50:60], 1)
+    eff = rng.normal(size=(9, 200))
+    eff[4, 9] = np.nan
+    ranks = np.stack([rlevel.rank_first(lp[c]) for c in range(9)])
+    libs = [port_lib] + ([native.load("ref")] if native.have_ref() else [])
+    for prop in (0.0, 0.25, 0.5, 1.0):
+        tops = [lib.top_from_ranks(ranks, prop) for lib in libs]
+        mids = [lib.choose_middle(lp, eff, prop) for lib in libs]
+        assert all(np.array_equal(t, tops[0]) for t in tops)
+        assert all(np.array_equal(m, mids[0], equal_nan=True) for m in mids)
+    assert tops[0][7] == native.NA_INT
+    ok = ~np.isnan(lp).any(0)
+    res = rlevel.combine_markers_one(lp, eff, "any", lib=port_lib)
+    want = np.array([np.log(false_discovery_control(np.exp(lp[:, g])).min()) for g in np.flatnonzero(ok)])
+    np.testing.assert_allclose(res["log_p"][ok], want, rtol=1e-12)
+    assert np.array_equal(res["Top"][ok], ranks[:, ok].min(0))
+    assert np.isnan(res["log_fdr"]).all()           # one NA p-value makes .logBH's cummin all NA
+    res = rlevel.combine_markers_one(lp[:, ok], eff[:, ok], "all", lib=port_lib)
+    np.testing.assert_allclose(res["log_p"], lp[:, ok].max(0))
+    np.testing.assert_allclose(np.exp(res["log_fdr"]), false_discovery_control(np.exp(res["log_p"])), rtol=1e-12)
