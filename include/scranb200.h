@@ -54,6 +54,23 @@ int scranb200_upload_csc(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const i
                          const double* x, scranb200_mat** out);
 int scranb200_upload_csc32(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const int32_t* p, const int32_t* i,
                            const double* x, scranb200_mat** out);
+/* The same matrix in column chunks: for matrices that do not exist as one object on
+ * the caller's side. An R dgCMatrix holds at most 2^31 - 1 entries (its @p is int), so the 1.3M-cell matrix
+ * of config 3 (3.1e9 entries) can only arrive as several; HDF5-backed matrices (TENxMatrix) are read block by
+ * block anyway. scranb200_mat_begin fixes the shape (nnz_hint: expected stored entries, 0 = unknown; the
+ * device arrays grow when it is exceeded); every scranb200_mat_append_columns adds the next ncol_chunk
+ * columns as a CSC piece of its own (p: ncol_chunk + 1 entries starting at 0; _columns32 takes R's int @p);
+ * the host buffers may be pageable or pinned and are free again when the call returns.
+ * scranb200_mat_finish (all ncol_total columns appended) yields the matrix and ends the builder;
+ * scranb200_mat_abort drops a builder that will not be finished. */
+typedef struct scranb200_builder scranb200_builder;
+int scranb200_mat_begin(scranb200_ctx* ctx, int64_t nrow, int64_t ncol_total, int64_t nnz_hint, scranb200_builder** out);
+int scranb200_mat_append_columns(scranb200_builder* b, int64_t ncol_chunk, const int64_t* p, const int32_t* i,
+                                 const double* x);
+int scranb200_mat_append_columns32(scranb200_builder* b, int64_t ncol_chunk, const int32_t* p, const int32_t* i,
+                                   const double* x);
+int scranb200_mat_finish(scranb200_builder* b, scranb200_mat** out);
+void scranb200_mat_abort(scranb200_builder* b);
 /* Ordinary column-major double matrix; exact zeros are not stored (the reference's dense branch
  * skips them too: src/compute_blocked_stats.cpp:74, src/overlap_exprs.cpp:43-47). */
 int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const double* x, scranb200_mat** out);
@@ -204,6 +221,14 @@ int scranb200_plan_pairs(const scranb200_plan* plan, int32_t* comb_group, int32_
  * by output table in column order: the full.* matrices of full.stats=TRUE. */
 int scranb200_score_markers(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan,
                             double* out, double* full_out);
+
+/* ---- summaryMarkerStats: R/summaryMarkerStats.R:62-95 ---------------------
+ * Per group the mean expression and the proportion of cells with a value > 0 (self.average, self.detected)
+ * and their mean over the other groups (other.*): the first four columns of the scoreMarkers tables, from
+ * the blocked statistics alone (no sort, no pair counting). plan: scranb200_plan_create with the groups
+ * (block = NULL for the reference's function; with a block the columns are scoreMarkers' block-corrected
+ * ones). out: host [K][4][nrow] in the order self.average, other.average, self.detected, other.detected. */
+int scranb200_summary_marker_stats(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan, double* out);
 
 /* ---- staged form for gene-sharded multi-GPU runs (all buffers are DEVICE pointers) ----------
  * stage 1 on each gene shard: effects d_eff [3][Q][ld] (gene-contiguous columns, this shard's

@@ -41,6 +41,11 @@ def _signatures():
         "scranb200_ctx_last_timing": (C.c_int, [c_ctx, _p, C.c_int]),
         "scranb200_upload_csc": (C.c_int, [c_ctx, i64, i64, _p, _p, _p, PP]),
         "scranb200_upload_csc32": (C.c_int, [c_ctx, i64, i64, _p, _p, _p, PP]),
+        "scranb200_mat_begin": (C.c_int, [c_ctx, i64, i64, i64, PP]),
+        "scranb200_mat_append_columns": (C.c_int, [C.c_void_p, i64, _p, _p, _p]),
+        "scranb200_mat_append_columns32": (C.c_int, [C.c_void_p, i64, _p, _p, _p]),
+        "scranb200_mat_finish": (C.c_int, [C.c_void_p, PP]),
+        "scranb200_mat_abort": (None, [C.c_void_p]),
         "scranb200_upload_dense": (C.c_int, [c_ctx, i64, i64, _p, PP]),
         "scranb200_wrap_device_csc": (C.c_int, [c_ctx, i64, i64, i64, _p, _p, _p, PP]),
         "scranb200_mat_free": (None, [c_mat]),
@@ -59,6 +64,7 @@ def _signatures():
         "scranb200_plan_tables": (C.c_int, [c_plan, _p, _p, _p, _p]),
         "scranb200_plan_pairs": (C.c_int, [c_plan] + [_p] * 12),
         "scranb200_score_markers": (C.c_int, [c_ctx, c_mat, c_plan, _p, _p]),
+        "scranb200_summary_marker_stats": (C.c_int, [c_ctx, c_mat, c_plan, _p]),
         "scranb200_score_effects_dev": (C.c_int, [c_ctx, c_mat, c_plan, i64, i64, _p, _p]),
         "scranb200_score_minrank_dev": (C.c_int, [c_ctx, c_plan, i64, i64, _p, i64, i64, _p]),
         "scranb200_score_finish_dev": (C.c_int, [c_ctx, c_plan, i64, i64, _p, _p]),

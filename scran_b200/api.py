@@ -112,6 +112,40 @@ class DeviceMatrix:
         self.shape = (int(nrow), int(ncol))
 
     @classmethod
+    def from_column_chunks(cls, nrow, ncol, chunks, nnz_hint=0, ctx=None):
+        """A matrix that arrives as CSC pieces of consecutive columns (scranb200_mat_begin / _append_columns /
+        _finish): chunks = iterable of scipy.sparse matrices or (p, i, x) triples, p starting at 0 (int32 p, R's
+        own, is taken as it is)."""
+        self = cls.__new__(cls)
+        self.ctx = ctx or default_context()
+        b = C.c_void_p()
+        check(lib().scranb200_mat_begin(self.ctx.handle, int(nrow), int(ncol), int(nnz_hint), C.byref(b)))
+        try:
+            for ch in chunks:
+                if not isinstance(ch, tuple):
+                    ch = ch.tocsc()
+                    if not ch.has_sorted_indices:
+                        ch = ch.sorted_indices()
+                    ch = (ch.indptr, ch.indices, ch.data)
+                p, i, v = ch
+                i = np.ascontiguousarray(i, np.int32)
+                v = np.ascontiguousarray(v, np.float64)
+                if np.asarray(p).dtype == np.int32:
+                    p = np.ascontiguousarray(p)
+                    check(lib().scranb200_mat_append_columns32(b, len(p) - 1, ptr(p), ptr(i), ptr(v)))
+                else:
+                    p = np.ascontiguousarray(p, np.int64)
+                    check(lib().scranb200_mat_append_columns(b, len(p) - 1, ptr(p), ptr(i), ptr(v)))
+            h = C.c_void_p()
+            check(lib().scranb200_mat_finish(b, C.byref(h)))
+        except Exception:
+            lib().scranb200_mat_abort(b)
+            raise
+        self.handle = h
+        self.shape = (int(nrow), int(ncol))
+        return self
+
+    @classmethod
     def wrap_device(cls, ctx, nrow, ncol, nnz, d_p, d_i, d_x):
         self = cls.__new__(cls)
         self.ctx = ctx
@@ -393,6 +427,22 @@ def score_markers(x, groups, block=None, pairings=None, lfc=0.0, full_stats=Fals
         res[g] = cols
     if own:
         plan.free()
+    return res
+
+
+def summary_marker_stats(x, groups, block=None):
+    """summaryMarkerStats(x, groups) (R/summaryMarkerStats.R:62-95): OrderedDict group -> OrderedDict with
+    self.average, other.average, self.detected, other.detected, from the blocked statistics on the device."""
+    m = _as_matrix(x)
+    if len(groups) != m.shape[1]:
+        raise ValueError("length of 'groups' does not equal 'ncol(x)'")
+    plan = ScorePlan(groups, block, None, 0.0, ctx=m.ctx)
+    out = np.zeros((max(1, plan.K), 4, m.shape[0]), np.float64)
+    check(lib().scranb200_summary_marker_stats(m.ctx.handle, m.handle, plan.handle, ptr(out)))
+    res = OrderedDict()
+    for k in range(plan.K):
+        res[plan.universe[plan.out_groups[k]]] = OrderedDict((name, out[k, c]) for c, name in enumerate(COLUMNS[:4]))
+    plan.free()
     return res
 
 

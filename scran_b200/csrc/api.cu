@@ -139,6 +139,14 @@ __global__ void __launch_bounds__(1024) scan_i64(const int64_t* counts, int64_t 
     if (t == 1023) out[n] = part[1023];
 }
 
+// p_out[k] = base + p_in[k], k < n: a chunk's own column pointers (starting at 0) moved to their place in the
+// whole matrix. PT = int64_t or int32_t (R's own @p).
+template <typename PT>
+__global__ void offset_colptr(const PT* __restrict__ p_in, int64_t n, int64_t base, int64_t* __restrict__ p_out) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) p_out[t] = base + (int64_t)p_in[t];
+}
+
 scranb200_mat* new_mat(scranb200_ctx* ctx, int64_t nrow, int64_t ncol) {
     if (nrow < 0 || ncol < 0 || nrow > INT32_MAX || ncol > INT32_MAX - 1) throw Error("matrix dimensions out of range");
     scranb200_mat* m = new scranb200_mat();
@@ -290,7 +298,74 @@ __global__ void __launch_bounds__(256) shift_means(double* mean, int64_t n, doub
 }  // namespace
 }  // namespace sb
 
+// A matrix being assembled from column chunks (scranb200_mat_begin / _append_columns / _finish).
+struct scranb200_builder {
+    scranb200_ctx* ctx = nullptr;
+    scranb200_mat* mat = nullptr;  // owns the device arrays while they grow
+    int64_t ncol_done = 0, nnz_done = 0;
+    size_t cap = 0;                // entries the value / index arrays hold
+};
+
 using namespace sb;
+
+namespace {
+
+// Grows the builder's index / value arrays to hold `need` entries, keeping what is there.
+void builder_reserve(scranb200_builder* b, size_t need) {
+    if (need <= b->cap) return;
+    if (need > 4294967295ull) throw Error("matrix has more than 2^32-1 stored entries; upload it in row blocks");
+    scranb200_ctx* ctx = b->ctx;
+    size_t cap = std::max<size_t>(need, b->cap + b->cap / 2);
+    cap = std::min<size_t>(cap, 4294967295ull);
+    scranb200_mat* m = b->mat;
+    size_t bytes_i = 0, bytes_x = 0;
+    int32_t* ni = dev_alloc<int32_t>(ctx, cap, bytes_i);
+    double* nx = nullptr;
+    try {
+        nx = dev_alloc<double>(ctx, cap, bytes_x);
+    } catch (...) {
+        cudaFree(ni);
+        throw;
+    }
+    if (b->nnz_done > 0) {
+        SB_CUDA(cudaMemcpyAsync(ni, m->d_i, (size_t)b->nnz_done * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        SB_CUDA(cudaMemcpyAsync(nx, m->d_x, (size_t)b->nnz_done * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    if (m->d_i) cudaFree(m->d_i);
+    if (m->d_x) cudaFree(m->d_x);
+    m->d_i = ni;
+    m->d_x = nx;
+    m->bytes_i = bytes_i;
+    m->bytes_x = bytes_x;
+    b->cap = cap;
+}
+
+template <typename PT>
+void builder_append(scranb200_builder* b, int64_t ncol_chunk, const PT* p, const int32_t* i, const double* x) {
+    if (!b || !b->mat) throw Error("null or finished matrix builder");
+    scranb200_ctx* ctx = b->ctx;
+    ctx_guard(ctx);
+    scranb200_mat* m = b->mat;
+    if (ncol_chunk < 0 || b->ncol_done + ncol_chunk > m->ncol) throw Error("more columns appended than the matrix was begun with");
+    if (ncol_chunk == 0) return;
+    const int64_t nnz_chunk = validate_colptr(p, m->nrow, ncol_chunk);
+    builder_reserve(b, (size_t)(b->nnz_done + nnz_chunk));
+    // the chunk's column pointers, moved to their place; entry ncol_total is written by _finish
+    ctx->io_a.reserve((size_t)(ncol_chunk + 1) * sizeof(PT));
+    SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, p, (size_t)ncol_chunk * sizeof(PT), cudaMemcpyHostToDevice, ctx->stream));
+    SB_LAUNCH(ctx, offset_colptr<PT>, (unsigned)ceil_div(ncol_chunk, 256), 256, 0, ctx->io_a.as<PT>(), ncol_chunk, b->nnz_done,
+              m->d_p + b->ncol_done);
+    if (nnz_chunk > 0) {
+        SB_CUDA(cudaMemcpyAsync(m->d_i + b->nnz_done, i, (size_t)nnz_chunk * 4, cudaMemcpyHostToDevice, ctx->stream));
+        SB_CUDA(cudaMemcpyAsync(m->d_x + b->nnz_done, x, (size_t)nnz_chunk * 8, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));  // the caller's buffers are free again when this returns
+    b->ncol_done += ncol_chunk;
+    b->nnz_done += nnz_chunk;
+}
+
+}  // namespace
 
 #define API_BEGIN try {
 #define API_END                           \
@@ -421,6 +496,60 @@ int scranb200_upload_csc32(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const
     finish_upload(ctx, m, i, x);
     *out = guard.release();
     API_END
+}
+
+int scranb200_mat_begin(scranb200_ctx* ctx, int64_t nrow, int64_t ncol_total, int64_t nnz_hint, scranb200_builder** out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    if (nnz_hint < 0) nnz_hint = 0;
+    MatGuard guard(new_mat(ctx, nrow, ncol_total));
+    scranb200_mat* m = guard.m;
+    m->d_p = dev_alloc<int64_t>(ctx, ncol_total + 1, m->bytes_p);
+    scranb200_builder* b = new scranb200_builder();
+    b->ctx = ctx;
+    b->mat = m;
+    try {
+        builder_reserve(b, (size_t)std::max<int64_t>(nnz_hint, 1));
+    } catch (...) {
+        delete b;
+        throw;
+    }
+    guard.release();
+    *out = b;
+    API_END
+}
+
+int scranb200_mat_append_columns(scranb200_builder* b, int64_t ncol_chunk, const int64_t* p, const int32_t* i, const double* x) {
+    API_BEGIN
+    builder_append<int64_t>(b, ncol_chunk, p, i, x);
+    API_END
+}
+
+int scranb200_mat_append_columns32(scranb200_builder* b, int64_t ncol_chunk, const int32_t* p, const int32_t* i, const double* x) {
+    API_BEGIN
+    builder_append<int32_t>(b, ncol_chunk, p, i, x);
+    API_END
+}
+
+int scranb200_mat_finish(scranb200_builder* b, scranb200_mat** out) {
+    API_BEGIN
+    if (!b || !b->mat) throw Error("null or finished matrix builder");
+    ctx_guard(b->ctx);
+    scranb200_mat* m = b->mat;
+    if (b->ncol_done != m->ncol) throw Error("fewer columns appended than the matrix was begun with");
+    m->nnz = b->nnz_done;
+    SB_CUDA(cudaMemcpyAsync(m->d_p + m->ncol, &m->nnz, 8, cudaMemcpyHostToDevice, b->ctx->stream));
+    SB_CUDA(cudaStreamSynchronize(b->ctx->stream));
+    b->mat = nullptr;
+    delete b;
+    *out = m;
+    API_END
+}
+
+void scranb200_mat_abort(scranb200_builder* b) {
+    if (!b) return;
+    if (b->mat) scranb200_mat_free(b->mat);
+    delete b;
 }
 
 int scranb200_upload_dense(scranb200_ctx* ctx, int64_t nrow, int64_t ncol, const double* x, scranb200_mat** out) {
@@ -836,6 +965,34 @@ int scranb200_score_markers(scranb200_ctx* ctx, const scranb200_mat* mat, const 
             }
         }
     }
+    API_END
+}
+
+int scranb200_summary_marker_stats(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan, double* out) {
+    API_BEGIN
+    ctx_guard(ctx);
+    mat_guard(ctx, mat);
+    if (mat->ncol != plan->ncells) throw Error("plan was built for a different number of cells");
+    if (plan->ctx != ctx) throw Error("plan was built without or for another context");
+    const int64_t ngenes = mat->nrow;
+    if (ngenes == 0 || plan->K == 0) return 0;
+    ctx->out.reserve((size_t)plan->K * SCRANB200_NCOLS * ngenes * 8);
+    double* d_out = ctx->out.as<double>();
+    // only the combinations' statistics are needed: a layout without pairs (no sort, no count)
+    PairLayout L;
+    build_layout(plan->comb_id.data(), plan->ncells, plan->C, nullptr, nullptr, 0, ctx->sm_count * 4, L);
+    upload_layout(ctx, L, ctx->layout_i32);
+    phase_begin(ctx);
+    run_pairs(ctx, mat, L, ctx->layout_i32, true, 0.0, false, false);
+    run_effects(ctx, *plan, (int)ngenes, ngenes, 0, ctx->mean.as<double>(), ctx->var.as<double>(), ctx->ndet.as<double>(), nullptr,
+                nullptr, d_out);
+    phase_mark(ctx, PH_EFFECTS);
+    for (int k = 0; k < plan->K; ++k) {
+        SB_CUDA(cudaMemcpyAsync(out + (size_t)k * 4 * ngenes, d_out + (size_t)k * SCRANB200_NCOLS * ngenes, (size_t)4 * ngenes * 8,
+                                cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    phase_collect(ctx);
     API_END
 }
 

@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(256) k4_selfother(SelfParams P) {
 void run_effects(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int64_t ld, int64_t row0, const double* d_mean,
                  const double* d_var, const double* d_ndet, const double* d_u, double* d_eff, double* d_out) {
     if (ngenes == 0) return;
-    if (P.Q > 0) {
+    if (P.Q > 0 && d_u != nullptr && d_eff != nullptr) {  // (null: only the self. / other. columns are wanted)
         EffParams ep;
         ep.ngenes = ngenes;
         ep.Q = P.Q;
