@@ -35,6 +35,8 @@ WORKLOADS = {
     "config1": dict(ngenes=10000, ncells=3000, G=10, B=1, density=0.63, seed=1001),
     "config2": dict(ngenes=33538, ncells=100000, G=20, B=4, density=0.07, seed=1002),
     "config3": dict(ngenes=33538, ncells=1300000, G=50, B=8, density=0.07, seed=1003),
+    # config 4: pairwiseTTests(lfc = 0.5) + modelGeneVar's blocked statistics on the 1.3M-cell matrix of config 3
+    "config4": dict(ngenes=33538, ncells=1300000, G=50, B=8, density=0.07, seed=1003),
     "config5": dict(ngenes=20000, ncells=500000, G=200, B=1, density=0.07, seed=1005),
     "tiny": dict(ngenes=2000, ncells=20000, G=8, B=2, density=0.07, seed=1999),
     # one eighth of config 3's genes over all its cells: the per-GPU share of the 8-GPU run, for profiling
@@ -191,6 +193,193 @@ def run_reference(args, w):
     print(json.dumps(line))
 
 
+def run_config4(args, w):
+    """BASELINE.json config 4: compute_blocked_stats_none on the 1.3M-cell matrix with the 400 block-major ids of
+    pairwiseTTests (R/pairwiseTTests.R:242) and with modelGeneVar's 8 block ids (R/modelGeneVar.R:148-157), plus the
+    t-test layer with lfc = 0.5. Metric: mean / variance cells per second = ngenes x nblocks /
+    device time of the blocked statistics (transpose + stats), with their achieved GB/s against
+    nnz 12 + ncells 4 + 2 ngenes nblocks 8 bytes. N > 1: genes sharded, no exchange (gather by rows only)."""
+    import ctypes as C
+
+    import torch
+
+    import scran_b200
+    from scran_b200._lib import check, lib, ptr
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L = lib()
+    groups, block = labels_for(w)
+    G, B, ng, nc = w["G"], w["B"], w["ngenes"], w["ncells"]
+    ids400 = np.ascontiguousarray(groups + block * G, np.int32)
+    ids8 = np.ascontiguousarray(block, np.int32)
+    starts = shard_starts(w, world)
+    g0, g1 = int(starts[rank]), int(starts[rank + 1])
+    nrow = g1 - g0
+    if args.impl == "reference":
+        if rank == 0:
+            run_reference_config4(args, w, groups, ids400, ids8)
+        return
+    ctx = scran_b200.Context(local)
+    mat = scran_b200.DeviceMatrix.synthetic(ctx, ng, g0, g1, nc, groups, G, w["density"], w["seed"])
+    nnz_t = torch.tensor([mat.nnz], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(nnz_t)
+    nnz = int(nnz_t.item())
+    out400 = [torch.empty((G * B, max(1, nrow)), dtype=torch.float64).pin_memory() for _ in range(2)]
+    out8 = [torch.empty((B, max(1, nrow)), dtype=torch.float64).pin_memory() for _ in range(2)]
+    npair = G * (G - 1)
+    outt = [torch.empty((npair, max(1, nrow)), dtype=torch.float64).pin_memory() for _ in range(3)]
+    gcodes = np.ascontiguousarray(groups, np.int32)
+
+    def step():
+        ms = {}
+        check(L.scranb200_blocked_stats(ctx.handle, mat.handle, ptr(ids400), G * B, ptr(out400[0]), ptr(out400[1]), None))
+        ms["stats400"] = ctx.last_timing()["total"]
+        check(L.scranb200_blocked_stats(ctx.handle, mat.handle, ptr(ids8), B, ptr(out8[0]), ptr(out8[1]), None))
+        ms["stats8"] = ctx.last_timing()["total"]
+        t0 = time.perf_counter()
+        check(L.scranb200_pairwise_t_tests(ctx.handle, mat.handle, ptr(gcodes), G, ptr(ids8), B, 0.5, 0, 0, ptr(outt[0]),
+                                           ptr(outt[1]), ptr(outt[2])))
+        ms["ttests_call"] = (time.perf_counter() - t0) * 1e3
+        return ms
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(max(args.warmup, 1)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launches
+    acc = {}
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for k, v in step().items():
+            acc[k] = acc.get(k, 0.0) + v / args.steps
+    barrier()
+    wall = (time.perf_counter() - t0) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    launches = ctx.launches - launches0
+    dev = torch.tensor([acc["stats400"] + acc["stats8"], acc["stats400"], acc["stats8"], acc["ttests_call"], wall * 1e3],
+                       dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(dev, op=dist.ReduceOp.MAX)
+    ms_stats, ms400, ms8, ms_tt, ms_wall = [float(v) for v in dev.tolist()]
+    # end to end: upload from pinned host memory + the two blocked-statistics calls
+    p_h, i_h, x_h = mat.download()
+    mat.free()
+    pin = [torch.from_numpy(a).pin_memory() for a in (p_h, i_h, x_h)]
+    del p_h, i_h, x_h
+
+    def e2e_step():
+        h = C.c_void_p()
+        check(L.scranb200_upload_csc(ctx.handle, nrow, nc, ptr(pin[0]), ptr(pin[1]), ptr(pin[2]), C.byref(h)))
+        try:
+            check(L.scranb200_blocked_stats(ctx.handle, h, ptr(ids400), G * B, ptr(out400[0]), ptr(out400[1]), None))
+            check(L.scranb200_blocked_stats(ctx.handle, h, ptr(ids8), B, ptr(out8[0]), ptr(out8[1]), None))
+        finally:
+            L.scranb200_mat_free(h)
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_step()
+    barrier()
+    t_e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+    if rank != 0:
+        dist.destroy_process_group()
+        return
+    peak, peak_src = measured_peak()
+    cells = ng * (G * B + B)
+    bytes400 = nnz * 12 + nc * 4 + 2 * ng * G * B * 8
+    bytes8 = nnz * 12 + nc * 4 + 2 * ng * B * 8
+    gbs = (bytes400 + bytes8) / world / (ms_stats * 1e-3) / 1e9
+    cpu = None
+    if not args.no_cpu and world == 1:
+        cpu = cpu_sample_config4(w, groups, ids400, ids8, ctx, args.cpu_genes or 512, 1)
+    line = {
+        "metric": "compute_blocked_stats mean/variance cells/sec (1.3M cells; 400 + 8 blocks)", "value": cells / (ms_stats * 1e-3),
+        "unit": "gene·block cells/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_stats,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "config4", "ngenes": ng, "ncells": nc, "G": G, "B": B, "density": w["density"], "nnz": nnz,
+                   "blocks": [G * B, B], "t_tests": "lfc=0.5, direction any, %d ordered pairs" % npair,
+                   "sharding": "genes x%d, ranges of equal expected nnz" % world,
+                   "l2": "inputs (%.1f GB) larger than L2" % (nnz * 12 / 1e9)},
+        "e2e": {"value": cells / float(t_e.item()), "unit": "gene·block cells/s", "h2d_bytes_per_step": int(nnz * 12 + (nc + 1) * 8),
+                "d2h_bytes_per_step": int(2 * ng * (G * B + B) * 8), "ms_per_step": float(t_e.item()) * 1e3, "host_memory": "pinned",
+                "call": "scranb200_upload_csc + 2 x scranb200_blocked_stats (host buffers)"},
+        "gpu_launches": int(launches), "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "transpose + stats (both calls)", "achieved": round(gbs, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(gbs / peak, 4), "traffic": None, "peak_source": peak_src},
+        "kernels": {"stats_400_blocks": {"ms": round(ms400, 3), "gbs": round(bytes400 / world / (ms400 * 1e-3) / 1e9, 1)},
+                    "stats_8_blocks": {"ms": round(ms8, 3), "gbs": round(bytes8 / world / (ms8 * 1e-3) / 1e9, 1)},
+                    "pairwise_t_tests_call": {"ms": round(ms_tt, 3),
+                                              "note": "host-buffer call: blocked statistics + t-test layer + log BH on the device, "
+                                                      "three [%d x ngenes] result arrays copied to the host" % npair}},
+        "wall_ms_per_step_all_three_calls": round(ms_wall, 2), "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_sample_config4(w, groups, ids400, ids8, ctx, nsample, threads):
+    """The reference's compute_blocked_stats_none (object code when oracle/_ref is there) on `nsample` genes x all cells."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    import scipy.sparse as sp
+
+    import scran_b200
+    from oracle import native
+    lib = native.load("best")
+    m = scran_b200.DeviceMatrix.synthetic(ctx, w["ngenes"], 1000, 1000 + nsample, w["ncells"], groups, w["G"], w["density"], w["seed"])
+    p, i, x = m.download()
+    m.free()
+    rows = sp.csc_matrix((x, i, p), shape=(nsample, w["ncells"])).tocsr()
+    pieces = [rows[idx].tocsc() for idx in np.array_split(np.arange(nsample), threads) if len(idx)]
+
+    def work(piece):
+        lib.blocked_stats(piece, ids400, w["G"] * w["B"])
+        lib.blocked_stats(piece, ids8, w["B"])
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(work, pieces))
+    dt = time.perf_counter() - t0
+    cells = nsample * (w["G"] * w["B"] + w["B"])
+    return {"value": cells / dt, "unit": "gene·block cells/s", "cores": threads, "kind": "reference" if lib.kind == "ref" else "port",
+            "sample": "%d genes x all %d cells, compute_blocked_stats_none with 400 and with 8 blocks, %.1f s" % (nsample, w["ncells"], dt)}
+
+
+def run_reference_config4(args, w, groups, ids400, ids8):
+    import scran_b200
+    ctx = scran_b200.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    threads = os.cpu_count() or 1
+    vals = []
+    for s in range(args.warmup + args.steps):
+        r = cpu_sample_config4(w, groups, ids400, ids8, ctx, 256 * threads, threads)
+        if s >= args.warmup:
+            vals.append(r)
+    value = float(np.mean([r["value"] for r in vals]))
+    print(json.dumps({
+        "impl": "reference", "metric": "compute_blocked_stats mean/variance cells/sec (1.3M cells; 400 + 8 blocks)", "value": value,
+        "unit": "gene·block cells/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "config4", **{k: w[k] for k in ("ngenes", "ncells", "G", "B", "density")}},
+        "cpu_baseline": {**vals[-1], "value": value},
+        "e2e": {"value": value, "unit": "gene·block cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
 def shard_starts(w, world):
     """Gene ranges of equal expected nnz (housekeeping genes are ten times heavier
     than the average, so equal gene counts leave the ranks unbalanced): int64[world + 1]."""
@@ -254,6 +443,9 @@ def main():
     w = dict(WORKLOADS[args.workload])
     args.warmup = max(args.warmup, 0)
 
+    if args.workload == "config4":
+        run_config4(args, w)
+        return
     if args.impl == "reference":
         run_reference(args, w)
         return
@@ -408,13 +600,17 @@ def main():
         kernels[k] = {"ms": round(ms, 4), "alg_bytes": int(pb[k] / world),
                       "gbs": None if gbs is None else round(gbs, 1), "frac": None if gbs is None else round(gbs / peak, 4)}
     # DRAM bytes of the dominant phase per step, from the committed ncu capture of this very workload
-    # (profiles/r01_dram_<workload>_n<N>.json); null when no capture exists for it
+    # (profiles/r0X_dram_<workload>_n<N>.json; re-captured whenever that kernel changes); null when there is none
     traffic = traffic_src = None
     try:
-        cap = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
-                                          "r01_dram_%s_n%d.json" % (args.workload, world))))
-        traffic = int(cap["phase_bytes"][dom])
-        traffic_src = cap["source"]
+        prof = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles")
+        for rnd in ("r02", "r01"):  # the newest capture of this workload
+            path = os.path.join(prof, "%s_dram_%s_n%d.json" % (rnd, args.workload, world))
+            if os.path.exists(path):
+                cap = json.load(open(path))
+                traffic = int(cap["phase_bytes"][dom])
+                traffic_src = cap["source"]
+                break
     except (OSError, KeyError, ValueError):
         pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",

@@ -16,6 +16,7 @@
 #include <limits>
 #include <memory>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 #ifndef NA_INTEGER
@@ -42,11 +43,28 @@ struct MatrixView {
 
 namespace Rcpp {
 
+class IntegerVector;
+class NumericVector;
+
+// What x.slot("p") yields: convertible to the vector type the caller asks for.
+struct SlotProxy {
+    const oracle_stub::MatrixView* mat;
+    const char* name;
+    operator IntegerVector() const;
+    operator NumericVector() const;
+};
+
 class RObject {
 public:
     RObject() {}
     explicit RObject(const oracle_stub::MatrixView* m) : mat(m) {}
     const oracle_stub::MatrixView* mat = nullptr;
+    std::shared_ptr<std::vector<int>> ivec;  // an integer vector held as a generic object (glue: block codes)
+    // the part of the S4 / SEXP surface that glue/scran_b200_glue.cpp uses: a sparse view is a "dgCMatrix"
+    bool isNULL() const { return mat == nullptr && !ivec; }
+    bool isS4() const { return mat != nullptr && mat->sparse; }
+    bool inherits(const char*) const { return mat != nullptr && mat->sparse; }
+    SlotProxy slot(const char* name) const { return SlotProxy{mat, name}; }
 };
 
 template <typename T>
@@ -77,6 +95,12 @@ public:
     };
     NumericMatrix() : nr(0), nc(0), store(std::make_shared<std::vector<double>>()) {}
     NumericMatrix(size_t r, size_t c) : nr(r), nc(c), store(std::make_shared<std::vector<double>>(r * c, 0.0)) {}
+    explicit NumericMatrix(const RObject& x) : nr(0), nc(0), store(std::make_shared<std::vector<double>>()) {
+        if (!x.mat || x.mat->sparse) throw std::runtime_error("stub: not an ordinary matrix");
+        nr = x.mat->nrow;
+        nc = x.mat->ncol;
+        store = std::make_shared<std::vector<double>>(x.mat->x, x.mat->x + nr * nc);
+    }
     double* begin() { return store->data(); }
     double* end() { return store->data() + store->size(); }
     Column column(size_t j) { return Column{store->data() + j * nr, store->data() + (j + 1) * nr}; }
@@ -87,8 +111,6 @@ public:
 };
 
 class List;
-
-class IntegerVector;
 
 // One slot of a List: may hold an integer vector, a numeric matrix or a nested list.
 struct ListSlot {
@@ -101,6 +123,7 @@ struct ListSlot {
         return *this;
     }
     ListSlot& operator=(const List& l);
+    ListSlot& operator=(const NumericVector& v);
 };
 
 class IntegerVector : public StubVector<int> {
@@ -112,6 +135,10 @@ public:
     IntegerVector(const ListSlot& s) {
         if (!s.ivec) throw std::runtime_error("stub: list slot holds no integer vector");
         store = s.ivec;
+    }
+    explicit IntegerVector(const RObject& x) {
+        if (!x.ivec) throw std::runtime_error("stub: object holds no integer vector");
+        store = x.ivec;
     }
 };
 
@@ -152,6 +179,36 @@ public:
 inline ListSlot& ListSlot::operator=(const List& l) {
     sub = std::make_shared<List>(l);
     return *this;
+}
+inline ListSlot& ListSlot::operator=(const NumericVector& v) {
+    nvec = v.store;
+    return *this;
+}
+
+// dgCMatrix slots of a sparse view: @p (converted to R's int), @i, @Dim as integer vectors, @x as numeric.
+inline SlotProxy::operator IntegerVector() const {
+    if (!mat) throw std::runtime_error("stub: no matrix behind the slot");
+    const std::string n(name);
+    if (n == "Dim") {
+        IntegerVector d(2);
+        d[0] = (int)mat->nrow;
+        d[1] = (int)mat->ncol;
+        return d;
+    }
+    if (n == "p") {
+        IntegerVector p(mat->ncol + 1);
+        for (size_t k = 0; k <= mat->ncol; ++k) {
+            if (mat->p[k] > INT_MAX) throw std::runtime_error("stub: a dgCMatrix holds at most 2^31 - 1 entries");
+            p[k] = (int)mat->p[k];
+        }
+        return p;
+    }
+    if (n == "i") return IntegerVector(mat->i, mat->i + mat->p[mat->ncol]);
+    throw std::runtime_error("stub: unknown integer slot");
+}
+inline SlotProxy::operator NumericVector() const {
+    if (!mat || std::string(name) != "x") throw std::runtime_error("stub: unknown numeric slot");
+    return NumericVector(mat->x, mat->x + mat->p[mat->ncol]);
 }
 
 }  // namespace Rcpp

@@ -200,11 +200,11 @@ __global__ void check_colptr(const int64_t* __restrict__ p, int64_t nrow, int64_
 void finish_upload(scranb200_ctx* ctx, scranb200_mat* m, const int32_t* i, const double* x) {
     m->d_i = dev_alloc<int32_t>(ctx, m->nnz, m->bytes_i);
     m->d_x = dev_alloc<double>(ctx, m->nnz, m->bytes_x);
-    if (m->nnz > 0) {
-        SB_CUDA(cudaMemcpyAsync(m->d_i, i, (size_t)m->nnz * 4, cudaMemcpyHostToDevice, ctx->stream));
-        SB_CUDA(cudaMemcpyAsync(m->d_x, x, (size_t)m->nnz * 8, cudaMemcpyHostToDevice, ctx->stream));
-    }
     SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (m->nnz > 0) {
+        h2d_copy(ctx, m->d_i, i, (size_t)m->nnz * 4);
+        h2d_copy(ctx, m->d_x, x, (size_t)m->nnz * 8);
+    }
 }
 
 // Cell -> group from the reference's list-of-index-vectors form (src/overlap_exprs.cpp:13-32).
@@ -356,11 +356,11 @@ void builder_append(scranb200_builder* b, int64_t ncol_chunk, const PT* p, const
     SB_CUDA(cudaMemcpyAsync(ctx->io_a.p, p, (size_t)ncol_chunk * sizeof(PT), cudaMemcpyHostToDevice, ctx->stream));
     SB_LAUNCH(ctx, offset_colptr<PT>, (unsigned)ceil_div(ncol_chunk, 256), 256, 0, ctx->io_a.as<PT>(), ncol_chunk, b->nnz_done,
               m->d_p + b->ncol_done);
-    if (nnz_chunk > 0) {
-        SB_CUDA(cudaMemcpyAsync(m->d_i + b->nnz_done, i, (size_t)nnz_chunk * 4, cudaMemcpyHostToDevice, ctx->stream));
-        SB_CUDA(cudaMemcpyAsync(m->d_x + b->nnz_done, x, (size_t)nnz_chunk * 8, cudaMemcpyHostToDevice, ctx->stream));
+    SB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (nnz_chunk > 0) {  // (synchronous: the caller's buffers are free again when this returns)
+        h2d_copy(ctx, m->d_i + b->nnz_done, i, (size_t)nnz_chunk * 4);
+        h2d_copy(ctx, m->d_x + b->nnz_done, x, (size_t)nnz_chunk * 8);
     }
-    SB_CUDA(cudaStreamSynchronize(ctx->stream));  // the caller's buffers are free again when this returns
     b->ncol_done += ncol_chunk;
     b->nnz_done += nnz_chunk;
 }
@@ -423,6 +423,7 @@ void scranb200_ctx_destroy(scranb200_ctx* ctx) {
                               &ctx->io_b, &ctx->io_c, &ctx->grp_avg, &ctx->logit, &ctx->jobs, &ctx->split, &ctx->vmin, &ctx->vmax,
                               &ctx->xchg_part, &ctx->xchg_recv, &ctx->xchg_cols};
         sb::comm_release(ctx);
+        sb::stage_release(ctx);
         for (sb::DevBuf* b : bufs) b->release();
         for (auto& sp : ctx->spare) cudaFree(sp.p);
         ctx->spare.clear();

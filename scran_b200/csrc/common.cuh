@@ -94,6 +94,10 @@ struct scranb200_ctx {
         size_t bytes;
     };
     std::vector<Spare> spare;
+    // staging for host -> device copies from pageable memory (hostcopy.cu): pinned buffers and one stream per worker
+    void* stage_pinned = nullptr;
+    cudaStream_t stage_streams[8] = {nullptr};
+    int stage_workers = 0;
     // live matrices and plans of this context: scranb200_ctx_destroy orphans them (frees their device
     // memory, clears their back-pointer), so that a later mat_free / plan_destroy only deletes the handle
     std::vector<scranb200_mat*> live_mats;
@@ -113,6 +117,8 @@ struct scranb200_mat {
 namespace sb {
 
 void set_last_error(const std::string& m);
+void h2d_copy(scranb200_ctx* ctx, void* dst, const void* src, size_t bytes);  // hostcopy.cu: synchronous, pinned or pageable source
+void stage_release(scranb200_ctx* ctx);
 void ctx_guard(scranb200_ctx* ctx);  // device current + fork check
 
 // Launch with accounting and an immediate launch-error check.

@@ -35,8 +35,6 @@ __device__ inline void dd_add(DD& s, double x) {  // s += x, error-free (Knuth t
     s.lo += err;
 }
 
-constexpr int SUM_WARPS = 8;
-
 struct SumParams {
     int ngenes, K, Q, maxr;
     int64_t ld, row0;
@@ -45,116 +43,168 @@ struct SumParams {
     double* out;  // [K][19][ld]
 };
 
+// One warp per (tile of 32 consecutive genes, output table): lane = gene, so every load of a comparison
+// column and every store of a result column is one coalesced 256-byte access. Nothing but a few counters is
+// kept per gene: the comparison values are streamed (from L2 after the first pass) once for the mean / min /
+// max and then a few more times for the median, which is found by selection through histograms: 32
+// equal-width bins over the range that still holds the wanted rank, the bin with that rank either gathered
+// (up to SUM_SLOTS values, sorted by insertion) or, if it holds more, narrowed to its exact [min, max] and
+// binned again. Equal values end the search at once. A table of hundreds of comparisons costs the same
+// 6 KB of shared memory a warp as one of ten, so the SMs stay full.
+constexpr int SUM_WARPS = 8;
+constexpr int SUM_BINS = 32;
+constexpr int SUM_SLOTS = 16;
+
 __global__ void __launch_bounds__(SUM_WARPS * 32) k5_summaries(SumParams P) {
-    extern __shared__ double s_vals[];  // [SUM_WARPS][maxr]
+    __shared__ uint16_t s_hist[SUM_WARPS][SUM_BINS][32];
+    __shared__ double s_slot[SUM_WARPS][SUM_SLOTS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t ntiles = (P.ngenes + 31) / 32;
     const int64_t item = (int64_t)blockIdx.x * SUM_WARPS + warp;
-    if (item >= (int64_t)P.ngenes * P.K) return;
-    const int g = (int)(item % P.ngenes), k = (int)(item / P.ngenes);
-    double* v = s_vals + (size_t)warp * P.maxr;
+    if (item >= ntiles * P.K) return;
+    const int k = (int)(item / ntiles);
+    const int g = (int)(item % ntiles) * 32 + lane;
+    const bool live = g < P.ngenes;
     const int j0 = P.right_ptr[k], nr = P.right_ptr[k + 1] - j0;
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
     const double inf = __longlong_as_double(0x7ff0000000000000ll);
 
     for (int e = 0; e < 3; ++e) {
-        DD sum = {0.0, 0.0};
-        double mn = inf, mx = -inf;
-        int cnt = 0;
-        for (int j = lane; j < nr; j += 32) {
-            double x = nan;
-            const int qd = P.q_direct[j0 + j], qf = P.q_flipped[j0 + j];
-            if (qd >= 0) {
-                x = P.eff[((size_t)e * P.Q + qd) * P.ld + P.row0 + g];
-            } else if (qf >= 0) {
-                const double y = P.eff[((size_t)e * P.Q + qf) * P.ld + P.row0 + g];
-                x = e == 1 ? 1.0 - y : -y;
+        const double* col = P.eff + (size_t)e * P.Q * P.ld + P.row0 + (live ? g : 0);
+        // f(x) for every comparison value of this lane's gene (NaN = NA), four loads in flight
+        auto for_each_value = [&](auto&& f) {
+            for (int j = 0; j < nr; j += 4) {
+                double x[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    x[u] = nan;
+                    if (j + u < nr && live) {
+                        const int qd = P.q_direct[j0 + j + u], qf = P.q_flipped[j0 + j + u];
+                        if (qd >= 0) {
+                            x[u] = col[(size_t)qd * P.ld];
+                        } else if (qf >= 0) {
+                            const double y = col[(size_t)qf * P.ld];
+                            x[u] = e == 1 ? 1.0 - y : -y;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) f(x[u]);
             }
-            v[j] = x;
+        };
+        DD sum = {0.0, 0.0};
+        double mn = inf, mx = -inf, fmn = inf, fmx = -inf;  // over all values / over the finite ones
+        int cnt = 0, n_ninf = 0, n_pinf = 0;
+        for_each_value([&](double x) {
             if (!isnan(x)) {
                 dd_add(sum, x);
                 mn = fmin(mn, x);
                 mx = fmax(mx, x);
                 ++cnt;
-            }
-        }
-        __syncwarp();
-        // Warp reduction: the partial sums are combined pairwise in double-double.
-        for (int o = 16; o > 0; o >>= 1) {
-            const double oh = __shfl_down_sync(0xffffffffu, sum.hi, o);
-            const double ol = __shfl_down_sync(0xffffffffu, sum.lo, o);
-            dd_add(sum, oh);
-            if (!isinf(sum.hi) && !isnan(sum.hi)) sum.lo += ol;
-            mn = fmin(mn, __shfl_down_sync(0xffffffffu, mn, o));
-            mx = fmax(mx, __shfl_down_sync(0xffffffffu, mx, o));
-            cnt += __shfl_down_sync(0xffffffffu, cnt, o);
-        }
-        cnt = __shfl_sync(0xffffffffu, cnt, 0);
-        // Median by rank counting: entry i has rank #(x_j < x_i) + #(x_j == x_i, j < i).
-        double med_lo = nan, med_hi = nan;
-        if (cnt > 0 && nr > 64) {
-            // Many comparisons: rank counting is quadratic. Bisect on the order-preserving key instead:
-            // the smallest key with at least r_lo + 1 values at or below it is the lower median.
-            const int r_lo = (cnt - 1) / 2, r_hi = cnt / 2;
-            mn = __shfl_sync(0xffffffffu, mn, 0);
-            mx = __shfl_sync(0xffffffffu, mx, 0);
-            unsigned long long* kv = reinterpret_cast<unsigned long long*>(v);
-            for (int j = lane; j < nr; j += 32) {
-                const double x = v[j];
-                kv[j] = isnan(x) ? ~0ull : key_of(x);  // NaN: above every key that is tried
-            }
-            __syncwarp();
-            unsigned long long lo = key_of(mn), hi = key_of(mx);
-            while (lo < hi) {
-                const unsigned long long mid = lo + ((hi - lo) >> 1);
-                int c = 0;
-                for (int j = lane; j < nr; j += 32) c += kv[j] <= mid ? 1 : 0;
-                c = __reduce_add_sync(0xffffffffu, c);
-                if (c >= r_lo + 1) hi = mid; else lo = mid + 1;
-            }
-            int c_le = 0;
-            unsigned long long next = ~0ull;  // smallest key above the lower median
-            for (int j = lane; j < nr; j += 32) {
-                const unsigned long long kj = kv[j];
-                c_le += kj <= lo ? 1 : 0;
-                if (kj > lo && kj < next) next = kj;
-            }
-            c_le = __reduce_add_sync(0xffffffffu, c_le);
-            for (int o = 16; o > 0; o >>= 1) {
-                const unsigned long long a = __shfl_xor_sync(0xffffffffu, next, o);
-                next = a < next ? a : next;
-            }
-            med_lo = value_of(lo);
-            med_hi = c_le >= r_hi + 1 ? med_lo : value_of(next);
-        } else if (cnt > 0) {
-            const int r_lo = (cnt - 1) / 2, r_hi = cnt / 2;
-            for (int i = lane; i < nr; i += 32) {
-                const double xi = v[i];
-                if (isnan(xi)) continue;
-                int r = 0;
-                for (int j = 0; j < nr; ++j) {
-                    const double xj = v[j];
-                    r += (xj < xi) || (xj == xi && j < i);
+                if (isinf(x)) {
+                    if (x < 0.0) ++n_ninf; else ++n_pinf;
+                } else {
+                    fmn = fmin(fmn, x);
+                    fmx = fmax(fmx, x);
                 }
-                if (r == r_lo) med_lo = xi;
-                if (r == r_hi) med_hi = xi;
             }
-            // exactly one lane holds each of them
-            for (int o = 16; o > 0; o >>= 1) {
-                const double a = __shfl_down_sync(0xffffffffu, med_lo, o);
-                const double b = __shfl_down_sync(0xffffffffu, med_hi, o);
-                if (isnan(med_lo)) med_lo = a;
-                if (isnan(med_hi)) med_hi = b;
+        });
+        // ---- the values at sorted positions r_lo = (cnt - 1) / 2 and r_lo + 1 ----
+        double v_lo = nan, v_next = nan;
+        const int r_lo = (cnt - 1) / 2;
+        const int n_fin = cnt - n_ninf - n_pinf;
+        bool searching = false;
+        int target = 0;                    // rank among the finite values that are still candidates, counted from `below`
+        double lo = fmn, hi = fmx;         // the candidates are the finite values in [lo, hi]
+        double above = n_pinf > 0 ? inf : nan;  // the smallest value known to lie above the candidates
+        if (cnt > 0) {
+            if (r_lo < n_ninf) {
+                v_lo = -inf;
+                v_next = r_lo + 1 < n_ninf ? -inf : (n_fin > 0 ? fmn : (n_pinf > 0 ? inf : nan));
+            } else if (r_lo >= n_ninf + n_fin) {
+                v_lo = inf;
+                v_next = inf;
+            } else {
+                searching = true;
+                target = r_lo - n_ninf;
             }
         }
-        if (lane == 0) {
+        int ncand = n_fin;                 // candidates left
+        while (__any_sync(0xffffffffu, searching)) {
+            if (searching && lo == hi) {   // all candidates are one value
+                v_lo = lo;
+                v_next = target + 1 < ncand ? lo : above;
+                searching = false;
+            }
+            // bin = floor((x - lo) / width), on values scaled by 1/32 so that hi - lo cannot overflow
+            const double sc = 1.0 / (double)SUM_BINS;
+            const double width = (hi * sc - lo * sc) * sc;
+            const double inv = searching && width > 0.0 ? 1.0 / width : 0.0;
+            const bool by_inv = inv < inf;
+            auto bin_of = [&](double x) {
+                const double t = x * sc - lo * sc;
+                return min(SUM_BINS - 1, (int)(by_inv ? t * inv : t / width));
+            };
+#pragma unroll
+            for (int b = 0; b < SUM_BINS; ++b) s_hist[warp][b][lane] = 0;
+            for_each_value([&](double x) {
+                if (searching && !isnan(x) && x >= lo && x <= hi) ++s_hist[warp][bin_of(x)][lane];
+            });
+            int bstar = 0, before = 0, c = 0;
+            if (searching) {
+                for (bstar = 0; bstar < SUM_BINS; ++bstar) {
+                    c = s_hist[warp][bstar][lane];
+                    if (target < before + c) break;
+                    before += c;
+                }
+            }
+            // second pass: gather the bin (if it is small), or its exact range (if not); the smallest value above it
+            const bool gather = searching && c <= SUM_SLOTS;
+            int ns = 0;
+            double bmin = inf, bmax = -inf, up = above;
+            for_each_value([&](double x) {
+                if (searching && !isnan(x) && x >= lo && x <= hi) {
+                    const int b = bin_of(x);
+                    if (b == bstar) {
+                        bmin = fmin(bmin, x);
+                        bmax = fmax(bmax, x);
+                        if (gather) {  // insertion into the lane's sorted slots
+                            int i = ns - 1;
+                            while (i >= 0 && s_slot[warp][i][lane] > x) {
+                                s_slot[warp][i + 1][lane] = s_slot[warp][i][lane];
+                                --i;
+                            }
+                            s_slot[warp][i + 1][lane] = x;
+                            ++ns;
+                        }
+                    } else if (b > bstar) {
+                        up = isnan(up) ? x : fmin(up, x);
+                    }
+                }
+            });
+            if (searching) {
+                if (gather) {
+                    const int idx = target - before;
+                    v_lo = s_slot[warp][idx][lane];
+                    v_next = idx + 1 < ns ? s_slot[warp][idx + 1][lane] : up;
+                    searching = false;
+                } else {
+                    lo = bmin;
+                    hi = bmax;
+                    target -= before;
+                    ncand = c;
+                    above = up;
+                }
+            }
+        }
+        if (live) {
             double* base = P.out + ((size_t)k * SCRANB200_NCOLS + 4 + 5 * e) * P.ld + P.row0 + g;
             const double total = sum.hi + sum.lo;
             base[0] = cnt > 0 ? total / (double)cnt : nan;
             base[P.ld] = mn;
-            base[2 * P.ld] = cnt > 0 ? ((cnt & 1) ? med_lo : (med_lo + med_hi) / 2.0) : nan;
+            base[2 * P.ld] = cnt > 0 ? ((cnt & 1) ? v_lo : (v_lo + v_next) / 2.0) : nan;
             base[3 * P.ld] = mx;
         }
-        __syncwarp();
     }
 }
 
@@ -714,10 +764,8 @@ void run_summaries(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int6
     sp.q_direct = P.d_q_direct;
     sp.q_flipped = P.d_q_flipped;
     sp.out = d_out;
-    const size_t smem = (size_t)SUM_WARPS * maxr * 8;
-    if (smem > ctx->smem_optin) throw Error("too many comparisons per group for the summary kernel");
-    allow_smem(k5_summaries, smem);
-    SB_LAUNCH(ctx, k5_summaries, (unsigned)ceil_div((int64_t)ngenes * P.K, SUM_WARPS), SUM_WARPS * 32, smem, sp);
+    const int64_t items = ceil_div(ngenes, 32) * P.K;
+    SB_LAUNCH(ctx, k5_summaries, (unsigned)ceil_div(items, SUM_WARPS), SUM_WARPS * 32, 0, sp);
 }
 
 // d_eff holds the comparison columns [eff_q0, eff_q0 + eff_nq) of every effect: [3][eff_nq][ld].
