@@ -158,8 +158,8 @@ int scranb200_combine_markers(scranb200_ctx* ctx, int64_t ngenes, int ncon, cons
 
 /* ---- overlap_exprs_paired: src/overlap_exprs.cpp:196-220 ------------------------------------
  * groups: the reference's list of 0-based cell-index vectors, flattened: group g owns
- * group_cells[group_ptr[g] .. group_ptr[g+1]). A cell may belong to at most one group (the
- * reference's R callers guarantee it: R/scoreMarkers.R:341-345).
+ * group_cells[group_ptr[g] .. group_ptr[g+1]). As in the reference, a cell may be listed by several
+ * groups, or several times by one (it then counts that many times).
  * left/right: 1-based group indices, exactly as the reference takes them (:215).
  * u_out: npairs x nrow column-major (pairs contiguous within a gene), U = #(a - lfc > b) +
  * 0.5 #(a - lfc == b) over a in left group, b in right group; exact half-integers.

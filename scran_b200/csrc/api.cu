@@ -207,15 +207,13 @@ void finish_upload(scranb200_ctx* ctx, scranb200_mat* m, const int32_t* i, const
     }
 }
 
-// Cell -> group from the reference's list-of-index-vectors form (src/overlap_exprs.cpp:13-32).
-void groups_to_ids(int64_t ncells, int ngroups, const int64_t* gptr, const int32_t* gcells, std::vector<int32_t>& ids) {
-    ids.assign(ncells, -1);
+// The reference's list-of-index-vectors form (src/overlap_exprs.cpp:13-32): its bounds check, message kept.
+void check_group_lists(int64_t ncells, int ngroups, const int64_t* gptr, const int32_t* gcells) {
+    if (ngroups < 0) throw Error("negative number of groups");
     for (int g = 0; g < ngroups; ++g) {
+        if (gptr[g + 1] < gptr[g]) throw Error("group pointers must be non-decreasing");
         for (int64_t k = gptr[g]; k < gptr[g + 1]; ++k) {
-            const int32_t c = gcells[k];
-            if (c < 0 || c >= ncells) throw Error("indices in 'groups' out of range");
-            if (ids[c] >= 0) throw Error("a cell listed in more than one group (or twice) is not supported");
-            ids[c] = g;
+            if (gcells[k] < 0 || gcells[k] >= ncells) throw Error("indices in 'groups' out of range");
         }
     }
 }
@@ -742,8 +740,7 @@ int scranb200_overlap_exprs_paired(scranb200_ctx* ctx, const scranb200_mat* mat,
     API_BEGIN
     ctx_guard(ctx);
     mat_guard(ctx, mat);
-    std::vector<int32_t> ids;
-    groups_to_ids(mat->ncol, ngroups, group_ptr, group_cells, ids);
+    check_group_lists(mat->ncol, ngroups, group_ptr, group_cells);
     std::vector<int32_t> l0(npairs), r0(npairs);
     for (int64_t k = 0; k < npairs; ++k) {
         l0[k] = left[k] - 1;  // 1-based, src/overlap_exprs.cpp:215
@@ -751,7 +748,7 @@ int scranb200_overlap_exprs_paired(scranb200_ctx* ctx, const scranb200_mat* mat,
         if (l0[k] < 0 || l0[k] >= ngroups || r0[k] < 0 || r0[k] >= ngroups) throw Error("pair index out of range");
     }
     PairLayout L;
-    build_layout(ids.data(), mat->ncol, ngroups, l0.data(), r0.data(), npairs, ctx->sm_count * 4, L);
+    build_layout_members(group_ptr, group_cells, mat->ncol, ngroups, l0.data(), r0.data(), npairs, ctx->sm_count * 4, L);
     upload_layout(ctx, L, ctx->layout_i32);
     phase_begin(ctx);
     run_pairs(ctx, mat, L, ctx->layout_i32, false, lfc, true, ties_out != nullptr);
@@ -770,8 +767,7 @@ int scranb200_overlap_exprs(scranb200_ctx* ctx, const scranb200_mat* mat, int ng
     API_BEGIN
     ctx_guard(ctx);
     mat_guard(ctx, mat);
-    std::vector<int32_t> ids;
-    groups_to_ids(mat->ncol, ngroups, group_ptr, group_cells, ids);
+    check_group_lists(mat->ncol, ngroups, group_ptr, group_cells);
     std::vector<int32_t> l0, r0;
     for (int a = 0; a < ngroups; ++a) {
         if (group_ptr[a + 1] == group_ptr[a]) continue;  // src/overlap_exprs.cpp:175
@@ -796,7 +792,7 @@ int scranb200_overlap_exprs(scranb200_ctx* ctx, const scranb200_mat* mat, int ng
     }
     if (npairs == 0 || ngenes == 0) return 0;
     PairLayout L;
-    build_layout(ids.data(), mat->ncol, ngroups, l0.data(), r0.data(), npairs, ctx->sm_count * 4, L);
+    build_layout_members(group_ptr, group_cells, mat->ncol, ngroups, l0.data(), r0.data(), npairs, ctx->sm_count * 4, L);
     upload_layout(ctx, L, ctx->layout_i32);
     std::vector<double> hu((size_t)ngenes * npairs), ht(ties_out ? (size_t)ngenes * npairs : 0);
     phase_begin(ctx);

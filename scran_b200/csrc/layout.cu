@@ -18,6 +18,28 @@ int uf_find(std::vector<int32_t>& parent, int a) {
 
 void build_layout(const int32_t* comb_id, int64_t ncells, int C, const int32_t* left, const int32_t* right,
                   int64_t npairs, int target_chunks, PairLayout& L) {
+    // cell -> combination becomes the list form (cells of every combination in ascending order)
+    std::vector<int64_t> gptr(C + 1, 0);
+    for (int64_t k = 0; k < ncells; ++k) {
+        const int c = comb_id[k];
+        if (c < 0) continue;
+        if (c >= C) throw Error("combination id out of range");
+        gptr[c + 1]++;
+    }
+    for (int c = 0; c < C; ++c) gptr[c + 1] += gptr[c];
+    std::vector<int32_t> gcells(std::max<int64_t>(1, gptr[C]));
+    {
+        std::vector<int64_t> fill(gptr.begin(), gptr.end() - 1);
+        for (int64_t k = 0; k < ncells; ++k) {
+            const int c = comb_id[k];
+            if (c >= 0) gcells[fill[c]++] = (int32_t)k;
+        }
+    }
+    build_layout_members(gptr.data(), gcells.data(), ncells, C, left, right, npairs, target_chunks, L);
+}
+
+void build_layout_members(const int64_t* gptr, const int32_t* gcells, int64_t ncells, int C, const int32_t* left,
+                          const int32_t* right, int64_t npairs, int target_chunks, PairLayout& L) {
     L = PairLayout();
     L.ncells = ncells;
     L.C = C;
@@ -66,22 +88,19 @@ void build_layout(const int32_t* comb_id, int64_t ncells, int C, const int32_t* 
         }
     }
 
-    // Cells per device combination and the stable cell permutation.
+    // Cells per device combination and the column list: the members of device combination 0 in the order
+    // given, then those of 1, ... A cell that belongs to several combinations is simply listed several times.
     L.ncells_dev.assign(C, 0);
-    for (int64_t k = 0; k < ncells; ++k) {
-        const int c = comb_id[k];
-        if (c < 0) continue;
-        if (c >= C) throw Error("combination id out of range");
-        L.ncells_dev[L.dev_of_caller[c]]++;
-    }
+    for (int c = 0; c < C; ++c) L.ncells_dev[L.dev_of_caller[c]] = gptr[c + 1] - gptr[c];
     std::vector<int64_t> start(C + 1, 0);
     for (int d = 0; d < C; ++d) start[d + 1] = start[d] + L.ncells_dev[d];
+    if (start[C] > 2147483647ll) throw Error("too many group memberships");
     L.perm.resize(start[C]);
-    {
-        std::vector<int64_t> fill(start.begin(), start.end() - 1);
-        for (int64_t k = 0; k < ncells; ++k) {
-            const int c = comb_id[k];
-            if (c >= 0) L.perm[fill[L.dev_of_caller[c]]++] = (int32_t)k;
+    for (int d = 0; d < C; ++d) {
+        const int c = L.caller_of_dev[d];
+        for (int64_t k = gptr[c]; k < gptr[c + 1]; ++k) {
+            if (gcells[k] < 0 || gcells[k] >= ncells) throw Error("indices in 'groups' out of range");
+            L.perm[start[d] + (k - gptr[c])] = gcells[k];
         }
     }
 

@@ -50,6 +50,11 @@ struct PairLayout {
 void build_layout(const int32_t* comb_id, int64_t ncells, int C, const int32_t* left, const int32_t* right,
                   int64_t npairs, int target_chunks, PairLayout& L);
 
+// The same from the reference's list form (src/overlap_exprs.cpp:13-32): combination c holds the cells
+// gcells[gptr[c] .. gptr[c + 1]). A cell may be listed by several combinations, or more than once.
+void build_layout_members(const int64_t* gptr, const int32_t* gcells, int64_t ncells, int C, const int32_t* left,
+                          const int32_t* right, int64_t npairs, int target_chunks, PairLayout& L);
+
 // Copies the arrays above into buf (grown as needed) on the context's stream.
 void upload_layout(scranb200_ctx* ctx, PairLayout& L, DevBuf& buf);
 

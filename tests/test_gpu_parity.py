@@ -104,6 +104,24 @@ def test_overlap_paired_exact(sb, oracle_lib, port_lib, lfc, sparse):
     assert np.array_equal(t[:, keep], pt[:, keep])
 
 
+def test_overlap_paired_cells_in_several_groups(sb, oracle_lib, port_lib):
+    """The reference takes any lists of cell indices (src/overlap_exprs.cpp:13-32): overlapping groups, a cell listed
+    twice by one group (it counts twice), groups in any order of cells."""
+    x = make_matrix(150, 200, seed=23)
+    rng = np.random.default_rng(10)
+    groups = [np.sort(rng.choice(200, n, replace=False)).astype(np.int32) for n in (60, 90, 40, 200)]
+    groups[2] = rng.permutation(np.concatenate([groups[2], groups[2][:7]])).astype(np.int32)  # repeats, unsorted
+    left, right = all_pairs(4)
+    for lfc in (0.0, 0.4):
+        u, t = sb.overlap_exprs_paired(as_csc(x), left, right, groups, lfc, want_ties=True)
+        assert np.array_equal(u, oracle_lib.overlap_paired(as_csc(x), left, right, groups, lfc))
+        pu, pt = port_lib.overlap_paired(as_csc(x), left, right, groups, lfc, want_ties=True)
+        assert np.array_equal(t, pt)
+        gu, gt = sb.overlap_exprs(as_csc(x), groups, lfc)
+        ru, rt = oracle_lib.overlap(as_csc(x), groups, lfc)
+        assert np.array_equal(gu, ru, equal_nan=True) and np.array_equal(gt, rt, equal_nan=True)
+
+
 def test_overlap_paired_matches_scipy(sb):
     import scipy.stats as st
     x = make_matrix(60, 150, seed=2)
@@ -329,7 +347,66 @@ def test_score_markers_blocked(sb):
     groups = rng.integers(0, 4, 400)
     block = rng.integers(0, 3, 400)
     got, want = _score_both(sb, x, groups, block=block, full_stats=True)
-    assert_tables_match(got, want, skip_selfother=True)
+    assert_tables_match(got, want)   # self. / other. included: against the restatement of scuttle::correctGroupSummary (parity unpinned)
+
+
+def test_score_markers_blocking_pins_of_the_reference_tests(sb):
+    """What the reference's own tests pin about blocking (tests/testthat/test-score-markers.R:216-256): the blocked
+    effect of a pair is the weighted mean of the per-block effects, weights = the products of the group sizes in the
+    block (from the full.* matrices of scoring every block alone), and self.average + (G - 1) other.average is the
+    same for every group while self.average is not."""
+    rng = np.random.default_rng(31)
+    y = rng.poisson(0.5, (10, 100)).astype(np.float64)
+    cluster = rng.integers(0, 5, 100)
+    block = rng.integers(0, 3, 100)
+    out = sb.score_markers(y, cluster, block=block, full_stats=True)
+    per = [sb.score_markers(y[:, block == b], cluster[block == b], full_stats=True) for b in range(3)]
+    for i in range(5):
+        for eff in ("logFC.cohen", "AUC", "logFC.detected"):
+            rights = list(out[i]["full." + eff + ".right"])
+            for j in rights:
+                v = np.stack([p[i]["full." + eff][:, list(p[i]["full." + eff + ".right"]).index(j)] for p in per], 1)
+                w = np.array([p[i]["full." + eff + ".weight"][list(p[i]["full." + eff + ".right"]).index(j)] for p in per])
+                wm = (~np.isnan(v)) * w[None, :]
+                with np.errstate(invalid="ignore"):
+                    want = np.nansum(v * wm, 1) / wm.sum(1)
+                got = out[i]["full." + eff][:, rights.index(j)]
+                np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-12, equal_nan=True)
+    summed = [out[i]["self.average"] + out[i]["other.average"] * 4 for i in range(5)]
+    for i in range(1, 5):
+        np.testing.assert_allclose(summed[i], summed[0], rtol=1e-10, atol=1e-12)
+        assert not np.allclose(out[i]["self.average"], out[0]["self.average"])
+
+
+def test_score_markers_group_specific_batches_stay_finite(sb):
+    """tests/testthat/test-score-markers.R:259-291, 296-343: groups that live in one batch only. Pairs that never share
+    a batch have NA effects; the self. / other. columns stay finite."""
+    rng = np.random.default_rng(32)
+    y = rng.poisson(0.5, (10, 100)).astype(np.float64)
+    cluster = rng.integers(10, 15, 100)
+    block = np.where(cluster % 2 == 1, "odd", "even")
+    out = sb.score_markers(y, cluster, block=block, full_stats=True)
+    for i in range(10, 15):
+        rights = list(out[i]["full.logFC.detected.right"])
+        for j in rights:
+            col = out[i]["full.logFC.detected"][:, rights.index(j)]
+            if j % 2 != i % 2:
+                assert np.isnan(col).all()
+            else:
+                alone = sb.score_markers(y[:, cluster % 2 == i % 2], cluster[cluster % 2 == i % 2], full_stats=True)
+                ref = alone[i]["full.logFC.detected"][:, list(alone[i]["full.logFC.detected.right"]).index(j)]
+                np.testing.assert_allclose(col, ref, rtol=1e-12, atol=1e-12)
+        for c in sb.COLUMNS[:4]:
+            assert np.isfinite(out[i][c]).all(), (i, c)
+    block2 = rng.integers(1, 3, 100)
+    block2[cluster == 10] = 1
+    block2[cluster == 14] = 2
+    out = sb.score_markers(y, cluster, block=block2, full_stats=True)
+    for i in range(10, 15):
+        for c in sb.COLUMNS[:4]:
+            assert np.isfinite(out[i][c]).all(), (i, c)
+    rights = list(out[10]["full.AUC.right"])
+    assert np.isnan(out[10]["full.AUC"][:, rights.index(14)]).all()
 
 
 def test_score_markers_blocked_lfc_missing_combinations(sb):
@@ -342,7 +419,7 @@ def test_score_markers_blocked_lfc_missing_combinations(sb):
     block[groups == 3] = 2          # group 3 only in block 2
     block[(groups == 0) & (block == 2)] = 0   # group 0 never in block 2
     got, want = _score_both(sb, x, groups, block=block, lfc=0.3, full_stats=True)
-    assert_tables_match(got, want, skip_selfother=True)
+    assert_tables_match(got, want)
     assert np.isnan(got[0]["full.AUC"][:, list(got[0]["full.AUC.right"]).index(3)]).all()
 
 
