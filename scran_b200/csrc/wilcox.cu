@@ -1008,6 +1008,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 constexpr int WALK_THREADS = 1024;
 constexpr int WALK_WARPS = WALK_THREADS / 32;
 constexpr int WALK_MAX_GROUPS = 32;
+constexpr int WALK_MAX_CHUNKS = 256;  // position chunks of one unit over all rounds of the 32-bit pass
 
 struct WalkParams {
     UnitTables ut;
@@ -1034,6 +1035,7 @@ struct WalkParams {
     int groups0;          // large-unit kernel: position chunks of the 32-bit pass (the 64-bit pass needs them to tell its units)
     int shared_table;     // large-unit kernel: the position chunks add into ONE table (32-bit cells, atomic adds)
     int by_task;          // large-unit kernel: walk EVERY unit (used when the per-warp mode has no room for its tables)
+    int shared0;          // large-unit kernel: the 32-bit pass runs with one shared table (and therefore in rounds)
 };
 
 // 2U from the count table (AccT entries, row stride `rpad`) for one pair.
@@ -1376,8 +1378,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
     const int HG = P.hist_groups;  // chunk rows kept: enough for the groups of either pass
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [2 * HG][Gmax1]: per-chunk counts, counted / adding role
     uint32_t* nnzv = hist + (size_t)(2 * HG) * Gmax1;                         // [Gmax1]
-    int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);                      // [WALK_MAX_GROUPS + 1]
-    uint32_t* misc = reinterpret_cast<uint32_t*>(bounds + WALK_MAX_GROUPS + 1);  // [4]
+    int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);                      // [WALK_MAX_CHUNKS + 1]
+    uint32_t* misc = reinterpret_cast<uint32_t*>(bounds + WALK_MAX_CHUNKS + 1);  // [4]
     size_t off = (size_t)((unsigned char*)(misc + 4) - smem_raw);
     off = (off + 15) & ~size_t(15);
     AccT* acc = reinterpret_cast<AccT*>(smem_raw + off);
@@ -1442,10 +1444,85 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
             __syncthreads();
             return misc[1] != 0u;
         };
+        // The 32-bit pass with ONE shared table walks a long unit in rounds: `g0` position chunks at a time, the
+        // table being added into the 64-bit totals (bfull) after every round, so that a unit of any length keeps
+        // all warps busy on 32-bit cells as long as no single round can overflow one (only a giant run of equal
+        // values, which no chunk boundary may cut, can). nrounds_for: the rounds it takes with g0 concurrent
+        // chunks, 0 if the unit has to take the 64-bit pass; leaves the chunk bounds behind.
+        auto nrounds_for = [&](int g0) {
+            const double per_chunk = 2.0 * sqrt(3.9e9 / ((double)g0 * (SHIFT ? 2.0 : 1.0)));  // entries a chunk may hold
+            const long long per_round = (long long)(per_chunk * g0);
+            const long long R = ((long long)m + per_round - 1) / per_round;
+            if (R * g0 > WALK_MAX_CHUNKS) return 0;
+            const int nc = (int)R * g0;
+            chunk_bounds(nc);
+            __syncthreads();
+            if (tid == 0) {
+                uint32_t ok = 1u;
+                for (int r = 0; r < (int)R; ++r) {
+                    unsigned long long sum = 0;
+                    for (int c = r * g0; c < (r + 1) * g0; ++c) {
+                        const unsigned long long len = (unsigned long long)(bounds[c + 1] - bounds[c]);
+                        sum += len * len;
+                    }
+                    if ((sum / 4) * (SHIFT ? 2ull : 1ull) >= 4000000000ull) ok = 0u;
+                }
+                misc[1] = ok;
+            }
+            __syncthreads();
+            return misc[1] != 0u ? (int)R : 0;
+        };
+        if (P.pass == 0 && P.shared_table) {
+            const int R = nrounds_for(groups);
+            if (R == 0) continue;
+            const size_t rpad = (size_t)ntiles * W;  // (shared_table: all tiles of the table are resident)
+            uint32_t* hist_l = hist + (size_t)HG * Gmax1;
+            for (int k = tid; k < Gt * Gt; k += blockDim.x) bfull[k] = 0ull;
+            for (int k = tid; k < Gt; k += blockDim.x) nnzv[k] = 0u;  // label counts of the rounds before
+            for (int r = 0; r < R; ++r) {
+                for (int k = tid; k < Gt * (int)rpad; k += blockDim.x) acc[k] = 0;
+                __syncthreads();
+                if (warp < groups * ntiles) {
+                    const int cg = warp / ntiles, tile = warp % ntiles;
+                    const int R0 = tile * W + lane;
+                    walk_range<AccT, SHIFT, J>(st, bounds[r * groups + cg], bounds[r * groups + cg + 1], R0, acc + R0, rpad,
+                                               hist + cg * Gmax1, hist_l + cg * Gmax1, Gt, lane);
+                }
+                __syncthreads();
+                // per-chunk counts -> counts before each chunk (earlier rounds included); the round's totals move on
+                for (int Rr = tid; Rr < Gt; Rr += blockDim.x) {
+                    uint32_t run = nnzv[Rr];
+                    for (int cg = 0; cg < groups; ++cg) {
+                        const uint32_t here = hist[cg * Gmax1 + Rr];
+                        hist[cg * Gmax1 + Rr] = run;
+                        if (!SHIFT) hist_l[cg * Gmax1 + Rr] = here;
+                        run += here;
+                    }
+                    nnzv[Rr] = run;
+                }
+                __syncthreads();
+                for (int k = tid; k < Gt * Gt; k += blockDim.x) {
+                    const int L = k / Gt, Rr = k % Gt;
+                    unsigned long long s2 = 0;  // what the entries before each chunk add to its rows
+                    for (int cg = 0; cg < groups; ++cg)
+                        s2 += (unsigned long long)hist_l[cg * Gmax1 + L] * (unsigned long long)hist[cg * Gmax1 + Rr];
+                    bfull[k] += (unsigned long long)acc[(size_t)L * rpad + Rr] + (SHIFT ? 2ull * s2 : s2);
+                }
+                __syncthreads();
+            }
+            for (int pp = P.pair_ptr[ui.u] + tid; pp < P.pair_ptr[ui.u + 1]; pp += blockDim.x) {
+                const int l = P.pair_l[pp], r = P.pair_r[pp];
+                const long long nL = ut.ncells_dev[ui.first + l], nR = ut.ncells_dev[ui.first + r];
+                const long long zL = nL - (long long)nnzv[l], zR = nR - (long long)nnzv[r];
+                P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] =
+                    pair_u<unsigned long long, SHIFT>(bfull, (size_t)Gt, l, r, G, nL, nR, zL, zR);
+            }
+            continue;
+        }
         if (P.pass == 0) {
             if (!fits32(groups)) continue;
         } else {
-            if (fits32(P.groups0)) continue;
+            if (P.shared0 ? nrounds_for(P.groups0) != 0 : fits32(P.groups0)) continue;
             __syncthreads();
             chunk_bounds(groups);
         }
@@ -1751,7 +1828,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     const int W = 32 * J;
     const int ntiles = (Gt + W - 1) / W;  // wide tiles = warps per unit
     // fixed part of the large-unit kernel's shared memory, with rows for hg chunk groups
-    auto walk_fixed_for = [&](int hg) { return ((size_t)(2 * hg) * Gt + Gt) * 4 + (WALK_MAX_GROUPS + 1) * 4 + 16 + 32; };
+    auto walk_fixed_for = [&](int hg) { return ((size_t)(2 * hg) * Gt + Gt) * 4 + (WALK_MAX_CHUNKS + 1) * 4 + 16 + 32; };
     const int walk_grid_max = ctx->sm_count * 2;
     ctx->plan_tmp.reserve((size_t)walk_grid_max * Gt * Gt * 8 + 64);
     wp.bfull = ctx->plan_tmp.as<unsigned long long>();
@@ -1760,6 +1837,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     wp.big_total = big_total;
     wp.nbig = nbig;
     wp.by_task = 0;
+    wp.shared0 = 0;
 
     // ---- units of up to big_total entries: one warp group per unit, no CTA-wide barriers ----
     {
@@ -1845,7 +1923,10 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
         }
         wp.tiles_per_batch = tpb;
         wp.groups = groups;
-        if (pass == 0) wp.groups0 = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
+        if (pass == 0) {
+            wp.groups0 = std::max(1, std::min(groups, WALK_WARPS / std::max(1, tpb)));
+            wp.shared0 = wp.shared_table;
+        }
         const size_t smem = walk_fixed + per_tile * tpb * copies;
         SB_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
         const int grid = (int)std::min<int64_t>(ntasks, smem * 2 <= ctx->smem_optin ? walk_grid_max : ctx->sm_count);
