@@ -40,6 +40,8 @@ def test_static_min_rank_matches_regular_entry_point_twice():
     got, want = _both(sb, torch, a)
     assert np.array_equal(got, want)
     assert got[11] == np.iinfo(np.int32).max
+    from oracle import rlevel
+    assert np.array_equal(got.astype(np.int64), rlevel.compute_min_rank(a))   # and against the CPU restatement
     # second call right after, smaller and with other contents: must not see the first call's state
     b = rng.normal(size=(700, 9))
     b[5:60, 3] = 0.5
