@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(1024) k1_scan_rows(const uint32_t* __restrict_
 constexpr int K1W_WARPS = 4;
 constexpr int K1W_DEPTH = 8;
 
-__global__ void __launch_bounds__(K1W_WARPS * 32, 7)
+__global__ void __launch_bounds__(K1W_WARPS * 32)
 k1_scatter_warp(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
                 const int32_t* __restrict__ perm, const int32_t* __restrict__ chunk_start, int ngenes, int nsub,
                 const uint32_t* __restrict__ sub_split, const uint32_t* __restrict__ table,
@@ -221,58 +221,46 @@ k1_scatter_warp(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, 
             }
         }
     };
-    // The columns are taken 32 at a time ("groups": lane l knows the bounds of column l of the group), but the
-    // ring of prefetched slices runs straight across the group boundaries: the bounds of the NEXT group are
-    // fetched while the current one is being applied, so the pipeline never drains inside a chunk. A ring slot
-    // holds only the lane's entry (gene, value); a slice's position and length are shuffled from the group's
-    // bounds again when it is applied (they are needed for slices beyond 32 entries only).
-    auto bounds = [&](int j0, int64_t& lo, int& n) {
-        lo = 0;
-        n = 0;
+    struct Slice {
+        int32_t g;
+        double v;
+        int64_t lo;
+        int n;
+    };
+    for (int j0 = 0; j0 < ncols; j0 += 32) {
+        // bounds of my sub-range inside the next 32 columns: one column per lane
+        int64_t my_lo = 0;
+        int my_n = 0;
         if (j0 + lane < ncols) {
             const int pos = c_lo + j0 + lane;
             const uint32_t* srow = sub_split + (size_t)pos * (nsub + 1);
             const uint32_t a = srow[sr], b = srow[sr + 1];
-            lo = p[perm[pos]] + a;
-            n = (int)(b - a);
+            my_lo = p[perm[pos]] + a;
+            my_n = (int)(b - a);
         }
-    };
-    int64_t lo_a, lo_b;
-    int n_a, n_b;
-    bounds(0, lo_a, n_a);
-    bounds(32, lo_b, n_b);
-    int32_t ring_g[K1W_DEPTH];
-    double ring_v[K1W_DEPTH];
-    auto load = [&](int d, int q) {  // column q of the current group (q >= 32: of the next one)
-        const int64_t lo = __shfl_sync(0xffffffffu, q < 32 ? lo_a : lo_b, q & 31);
-        const int n = __shfl_sync(0xffffffffu, q < 32 ? n_a : n_b, q & 31);
-        ring_g[d] = -1;
-        if (lane < n) {
-            ring_g[d] = idx[lo + lane];
-            ring_v[d] = x[lo + lane];
-        }
-    };
+        const int nb = min(32, ncols - j0);
+        Slice ring[K1W_DEPTH];
+        auto load = [&](Slice& sl, int q) {
+            sl.lo = __shfl_sync(0xffffffffu, my_lo, q & 31);
+            sl.n = q < nb ? __shfl_sync(0xffffffffu, my_n, q & 31) : 0;
+            sl.g = -1;
+            if (lane < sl.n) {
+                sl.g = idx[sl.lo + lane];
+                sl.v = x[sl.lo + lane];
+            }
+        };
 #pragma unroll
-    for (int d = 0; d < K1W_DEPTH; ++d) load(d, d);
-    for (int j0 = 0; j0 < ncols; j0 += 32) {
-        static_assert(32 % K1W_DEPTH == 0, "the ring must divide a group");
-        for (int q0 = 0; q0 < 32; q0 += K1W_DEPTH) {
+        for (int d = 0; d < K1W_DEPTH; ++d) load(ring[d], d);
+        for (int q0 = 0; q0 < nb; q0 += K1W_DEPTH) {
 #pragma unroll
             for (int d = 0; d < K1W_DEPTH; ++d) {
-                const int q = q0 + d;
-                if (ring_g[d] >= 0) put(ring_g[d], ring_v[d]);
-                const int n = __shfl_sync(0xffffffffu, n_a, q);
-                if (n > 32) {  // (warp-uniform) a slice longer than the warp: the rest straight from memory
-                    const int64_t lo = __shfl_sync(0xffffffffu, lo_a, q);
-                    for (int k = 32 + lane; k < n; k += 32) put(idx[lo + k], x[lo + k]);
-                }
+                Slice& sl = ring[d];
+                if (sl.g >= 0) put(sl.g, sl.v);
+                for (int k = 32 + lane; k < sl.n; k += 32) put(idx[sl.lo + k], x[sl.lo + k]);
                 __syncwarp();  // the next column may touch the same genes from other lanes
-                load(d, q + K1W_DEPTH);
+                load(sl, q0 + d + K1W_DEPTH);
             }
         }
-        lo_a = lo_b;
-        n_a = n_b;
-        bounds(j0 + 64, lo_b, n_b);
     }
     __syncwarp();
     // flush the incomplete last sector of every gene

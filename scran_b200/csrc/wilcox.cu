@@ -1013,7 +1013,7 @@ constexpr int WALK_MAX_CHUNKS = 256;  // position chunks of one unit over all ro
 struct WalkParams {
     UnitTables ut;
     const uint16_t* stream;
-    const uint32_t* unit_m;
+    uint32_t* unit_m;   // entries of every unit's stream; bit 31: the unit has been walked by the 32-bit pass of k3_walk
     const int32_t *pair_ptr, *pair_l, *pair_r, *pair_out;
     int64_t npairs;
     double* u_out;
@@ -1326,7 +1326,7 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk_small(WalkParams P) {
         const UnitInfo ui = unit_info(ut, task);
         if (ui.total > P.big_total) continue;  // walked by k3_walk
         const int Gt = ui.G + 1;
-        const uint32_t m = P.unit_m[task];
+        const uint32_t m = P.unit_m[task] & 0x7fffffffu;
         const uint16_t* st = P.stream + ui.soff;
         for (int k = stid; k < Gt * (int)rpad; k += sthreads) sacc[k] = 0;
         if (nch == 2 && ws == 0) {  // second chunk: from the first run start at or after the middle
@@ -1379,7 +1379,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);                 // [2 * HG][Gmax1]: per-chunk counts, counted / adding role
     uint32_t* nnzv = hist + (size_t)(2 * HG) * Gmax1;                         // [Gmax1]
     int* bounds = reinterpret_cast<int*>(nnzv + Gmax1);                      // [WALK_MAX_CHUNKS + 1]
-    uint32_t* misc = reinterpret_cast<uint32_t*>(bounds + WALK_MAX_CHUNKS + 1);  // [4]
+    int* cand = bounds + WALK_MAX_CHUNKS + 1;                                // [WALK_MAX_CHUNKS]: run start / end at every cut target
+    uint32_t* misc = reinterpret_cast<uint32_t*>(cand + WALK_MAX_CHUNKS);    // [4]
     size_t off = (size_t)((unsigned char*)(misc + 4) - smem_raw);
     off = (off + 15) & ~size_t(15);
     AccT* acc = reinterpret_cast<AccT*>(smem_raw + off);
@@ -1402,8 +1403,9 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
             t0 = P.jobs[P.order[misc[0]]];
         }
         // ---- one large unit, all warps: position chunks with private tables -----------------
-        const uint32_t m = P.unit_m[t0];
-        if (P.pass == 1 && m <= 65536u) continue;  // always fits 32-bit cells
+        const uint32_t m_raw = P.unit_m[t0];
+        const uint32_t m = m_raw & 0x7fffffffu;
+        if (P.pass == 1 && ((m_raw >> 31) || m <= 65536u)) continue;  // walked by the 32-bit pass / always fits 32-bit cells
         const UnitInfo ui = unit_info(ut, t0);
         const int G = ui.G, Gt = G + 1;
         const uint16_t* st = P.stream + ui.soff;
@@ -1449,28 +1451,109 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
         // all warps busy on 32-bit cells as long as no single round can overflow one (only a giant run of equal
         // values, which no chunk boundary may cut, can). nrounds_for: the rounds it takes with g0 concurrent
         // chunks, 0 if the unit has to take the 64-bit pass; leaves the chunk bounds behind.
-        auto nrounds_for = [&](int g0) {
-            const double per_chunk = 2.0 * sqrt(3.9e9 / ((double)g0 * (SHIFT ? 2.0 : 1.0)));  // entries a chunk may hold
-            const long long per_round = (long long)(per_chunk * g0);
-            const long long R = ((long long)m + per_round - 1) / per_round;
-            if (R * g0 > WALK_MAX_CHUNKS) return 0;
-            const int nc = (int)R * g0;
-            chunk_bounds(nc);
-            __syncthreads();
-            if (tid == 0) {
-                uint32_t ok = 1u;
-                for (int r = 0; r < (int)R; ++r) {
-                    unsigned long long sum = 0;
-                    for (int c = r * g0; c < (r + 1) * g0; ++c) {
-                        const unsigned long long len = (unsigned long long)(bounds[c + 1] - bounds[c]);
-                        sum += len * len;
-                    }
-                    if ((sum / 4) * (SHIFT ? 2ull : 1ull) >= 4000000000ull) ok = 0u;
+        // Start of the run (of equal values) that holds position b, and the first run start at or after b: a warp
+        // looks at 128 entries a step, four loads in flight per lane (a run of 150,000 equal values - an
+        // integer-valued gene - is crossed in a millisecond instead of five).
+        auto run_start_at_or_before = [&](int64_t b) {
+            while (b > 0) {
+                unsigned best = 0u;  // 1 + offset from (b - 127) of the last entry without the tie bit
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int64_t i = b - 127 + (lane * 4 + q);
+                    if (i >= 0 && i <= b && !(st[i] & TIE_BIT)) best = (unsigned)(lane * 4 + q) + 1u;
                 }
-                misc[1] = ok;
+                best = __reduce_max_sync(0xffffffffu, best);
+                if (best) return b - 127 + (int64_t)(best - 1u);
+                b -= 128;
+            }
+            return (int64_t)0;
+        };
+        auto run_start_at_or_after = [&](int64_t b) {
+            while (b < (int64_t)m) {
+                unsigned best = 0xffffffffu;
+#pragma unroll
+                for (int q = 3; q >= 0; --q) {
+                    const int64_t i = b + (lane * 4 + q);
+                    if (i < (int64_t)m && !(st[i] & TIE_BIT)) best = (unsigned)(lane * 4 + q);
+                }
+                best = __reduce_min_sync(0xffffffffu, best);
+                if (best != 0xffffffffu) return b + (int64_t)best;
+                b += 128;
+            }
+            return (int64_t)m;
+        };
+        // The 32-bit pass with ONE shared table walks a long unit in rounds: `g0` position chunks at a time, the
+        // table being added into the 64-bit totals (bfull) after every round, so that a unit of any length keeps
+        // all warps busy on 32-bit cells as long as no single round can overflow one. Chunks start where a run of
+        // equal values starts. A LONG run gets a chunk of its own (boundaries at its start and at its end):
+        // walked from zero counts it adds nothing to the table (every entry adds the counts at the run start, zero),
+        // however long it is; what it owes comes from the counts before it, in 64 bits. (With a shift a run is
+        // not free of additions, so there it counts in full.) nrounds_for: the rounds it takes with g0
+        // concurrent chunks, 0 if the unit has to take the 64-bit pass; leaves the chunk bounds behind.
+        auto nrounds_for = [&](int g0) {
+            constexpr int LONG_RUN = 2048;
+            // entries a chunk may hold: g0 chunks of this length, each stretched by up to LONG_RUN entries when its
+            // end moves to the next run start, stay below 2^32 in any cell (sum over the chunks of (entries / 2)^2)
+            const double per_chunk = 2.0 * sqrt(3.0e9 / ((double)g0 * (SHIFT ? 2.0 : 1.0)));
+            const long long per_round = (long long)(per_chunk * g0);
+            const long long rounds = ((long long)m + per_round - 1) / per_round;
+            const long long ntargets = rounds * g0 - 1;  // interior cuts of an even split into rounds * g0 chunks
+            if (2 * (ntargets + 1) + g0 > WALK_MAX_CHUNKS) return 0;
+            if (tid == 0) misc[3] = 0u;
+            __syncthreads();
+            for (int k = warp; k < (int)ntargets; k += WALK_WARPS) {
+                const int64_t b = ((int64_t)m * (k + 1)) / (ntargets + 1);
+                const int64_t s0 = run_start_at_or_before(b);
+                const int64_t e0 = s0 == b ? b : run_start_at_or_after(b);
+                if (lane == 0) {
+                    cand[2 * k] = (int)s0;
+                    cand[2 * k + 1] = (int)e0;
+                    if (e0 - s0 > LONG_RUN) misc[3] = 1u;
+                }
             }
             __syncthreads();
-            return misc[1] != 0u ? (int)R : 0;
+            if (misc[3] == 0u) {
+                // no long run at any cut (the usual case): chunk k ends at the first run start at or after its even
+                // cut; by the choice of per_chunk no round can overflow
+                for (int k = tid; k <= (int)ntargets + 1; k += blockDim.x) {
+                    bounds[k] = k == 0 ? 0 : (k == (int)ntargets + 1 ? (int)m : cand[2 * (k - 1) + 1]);
+                }
+                __syncthreads();
+                return (int)rounds;
+            }
+            if (tid == 0) {
+                int n = 0;  // chunks so far; bounds[n] = start of the next one
+                bounds[0] = 0;
+                unsigned long long sum = 0;
+                uint32_t ok = 1u;
+                auto close_chunk = [&](int end, bool isrun) {
+                    if (end <= bounds[n]) return;
+                    const unsigned long long len = (unsigned long long)(end - bounds[n]);
+                    if (!(isrun && !SHIFT)) sum += len * len;
+                    bounds[++n] = end;
+                    if (n % g0 == 0) {  // a round is complete
+                        if ((sum / 4) * (SHIFT ? 2ull : 1ull) >= 4000000000ull) ok = 0u;
+                        sum = 0;
+                    }
+                };
+                for (int k = 0; k < (int)ntargets; ++k) {
+                    const int s0 = cand[2 * k], e0 = cand[2 * k + 1];
+                    if (e0 - s0 > LONG_RUN) {
+                        close_chunk(s0, false);
+                        close_chunk(e0, true);
+                    } else {
+                        close_chunk(e0, false);
+                    }
+                }
+                close_chunk((int)m, false);
+                if ((sum / 4) * (SHIFT ? 2ull : 1ull) >= 4000000000ull) ok = 0u;
+                const int R = (n + g0 - 1) / g0;
+                for (int c = n + 1; c <= R * g0; ++c) bounds[c] = (int)m;  // the last round's spare chunks are empty
+                misc[1] = ok;
+                misc[2] = (uint32_t)R;
+            }
+            __syncthreads();
+            return misc[1] != 0u ? (int)misc[2] : 0;
         };
         if (P.pass == 0 && P.shared_table) {
             const int R = nrounds_for(groups);
@@ -1517,14 +1600,14 @@ __global__ void __launch_bounds__(WALK_THREADS) k3_walk(WalkParams P) {
                 P.u_out[(size_t)ui.g * P.npairs + P.pair_out[pp]] =
                     pair_u<unsigned long long, SHIFT>(bfull, (size_t)Gt, l, r, G, nL, nR, zL, zR);
             }
+            if (tid == 0) P.unit_m[t0] = m | 0x80000000u;  // the 64-bit pass skips it
             continue;
         }
         if (P.pass == 0) {
             if (!fits32(groups)) continue;
+            if (tid == 0) P.unit_m[t0] = m | 0x80000000u;
         } else {
-            if (P.shared0 ? nrounds_for(P.groups0) != 0 : fits32(P.groups0)) continue;
-            __syncthreads();
-            chunk_bounds(groups);
+            chunk_bounds(groups);  // (whatever the 32-bit pass took carries the flag and never gets here)
         }
         for (int tb = 0; tb < ntiles; tb += tpb) {
             const int bt = min(tpb, ntiles - tb);
@@ -1633,7 +1716,7 @@ __global__ void __launch_bounds__(256) k3_ties(TieParams P) {
     const UnitInfo ui = unit_info(P.ut, task);
     const int G = ui.G;
     const uint16_t* st = P.stream + ui.soff;
-    const uint32_t m = P.unit_m[task];
+    const uint32_t m = P.unit_m[task] & 0x7fffffffu;
     for (int k = tid; k <= G; k += blockDim.x) hist[k] = 0;
     if (tid == 0) {
         wsum[8] = 0;
@@ -1828,7 +1911,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     const int W = 32 * J;
     const int ntiles = (Gt + W - 1) / W;  // wide tiles = warps per unit
     // fixed part of the large-unit kernel's shared memory, with rows for hg chunk groups
-    auto walk_fixed_for = [&](int hg) { return ((size_t)(2 * hg) * Gt + Gt) * 4 + (WALK_MAX_CHUNKS + 1) * 4 + 16 + 32; };
+    auto walk_fixed_for = [&](int hg) { return ((size_t)(2 * hg) * Gt + Gt) * 4 + (2 * WALK_MAX_CHUNKS + 1) * 4 + 16 + 32; };
     const int walk_grid_max = ctx->sm_count * 2;
     ctx->plan_tmp.reserve((size_t)walk_grid_max * Gt * Gt * 8 + 64);
     wp.bfull = ctx->plan_tmp.as<unsigned long long>();
