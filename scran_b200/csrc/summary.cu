@@ -51,13 +51,17 @@ struct SumParams {
 // (up to SUM_SLOTS values, sorted by insertion) or, if it holds more, narrowed to its exact [min, max] and
 // binned again. Equal values end the search at once. A table of hundreds of comparisons costs the same
 // 6 KB of shared memory a warp as one of ten, so the SMs stay full.
+// (Tables of 65 - 255 comparisons take 128 bins with 8-bit counters - one histogram then usually settles the
+// median - at the price of fewer resident warps. Keeping a table's values in shared memory instead of
+// streaming them again was measured too: three warps an SM at 199 comparisons, 2.5 times slower.)
 constexpr int SUM_WARPS = 8;
-constexpr int SUM_BINS = 32;
 constexpr int SUM_SLOTS = 16;
 
-__global__ void __launch_bounds__(SUM_WARPS * 32) k5_summaries(SumParams P) {
-    __shared__ uint16_t s_hist[SUM_WARPS][SUM_BINS][32];
-    __shared__ double s_slot[SUM_WARPS][SUM_SLOTS][32];
+template <int SUM_BINS, typename CountT>
+__global__ void __launch_bounds__(SUM_WARPS * 32, 4) k5_summaries(SumParams P) {
+    extern __shared__ __align__(16) unsigned char sum_smem[];
+    double(*s_slot)[SUM_SLOTS][32] = reinterpret_cast<double(*)[SUM_SLOTS][32]>(sum_smem);
+    CountT(*s_hist)[SUM_BINS][32] = reinterpret_cast<CountT(*)[SUM_BINS][32]>(sum_smem + sizeof(double) * SUM_WARPS * SUM_SLOTS * 32);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t ntiles = (P.ngenes + 31) / 32;
     const int64_t item = (int64_t)blockIdx.x * SUM_WARPS + warp;
@@ -765,7 +769,16 @@ void run_summaries(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int6
     sp.q_flipped = P.d_q_flipped;
     sp.out = d_out;
     const int64_t items = ceil_div(ngenes, 32) * P.K;
-    SB_LAUNCH(ctx, k5_summaries, (unsigned)ceil_div(items, SUM_WARPS), SUM_WARPS * 32, 0, sp);
+    const size_t slots = sizeof(double) * SUM_WARPS * SUM_SLOTS * 32;
+    if (maxr > 64 && maxr <= 255) {
+        const size_t smem = slots + (size_t)SUM_WARPS * 128 * 32;
+        allow_smem(k5_summaries<128, uint8_t>, smem);
+        SB_LAUNCH(ctx, (k5_summaries<128, uint8_t>), (unsigned)ceil_div(items, SUM_WARPS), SUM_WARPS * 32, smem, sp);
+    } else {
+        const size_t smem = slots + (size_t)SUM_WARPS * 32 * 32 * 2;
+        allow_smem(k5_summaries<32, uint16_t>, smem);
+        SB_LAUNCH(ctx, (k5_summaries<32, uint16_t>), (unsigned)ceil_div(items, SUM_WARPS), SUM_WARPS * 32, smem, sp);
+    }
 }
 
 // d_eff holds the comparison columns [eff_q0, eff_q0 + eff_nq) of every effect: [3][eff_nq][ld].
