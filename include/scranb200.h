@@ -264,12 +264,19 @@ int scranb200_fill_i32(scranb200_ctx* ctx, int32_t* d_ptr, int64_t n, int32_t va
  *   receives the result; root < 0: every rank. out (nullable, host): [K][19][ngenes_total] as
  *   scranb200_score_markers writes it; d_out (nullable): receives the DEVICE address of the same
  *   table inside the context's scratch (valid until the context's next call; null on ranks that
- *   do not receive the result). */
+ *   do not receive the result).
+ * scranb200_exchange_plan: host arithmetic only, no GPU needed - the block positions of the one exchange step
+ *   as scranb200_score_markers_sharded uses them (comparison shards q_starts[world + 1]; for `rank`, per peer s:
+ *   offset / length in doubles of the block sent to s inside one effect's [Q][nrows_rank] plane, offset /
+ *   length of the block received from s in the staging buffer, effect e at offset + e * length). Exposed so
+ *   that the plan can be exercised by a multi-process test on CPUs (tests/test_distributed_cpu.py, gloo). */
 #define SCRANB200_COMM_ID_BYTES 128
 int scranb200_comm_unique_id(char* id_out);
 int scranb200_ctx_comm_init(scranb200_ctx* ctx, int world, int rank, const char* id_in);
 int scranb200_ctx_comm_init_all(scranb200_ctx** ctxs, int n);
 int scranb200_balance_rows(const double* weight, int64_t nrow, int world, int64_t* row_starts);
+int scranb200_exchange_plan(int64_t Q, int world, int rank, const int64_t* row_starts, int64_t* q_starts, int64_t* send_off,
+                            int64_t* send_len, int64_t* recv_off, int64_t* recv_len);
 int scranb200_score_markers_sharded(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb200_plan* plan,
                                     int64_t ngenes_total, const int64_t* row_starts, int root, double* out,
                                     double** d_out);

@@ -74,6 +74,7 @@ def _signatures():
         "scranb200_comm_unique_id": (C.c_int, [_p]),
         "scranb200_ctx_comm_init": (C.c_int, [c_ctx, C.c_int, C.c_int, _p]),
         "scranb200_ctx_comm_init_all": (C.c_int, [_p, C.c_int]),
+        "scranb200_exchange_plan": (C.c_int, [i64, C.c_int, C.c_int, _p, _p, _p, _p, _p, _p]),
         "scranb200_balance_rows": (C.c_int, [_p, i64, C.c_int, _p]),
         "scranb200_score_markers_sharded": (C.c_int, [c_ctx, c_mat, c_plan, i64, _p, C.c_int, _p, _p]),
         "scranb200_synth_row_weights": (C.c_int, [i64, i64, dbl, u64, _p]),

@@ -99,6 +99,25 @@ __global__ void __launch_bounds__(256) dist_place_rows(const double* __restrict_
 
 }  // namespace
 
+// Who sends what where in the one exchange step: the comparison columns are cut into `world` contiguous,
+// equally sized shards (q_starts); rank r sends to rank s, for every effect e, the block
+// eff_local[e][q_starts[s] .. q_starts[s+1])[0 .. n_r) - contiguous, send_off / send_len doubles inside effect e's
+// plane of [Q][n_r] - and receives from s the block [nq_r][n_s] of every effect into its staging buffer at
+// recv_off[s] + e * recv_len[s]. Host arithmetic only: score_sharded uses it, and so does the gloo test on CPU.
+void exchange_plan(int64_t Q, int world, int rank, const int64_t* row_starts, int64_t* q_starts, int64_t* send_off,
+                   int64_t* send_len, int64_t* recv_off, int64_t* recv_len) {
+    const int64_t qper = (Q + world - 1) / world;
+    for (int s = 0; s <= world; ++s) q_starts[s] = std::min<int64_t>(Q, s * qper);
+    const int64_t n_r = row_starts[rank + 1] - row_starts[rank];
+    const int64_t nq_r = q_starts[rank + 1] - q_starts[rank];
+    for (int s = 0; s < world; ++s) {
+        send_off[s] = q_starts[s] * n_r;
+        send_len[s] = (q_starts[s + 1] - q_starts[s]) * n_r;
+        recv_off[s] = 3 * nq_r * row_starts[s];
+        recv_len[s] = nq_r * (row_starts[s + 1] - row_starts[s]);
+    }
+}
+
 void comm_release(scranb200_ctx* ctx) {
     if (ctx->comm) {
         try {
@@ -137,10 +156,10 @@ double* score_sharded(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb
         for (int s = 0; s < W; ++s) m = std::max(m, row_starts[s + 1] - row_starts[s]);
         return m;
     }();
-    // comparison shards: contiguous, equally sized
-    const int64_t qper = (Q + W - 1) / W;
-    auto qlo = [&](int s) { return std::min<int64_t>(Q, s * qper); };
-    const int64_t qa = qlo(r), qb = qlo(r + 1), nq = qb - qa;
+    // comparison shards and block positions
+    std::vector<int64_t> q_starts(W + 1), send_off(W), send_len(W), recv_off(W), recv_len(W);
+    exchange_plan(Q, W, r, row_starts, q_starts.data(), send_off.data(), send_len.data(), recv_off.data(), recv_len.data());
+    const int64_t qa = q_starts[r], qb = q_starts[r + 1], nq = qb - qa;
 
     const size_t K1 = (size_t)std::max(1, K), Q1 = (size_t)std::max(1, Q);
     ctx->eff.reserve(3 * Q1 * (size_t)std::max<int64_t>(1, n) * 8);                 // local effects [3][Q][n]
@@ -168,26 +187,23 @@ double* score_sharded(scranb200_ctx* ctx, const scranb200_mat* mat, const scranb
         SB_NCCL(N.GroupStart());
         for (int s = 0; s < W; ++s) {
             if (s == r) continue;
-            const int64_t qs = qlo(s), nqs = qlo(s + 1) - qs;
-            for (int e = 0; e < 3 && nqs > 0 && n > 0; ++e) {
-                SB_NCCL(N.Send(d_eff + ((size_t)e * Q + qs) * n, (size_t)(nqs * n), ncclDouble, s, comm, ctx->stream));
+            for (int e = 0; e < 3 && send_len[s] > 0; ++e) {
+                SB_NCCL(N.Send(d_eff + (size_t)e * Q * n + send_off[s], (size_t)send_len[s], ncclDouble, s, comm, ctx->stream));
             }
-            const int64_t ns = row_starts[s + 1] - row_starts[s];
-            for (int e = 0; e < 3 && nq > 0 && ns > 0; ++e) {
-                SB_NCCL(N.Recv(d_recv + 3 * (size_t)nq * row_starts[s] + (size_t)e * nq * ns, (size_t)(nq * ns), ncclDouble, s,
-                               comm, ctx->stream));
+            for (int e = 0; e < 3 && recv_len[s] > 0; ++e) {
+                SB_NCCL(N.Recv(d_recv + recv_off[s] + (size_t)e * recv_len[s], (size_t)recv_len[s], ncclDouble, s, comm, ctx->stream));
             }
         }
         SB_NCCL(N.GroupEnd());
-        for (int e = 0; e < 3 && nq > 0 && n > 0; ++e) {  // this rank's own rows of its own columns
-            SB_CUDA(cudaMemcpyAsync(d_recv + 3 * (size_t)nq * g0 + (size_t)e * nq * n, d_eff + ((size_t)e * Q + qa) * n,
-                                    (size_t)(nq * n) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        for (int e = 0; e < 3 && send_len[r] > 0; ++e) {  // this rank's own rows of its own columns
+            SB_CUDA(cudaMemcpyAsync(d_recv + recv_off[r] + (size_t)e * recv_len[r], d_eff + (size_t)e * Q * n + send_off[r],
+                                    (size_t)send_len[r] * 8, cudaMemcpyDeviceToDevice, ctx->stream));
         }
         for (int s = 0; s < W && nq > 0; ++s) {
             const int64_t ns = row_starts[s + 1] - row_starts[s];
             if (ns == 0) continue;
-            SB_LAUNCH(ctx, dist_unpack, (unsigned)ceil_div(3 * nq * ns, 256), 256, 0, d_recv + 3 * (size_t)nq * row_starts[s], ns, nq,
-                      row_starts[s], ngenes, d_full);
+            SB_LAUNCH(ctx, dist_unpack, (unsigned)ceil_div(3 * nq * ns, 256), 256, 0, d_recv + recv_off[s], ns, nq, row_starts[s], ngenes,
+                      d_full);
         }
         d_cols = d_full;
         cols_q0 = qa;
@@ -295,6 +311,18 @@ int scranb200_ctx_comm_init_all(scranb200_ctx** ctxs, int n) {
             SB_NCCL(nccl().CommInitAll(comms.data(), n, devs.data()));
             for (int k = 0; k < n; ++k) ctxs[k]->comm = comms[k];
         }
+    } catch (const std::exception& e) {
+        sb::set_last_error(e.what());
+        return 1;
+    }
+    return 0;
+}
+
+int scranb200_exchange_plan(int64_t Q, int world, int rank, const int64_t* row_starts, int64_t* q_starts, int64_t* send_off,
+                            int64_t* send_len, int64_t* recv_off, int64_t* recv_len) {
+    try {
+        if (world < 1 || rank < 0 || rank >= world || Q < 0) throw Error("bad world size, rank or number of comparisons");
+        exchange_plan(Q, world, rank, row_starts, q_starts, send_off, send_len, recv_off, recv_len);
     } catch (const std::exception& e) {
         sb::set_last_error(e.what());
         return 1;
