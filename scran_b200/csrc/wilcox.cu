@@ -49,6 +49,42 @@ constexpr int MAX_LABELS = 16383;
 constexpr int MAXB = 256;      // units per job at most (also: the 256 value buckets of a large unit)
 constexpr int MAXSEG = 4096;   // segment boundaries staged per job at most
 
+// L2 eviction hints (createpolicy + .L2::cache_hint). The scratch of a unit beyond the shared-memory capacity is
+// written once and read back twice within a few hundred microseconds: it should stay in L2 (evict_last) while the
+// values that stream through the same L2 on their last read should go first (evict_first), or the scratch is
+// pushed out to HBM and fetched back (round 1 / early round 2: 40 GB of the sort's DRAM traffic).
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void st_hint(uint64_t* a, uint64_t v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.b64 [%0], %1, %2;" ::"l"(a), "l"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_hint(uint32_t* a, uint32_t v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(a), "r"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_hint(const uint64_t* a, uint64_t pol) {
+    uint64_t v;
+    asm volatile("ld.global.L2::cache_hint.b64 %0, [%1], %2;" : "=l"(v) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_hint(const uint32_t* a, uint64_t pol) {
+    uint32_t v;
+    asm volatile("ld.global.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ double ld_hint(const double* a, uint64_t pol) {
+    double v;
+    asm volatile("ld.global.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(a), "l"(pol));
+    return v;
+}
+
 struct UnitTables {
     const int64_t* row_ptr;
     const uint32_t* seg_off;
@@ -412,6 +448,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     // body(key, label | role, keep, bucket, segment) for every element of the warp's chunk
     auto for_each_element = [&](bool want_label, auto&& body) {
         if constexpr (SCRATCH) {
+            const uint64_t pol_keep = l2_policy_evict_last();
             for (uint32_t t = c_lo + lane; t < c_hi; t += 128) {  // four loads in flight per thread
                 uint64_t key[4];
                 uint32_t lab[4];
@@ -420,8 +457,8 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                 for (int q = 0; q < 4; ++q) {
                     const uint32_t e = t + q * 32;
                     valid[q] = e < c_hi;
-                    key[q] = valid[q] ? gk[e] : 0ull;
-                    lab[q] = valid[q] && want_label ? (gp[e] & 0xffffu) : 0u;
+                    key[q] = valid[q] ? ld_hint(gk + e, pol_keep) : 0ull;
+                    lab[q] = valid[q] && want_label ? (ld_hint(gp + e, pol_keep) & 0xffffu) : 0u;
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
@@ -830,6 +867,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
             }
             __syncthreads();
             {  // warp chunks, so that the group label of a lane's elements only moves forward
+                const uint64_t pol_keep = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
                 const uint32_t nwarps = blockDim.x / 32;
                 const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
                 const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
@@ -857,7 +895,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                             keep[q] = true;
                             lab[q] = (uint32_t)G;
                             if (k < n) {
-                                v = P.vals[vbase + k];
+                                v = ld_hint(P.vals + vbase + k, pol_stream);  // the last read of these values
                                 keep[q] = v != 0.0;
                                 while (cur_lab + 1u < (uint32_t)G && S.seg[cur_lab + 1u] <= k) ++cur_lab;
                                 lab[q] = cur_lab;
@@ -874,8 +912,8 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                         if (valid[q]) {
                             const unsigned d = value_bucket(key[q], keep[q], vm256, 256u);
                             const uint32_t dst = atomicAdd(&S.gcur[d], 1u);
-                            ga[dst] = key[q];
-                            gp[dst] = lab[q];
+                            st_hint(ga + dst, key[q], pol_keep);
+                            st_hint(gp + dst, lab[q], pol_keep);
                         }
                     }
                 }
