@@ -37,6 +37,10 @@ static void mat_guard(scranb200_ctx* ctx, const scranb200_mat* mat) {
 }
 
 void phase_collect(scranb200_ctx* ctx) {
+    if (ctx->nvtx_open) {
+        nvtxRangePop();
+        ctx->nvtx_open = false;
+    }
     for (int k = 0; k < PH_N; ++k) ctx->timing[k] = 0.0;
     for (int i = 1; i <= ctx->nev; ++i) {
         float ms = 0.f;

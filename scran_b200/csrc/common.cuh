@@ -3,6 +3,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>  // header-only; ranges cost nothing unless a profiler is attached
 #include <stdint.h>
 #include <unistd.h>
 
@@ -76,6 +77,7 @@ struct scranb200_ctx {
     int sm_count = 148;
     size_t smem_optin = 0;
     double timing[sb::PH_N] = {0};
+    bool nvtx_open = false;
     cudaEvent_t ev[16] = {nullptr};
     int ev_phase[16] = {0};
     int nev = 0;
@@ -135,11 +137,20 @@ inline void allow_smem(F kernel, size_t bytes) {
 }
 
 // Device-time accounting: an event at the start of a call and one at the end of each phase.
+// (Each phase is also an NVTX range on the host timeline - "scranb200:<phase>" from the previous mark to this one -
+// so that a timeline profiler groups the launches by phase.)
 inline void phase_begin(scranb200_ctx* ctx) {
     ctx->nev = 0;
     SB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+    if (ctx->nvtx_open) nvtxRangePop();
+    nvtxRangePushA("scranb200:call");
+    ctx->nvtx_open = true;
 }
 inline void phase_mark(scranb200_ctx* ctx, int k) {
+    static const char* const names[PH_N] = {"scranb200:transpose done", "scranb200:stats done", "scranb200:sort done",
+                                            "scranb200:count done", "scranb200:effects done", "scranb200:summaries done",
+                                            "scranb200:minrank done", "scranb200:total"};
+    if (k >= 0 && k < PH_N) nvtxMarkA(names[k]);
     if (ctx->nev >= 15) return;
     ctx->nev++;
     ctx->ev_phase[ctx->nev] = k;
