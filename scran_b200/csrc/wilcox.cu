@@ -399,10 +399,12 @@ __device__ inline void warp_bitonic(uint64_t* k, uint16_t* l, int sz, int lane) 
 //  * larger buckets (many equal values, or a very uneven value distribution) go to a list and
 //    are finished by one warp each: nothing to do if all keys are equal, else a bitonic sort.
 // The bucket index space is the element index space: bucket off[s] + b of segment s.
-// SCRATCH = false: segments are whole units, elements are read from K1's values;
-// SCRATCH = true:  one run of consecutive coarse buckets of ONE large unit, which the split left in
-//                  global memory (gk, gp: the run's first element). There are no segments: the fine
-//                  bucket of a value follows from the unit-wide coarse offsets (fine_bucket()).
+// MODE 0: segments are whole units, elements are read from K1's values;
+// MODE 1: one run of consecutive coarse buckets of ONE large unit, which the 256-way split left in
+//         global memory (gk, gp: the run's first element). There are no segments: the fine
+//         bucket of a value follows from the unit-wide coarse offsets (fine_bucket());
+// MODE 2: one value range of ONE large unit, which the sample split left in global memory: as many
+//         equal-width buckets over the range (run.vm) as it has entries; no dropped entries.
 struct ScratchRun {
     uint32_t start;  // position of the run inside the unit (= its first fine bucket)
     uint32_t lim;    // entries of the run that belong to the stream (the stored zeros at the very end do not)
@@ -431,9 +433,17 @@ __device__ __forceinline__ uint32_t fine_bucket(uint64_t key, const uint32_t* bo
     return lo + min(__double2uint_rz(frac * (double)c), c - 1u);
 }
 
-template <bool SCRATCH>
+template <int MODE>
 __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, uint32_t total, const uint64_t* gk,
                                 const uint32_t* gp, const ScratchRun run) {
+    constexpr bool SCRATCH = MODE != 0;
+    auto scratch_bucket = [&](uint64_t key) -> uint32_t {
+        if constexpr (MODE == 1) {
+            return fine_bucket(key, S.boff, run.vm) - run.start;
+        } else {
+            return value_bucket(key, true, run.vm, total);
+        }
+    };
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool two_roles = P.ut.mult == 2;
     uint16_t* bh = reinterpret_cast<uint16_t*>(S.bk);
@@ -462,7 +472,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
-                    if (valid[q]) body(key[q], lab[q], key[q] != ~0ull, fine_bucket(key[q], S.boff, run.vm) - run.start, 0);
+                    if (valid[q]) body(key[q], lab[q], key[q] != ~0ull, scratch_bucket(key[q]), 0);
             }
         } else {
             if (c_lo >= c_hi) return;
@@ -616,7 +626,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     if constexpr (SCRATCH) {
         for (uint32_t p = c_lo + lane; p < c_hi; p += 32) {
             const uint64_t key = S.key[p];
-            rank_element(p, key, fine_bucket(key, S.boff, run.vm) - run.start, 0u, run.lim, run.out);
+            rank_element(p, key, scratch_bucket(key), 0u, run.lim, run.out);
         }
     } else if (c_lo < c_hi) {
         int s = find_segment(S.off, nb, c_lo);
@@ -682,6 +692,156 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
             }
         }
     }
+}
+
+// A unit beyond the shared-memory capacity, first choice: split it by value into R ranges of about
+// three quarters of the capacity each, with ONE pass over its values. The range boundaries are the
+// quantiles of a sorted sample (SPLIT_SAMPLES per range, taken at equal strides over the unit, so every
+// group is represented in proportion); an entry finds its range by binary search over the R - 1 splitter
+// keys (integers: no floating point), a warp appends what it has for a range with one shared-memory
+// atomic, and every range has room for `cap` entries in the CTA's scratch. Each range is then sorted in
+// shared memory like a small unit (as many equal-width value buckets as it has entries). Equal keys
+// share a range, so ties never straddle one. Returns false - and has written nothing that matters - if
+// some range came out larger than the capacity (a heavily tied value, or an unlucky sample): the caller
+// then takes the exact 256-way split below.
+constexpr uint32_t SPLIT_SAMPLES = 256;    // per range (a power of two); the counts then vary by about 1/16
+constexpr uint32_t SPLIT_MAX_RANGES = 64;
+
+__device__ bool sample_split_unit(const SortParams& P, const SortSmem& S, uint32_t total, int64_t vbase, uint32_t n,
+                                  int G, int64_t soff, uint64_t* ga, uint32_t* gp, double fmin, double fmax, uint32_t R,
+                                  uint32_t* m_out) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t cap = (uint32_t)P.cap;
+    uint32_t Rp = 2;
+    while (Rp < R) Rp <<= 1;
+    const uint32_t ns = Rp * SPLIT_SAMPLES;
+    uint64_t* sk = S.key;                                    // the sample (ns <= cap keys)
+    uint64_t* sp = reinterpret_cast<uint64_t*>(S.scale);     // splitters: sp[j] = smallest key of range j (j >= 1)
+
+    for (uint32_t i = tid; i < ns; i += blockDim.x) {
+        uint64_t key;
+        bool keep;
+        unit_key(P.vals, vbase, n, P.shift, (uint32_t)(((uint64_t)i * total) / ns), key, keep);
+        sk[i] = key;  // stored zeros carry ~0 and sort last
+    }
+    if (tid == 0) S.misc[6] = 0;
+    __syncthreads();
+    for (uint32_t k = 2; k <= ns; k <<= 1) {  // bitonic sort of the sample
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t p = tid; p < (ns >> 1); p += blockDim.x) {
+                const uint32_t i = ((p & ~(j - 1u)) << 1) | (p & (j - 1u)), x = i | j;
+                const uint64_t a = sk[i], b = sk[x];
+                if ((a > b) == ((i & k) == 0u)) {
+                    sk[i] = b;
+                    sk[x] = a;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    for (uint32_t i = tid; i < ns; i += blockDim.x)  // sampled entries that are part of the stream
+        if (sk[i] != ~0ull && (i + 1u == ns || sk[i + 1u] == ~0ull)) S.misc[6] = i + 1u;
+    __syncthreads();
+    const uint32_t nv = S.misc[6];
+    if (nv < 8u * R) return false;
+    if (tid < 256) S.gcur[tid] = 0;
+    if ((uint32_t)tid < Rp) sp[tid] = tid == 0 ? 0ull : (uint32_t)tid < R ? sk[(size_t)(((uint64_t)tid * nv) / R)] : ~0ull;
+    __syncthreads();
+
+    // ---- the one pass: every entry to the next free place of its range ----
+    {
+        const uint64_t pol_keep = l2_policy_evict_last();
+        const uint32_t nwarps = blockDim.x / 32;
+        const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
+        const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
+        const unsigned below = (1u << lane) - 1u;
+        uint32_t cur_lab = 0;
+        bool cur_role = false;
+        for (uint32_t t = c_lo; t < c_hi; t += 128) {  // the whole warp takes every step: match_any needs all lanes
+            uint64_t key[4];
+            uint32_t lab[4];
+            bool keep[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t e = t + lane + q * 32;
+                key[q] = ~0ull;
+                lab[q] = 0;
+                keep[q] = false;
+                if (e < c_hi) {
+                    const bool role = e > n;
+                    const uint32_t k = role ? e - (n + 1u) : e;
+                    if (role != cur_role) {
+                        cur_role = role;
+                        cur_lab = 0;
+                    }
+                    double v = 0.0;
+                    keep[q] = true;
+                    lab[q] = (uint32_t)G;
+                    if (k < n) {
+                        v = P.vals[vbase + k];
+                        keep[q] = v != 0.0;
+                        while (cur_lab + 1u < (uint32_t)G && S.seg[cur_lab + 1u] <= k) ++cur_lab;
+                        lab[q] = cur_lab;
+                    }
+                    if (role) {
+                        v = v - P.shift;
+                        lab[q] |= ROLE_L;
+                    }
+                    key[q] = key_of(v);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t r = 0xffffffffu;
+                if (keep[q]) {
+                    r = 0;
+                    for (uint32_t step = Rp >> 1; step > 0; step >>= 1)
+                        if (sp[r + step] <= key[q]) r += step;
+                    r = min(r, R - 1u);
+                }
+                const unsigned peers = __match_any_sync(0xffffffffu, r);
+                const int leader = __ffs(peers) - 1;
+                uint32_t base = 0;
+                if (lane == leader && keep[q]) base = atomicAdd(&S.gcur[r], (uint32_t)__popc(peers));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                const uint32_t pos = base + (uint32_t)__popc(peers & below);
+                if (keep[q] && pos < cap) {
+                    st_hint(ga + (size_t)r * cap + pos, key[q], pol_keep);
+                    st_hint(gp + (size_t)r * cap + pos, lab[q], pol_keep);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t run = 0, ok = 1;
+        for (uint32_t r = 0; r < R; ++r) {
+            const uint32_t c = S.gcur[r];
+            S.boff[r] = run;
+            run += c;
+            ok &= c <= cap ? 1u : 0u;
+        }
+        S.boff[R] = run;
+        S.misc[7] = ok;
+    }
+    __syncthreads();
+    if (!S.misc[7]) return false;
+    *m_out = S.boff[R];
+
+    // ---- every range through shared memory ----
+    for (uint32_t r = 0; r < R; ++r) {
+        const uint32_t cnt = S.gcur[r];
+        if (cnt == 0) continue;
+        const double lo = r == 0 ? fmin : value_of(sp[r]), hi = r + 1u == R ? fmax : value_of(sp[r + 1u]);
+        ScratchRun run;
+        run.start = 0;
+        run.lim = cnt;
+        run.out = soff + S.boff[r];
+        run.vm = {lo, hi, hi > lo && cnt >= 3u ? (double)(cnt - 2u) / (hi - lo) : 0.0};
+        __syncthreads();
+        bucket_sort_job<2>(P, S, 1, cnt, ga + (size_t)r * cap, gp + (size_t)r * cap, run);
+    }
+    return true;
 }
 
 __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
@@ -792,7 +952,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
 
         if (total <= (uint32_t)P.cap) {
             // ---- shared-memory path: all units of the job at once -----------------------------
-            bucket_sort_job<false>(P, S, nb, total, nullptr, nullptr, ScratchRun());
+            bucket_sort_job<0>(P, S, nb, total, nullptr, nullptr, ScratchRun());
             if (tid < nb) P.unit_m[t0 + tid] = (S.off[tid + 1] - S.off[tid]) - S.drop[tid];
             continue;
         }
@@ -809,6 +969,17 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         uint64_t* gb = P.g_kb + (size_t)blockIdx.x * P.scratch_len;
         uint32_t* gq = P.g_pb + (size_t)blockIdx.x * P.scratch_len;
         const double fmin = reinterpret_cast<double*>(S.scan)[0], fmax = reinterpret_cast<double*>(S.scan)[1];
+        {
+            const uint32_t per = (uint32_t)P.cap - (uint32_t)P.cap / 4u;
+            const uint32_t R = (total + per - 1u) / per;
+            uint32_t m_split = 0;
+            if (R <= SPLIT_MAX_RANGES && (int64_t)R * P.cap <= P.scratch_len && fmax > fmin &&
+                sample_split_unit(P, S, total, vbase, n, G, soff, ga, gp, fmin, fmax, R, &m_split)) {
+                if (tid == 0) P.unit_m[t0] = m_split;
+                continue;
+            }
+            __syncthreads();
+        }
         const ValueMap vm256 = {fmin, fmax, fmax > fmin ? 254.0 / (fmax - fmin) : 0.0};
         if (tid == 0) S.misc[3] = 0;  // dropped (stored zero) entries, counted in pass 1
         __syncthreads();
@@ -945,7 +1116,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
                 run.lim = m > start ? min(cnt, m - start) : 0u;
                 run.out = soff + start;
                 run.vm = vm256;
-                bucket_sort_job<true>(P, S, 1, cnt, ga + start, gp + start, run);
+                bucket_sort_job<1>(P, S, 1, cnt, ga + start, gp + start, run);
                 continue;
             }
             // a single coarse bucket larger than shared memory (e.g. one heavily tied value): radix sort
@@ -1906,7 +2077,8 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     sp.g_ka = sp.g_kb = nullptr;
     sp.g_pa = sp.g_pb = nullptr;
     const int sort_grid = (int)std::min<int64_t>(ntasks, (int64_t)ctx->sm_count);
-    sp.scratch_len = (max_m + 63) & ~int64_t(63);
+    // room for the sample split: up to SPLIT_MAX_RANGES ranges of `cap` entries, three quarters full on average
+    sp.scratch_len = (std::max(max_m, std::min(max_m + max_m / 3 + 2 * (int64_t)cap_large, (int64_t)(SPLIT_MAX_RANGES + 1) * cap_large)) + 63) & ~int64_t(63);
     if (max_m > cap_large) {  // some unit may not fit shared memory: a scratch region per CTA, sized for the largest unit
         const size_t all = (size_t)sort_grid * (size_t)sp.scratch_len;
         ctx->sort_keys.reserve(all * 16 + 64);
