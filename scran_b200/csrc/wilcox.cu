@@ -167,7 +167,8 @@ __global__ void __launch_bounds__(1024) k3_plan(UnitTables ut, uint32_t small_ma
 // tail of the launch (longest-processing-time-first over ORDER_CLASSES + 1 classes).
 constexpr int ORDER_CLASSES = 6;
 __global__ void __launch_bounds__(1024) k3_order(UnitTables ut, const int32_t* jobs, const int32_t* njobs_ptr,
-                                                  uint32_t big_total, int32_t* order, int32_t* nbig_out) {
+                                                  uint32_t big_total, int32_t* order, int2* order_range,
+                                                  int32_t* nbig_out) {
     __shared__ int part[ORDER_CLASSES + 1][1024];
     __shared__ int class_base[ORDER_CLASSES + 2];
     const int njobs = *njobs_ptr;
@@ -218,7 +219,10 @@ __global__ void __launch_bounds__(1024) k3_order(UnitTables ut, const int32_t* j
         const int cl = class_of(j);
 #pragma unroll
         for (int c = 0; c <= ORDER_CLASSES; ++c)
-            if (cl == c) order[at[c]++] = j;
+            if (cl == c) {
+                order_range[at[c]] = make_int2(jobs[j], jobs[j + 1]);  // what k3_sort needs of the job, in one load
+                order[at[c]++] = j;
+            }
     }
 }
 
@@ -239,6 +243,7 @@ struct SortParams {
     const int32_t* jobs;
     const int32_t* njobs;
     const int32_t* order;
+    const int2* order_range;  // (first task, end task) of the jobs in `order`
     unsigned long long* job_counter;
 };
 
@@ -451,7 +456,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     // elements a step: what belongs to the unit (offsets, value range, group boundaries) is loaded
     // once and is the same for all lanes, and the group label of a lane's elements only ever moves
     // forward, so a cursor replaces the binary search.
-    const uint32_t nwarps = blockDim.x / 32;
+    constexpr uint32_t nwarps = SORT_THREADS / 32;  // (the kernel is launched with SORT_THREADS threads)
     const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
     const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
 
@@ -542,7 +547,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
     {
         // a thread owns a multiple of 8 counters = whole 16-byte words (counters past `total` are zero
         // up to the end of the last 32-bit word; the words beyond that are never read)
-        const uint32_t per = ((total + blockDim.x * 8u - 1u) / (blockDim.x * 8u)) * 8u;
+        const uint32_t per = ((total + SORT_THREADS * 8u - 1u) / (SORT_THREADS * 8u)) * 8u;
         const uint32_t lo = min(total, (uint32_t)tid * per), hi = min(total, lo + per);
         uint32_t sum = 0;
         for (uint32_t i = lo; i < hi; i += 8) {
@@ -573,11 +578,35 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
         }
         __syncthreads();
         uint32_t at = (warp ? S.scan[warp - 1] : 0u) + incl - sum;
-        for (uint32_t i = lo; i < hi; ++i) {
-            const uint32_t c = bh[i];
-            bh[i] = (uint16_t)at;
-            at += c;
-            if (c > (uint32_t)BUCKET_RANK_MAX) S.biglist[atomicAdd(&S.misc[5], 1u)] = i;
+        for (uint32_t i = lo; i < hi; i += 8) {
+            if (i + 8 <= hi) {  // eight counters = one 16-byte word in, one out
+                const uint4 w = *reinterpret_cast<const uint4*>(bh + i);
+                const uint32_t in[4] = {w.x, w.y, w.z, w.w};
+                uint32_t outw[4];
+                bool big = false;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t c0 = in[q] & 0xffffu, c1 = in[q] >> 16;
+                    outw[q] = (at & 0xffffu) | ((at + c0) << 16);
+                    at += c0 + c1;
+                    big |= c0 > (uint32_t)BUCKET_RANK_MAX || c1 > (uint32_t)BUCKET_RANK_MAX;
+                }
+                *reinterpret_cast<uint4*>(bh + i) = make_uint4(outw[0], outw[1], outw[2], outw[3]);
+                if (big) {
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const uint32_t c = (in[q >> 1] >> ((q & 1) * 16)) & 0xffffu;
+                        if (c > (uint32_t)BUCKET_RANK_MAX) S.biglist[atomicAdd(&S.misc[5], 1u)] = i + q;
+                    }
+                }
+            } else {
+                for (uint32_t k = i; k < hi; ++k) {
+                    const uint32_t c = bh[k];
+                    bh[k] = (uint16_t)at;
+                    at += c;
+                    if (c > (uint32_t)BUCKET_RANK_MAX) S.biglist[atomicAdd(&S.misc[5], 1u)] = k;
+                }
+            }
         }
     }
     __syncthreads();
@@ -696,15 +725,17 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
 
 // A unit beyond the shared-memory capacity, first choice: split it by value into R ranges of about
 // three quarters of the capacity each, with ONE pass over its values. The range boundaries are the
-// quantiles of a sorted sample (SPLIT_SAMPLES per range, taken at equal strides over the unit, so every
-// group is represented in proportion); an entry finds its range by binary search over the R - 1 splitter
+// quantiles of a sample (SPLIT_SAMPLES per range, taken at equal strides over the unit, so every group
+// is represented in proportion), read off a histogram of the sample over SPLIT_BINS equal-width value
+// bins: a boundary is the lower edge of a bin; an entry finds its range by binary search over the R - 1 splitter
 // keys (integers: no floating point), a warp appends what it has for a range with one shared-memory
 // atomic, and every range has room for `cap` entries in the CTA's scratch. Each range is then sorted in
 // shared memory like a small unit (as many equal-width value buckets as it has entries). Equal keys
 // share a range, so ties never straddle one. Returns false - and has written nothing that matters - if
 // some range came out larger than the capacity (a heavily tied value, or an unlucky sample): the caller
 // then takes the exact 256-way split below.
-constexpr uint32_t SPLIT_SAMPLES = 256;    // per range (a power of two); the counts then vary by about 1/16
+constexpr uint32_t SPLIT_SAMPLES = 512;    // per range; the counts of the ranges then vary by about 1/22
+constexpr uint32_t SPLIT_BINS = 8192;      // value bins of the sample histogram
 constexpr uint32_t SPLIT_MAX_RANGES = 64;
 
 __device__ bool sample_split_unit(const SortParams& P, const SortSmem& S, uint32_t total, int64_t vbase, uint32_t n,
@@ -715,43 +746,82 @@ __device__ bool sample_split_unit(const SortParams& P, const SortSmem& S, uint32
     uint32_t Rp = 2;
     while (Rp < R) Rp <<= 1;
     const uint32_t ns = Rp * SPLIT_SAMPLES;
-    uint64_t* sk = S.key;                                    // the sample (ns <= cap keys)
     uint64_t* sp = reinterpret_cast<uint64_t*>(S.scale);     // splitters: sp[j] = smallest key of range j (j >= 1)
 
+    // ---- histogram of the sample over SPLIT_BINS equal-width value bins, prefix sums, quantiles ----
+    uint16_t* bh = reinterpret_cast<uint16_t*>(S.bk);
+    const ValueMap vs = {fmin, fmax, (double)(SPLIT_BINS - 2u) / (fmax - fmin)};
+    for (uint32_t i = tid; i < SPLIT_BINS / 2u; i += blockDim.x) S.bk[i] = 0;
+    __syncthreads();
     for (uint32_t i = tid; i < ns; i += blockDim.x) {
         uint64_t key;
         bool keep;
         unit_key(P.vals, vbase, n, P.shift, (uint32_t)(((uint64_t)i * total) / ns), key, keep);
-        sk[i] = key;  // stored zeros carry ~0 and sort last
-    }
-    if (tid == 0) S.misc[6] = 0;
-    __syncthreads();
-    for (uint32_t k = 2; k <= ns; k <<= 1) {  // bitonic sort of the sample
-        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-            for (uint32_t p = tid; p < (ns >> 1); p += blockDim.x) {
-                const uint32_t i = ((p & ~(j - 1u)) << 1) | (p & (j - 1u)), x = i | j;
-                const uint64_t a = sk[i], b = sk[x];
-                if ((a > b) == ((i & k) == 0u)) {
-                    sk[i] = b;
-                    sk[x] = a;
-                }
-            }
-            __syncthreads();
+        if (keep) {  // stored zeros are not part of the stream
+            const uint32_t b = value_bucket(key, true, vs, SPLIT_BINS);
+            atomicAdd(&S.bk[b >> 1], 1u << ((b & 1u) * 16u));
         }
     }
-    for (uint32_t i = tid; i < ns; i += blockDim.x)  // sampled entries that are part of the stream
-        if (sk[i] != ~0ull && (i + 1u == ns || sk[i + 1u] == ~0ull)) S.misc[6] = i + 1u;
     __syncthreads();
-    const uint32_t nv = S.misc[6];
+    {  // exclusive prefix sums in place: eight bins per thread
+        static_assert(SPLIT_BINS == 8u * SORT_THREADS, "one 16-byte word of bins per thread");
+        const uint4 w = *reinterpret_cast<const uint4*>(bh + tid * 8);
+        const uint32_t in[4] = {w.x, w.y, w.z, w.w};
+        uint32_t sum = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) sum += (in[q] & 0xffffu) + (in[q] >> 16);
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) S.scan[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t v = S.scan[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += y;
+            }
+            S.scan[lane] = v;
+        }
+        __syncthreads();
+        uint32_t at = (warp ? S.scan[warp - 1] : 0u) + incl - sum;
+        uint32_t outw[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t c0 = in[q] & 0xffffu, c1 = in[q] >> 16;
+            outw[q] = (at & 0xffffu) | ((at + c0) << 16);
+            at += c0 + c1;
+        }
+        *reinterpret_cast<uint4*>(bh + tid * 8) = make_uint4(outw[0], outw[1], outw[2], outw[3]);
+    }
+    const uint32_t nv = S.scan[31];  // sampled entries that are part of the stream
+    __syncthreads();
     if (nv < 8u * R) return false;
     if (tid < 256) S.gcur[tid] = 0;
-    if ((uint32_t)tid < Rp) sp[tid] = tid == 0 ? 0ull : (uint32_t)tid < R ? sk[(size_t)(((uint64_t)tid * nv) / R)] : ~0ull;
+    if ((uint32_t)tid < Rp) {
+        // splitter j = lower edge of the bin that holds the sample of rank j nv / R: the last bin whose prefix is <= that rank
+        uint64_t key = tid == 0 ? 0ull : ~0ull;
+        if (tid > 0 && (uint32_t)tid < R) {
+            const uint32_t want = (uint32_t)(((uint64_t)tid * nv) / R);
+            uint32_t lo = 0, hi = SPLIT_BINS;
+            while (hi - lo > 1u) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if ((uint32_t)bh[mid] <= want) lo = mid; else hi = mid;
+            }
+            key = lo == 0 ? 0ull : key_of(fmin + (double)(lo - 1u) / vs.scale);
+        }
+        sp[tid] = key;
+    }
     __syncthreads();
 
     // ---- the one pass: every entry to the next free place of its range ----
     {
         const uint64_t pol_keep = l2_policy_evict_last();
-        const uint32_t nwarps = blockDim.x / 32;
+        constexpr uint32_t nwarps = SORT_THREADS / 32;
         const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
         const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
         const unsigned below = (1u << lane) - 1u;
@@ -844,6 +914,11 @@ __device__ bool sample_split_unit(const SortParams& P, const SortSmem& S, uint32
     return true;
 }
 
+#ifndef SB_SORT_JOB_BATCH
+#define SB_SORT_JOB_BATCH 4
+#endif
+constexpr int SORT_JOB_BATCH = SB_SORT_JOB_BATCH;
+
 __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const SortSmem S = carve_sort_smem(smem_raw, P.cap, P.segcap);
@@ -852,13 +927,25 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
     const UnitTables& ut = P.ut;
     const double inf = __longlong_as_double(0x7ff0000000000000ll);
 
+    // Jobs are taken SORT_JOB_BATCH at a time (one round trip to the global counter per batch), and a job's
+    // task range comes with its place in the order (one load instead of order -> jobs).
+    if (tid == 0) S.misc[8] = S.misc[9] = 0;  // next job of the batch, end of the batch
     while (true) {
         __syncthreads();
-        if (tid == 0) S.misc[0] = (uint32_t)atomicAdd(P.job_counter, 1ull);
+        if (tid == 0) {
+            uint32_t b = S.misc[8], e = S.misc[9];
+            if (b == e) {
+                b = (uint32_t)min(atomicAdd(P.job_counter, (unsigned long long)SORT_JOB_BATCH), (unsigned long long)njobs);
+                e = min(b + (uint32_t)SORT_JOB_BATCH, (uint32_t)njobs);
+                S.misc[9] = e;
+            }
+            S.misc[0] = b;
+            S.misc[8] = b < e ? b + 1u : b;
+        }
         __syncthreads();
         if ((int)S.misc[0] >= njobs) break;
-        const int job = P.order[S.misc[0]];
-        const int64_t t0 = P.jobs[job], t1 = P.jobs[job + 1];
+        const int2 jr = P.order_range[S.misc[0]];
+        const int64_t t0 = jr.x, t1 = jr.y;
         const int nb = (int)(t1 - t0);
 
         // ---- per-unit tables -------------------------------------------------------------
@@ -970,10 +1057,13 @@ __global__ void __launch_bounds__(SORT_THREADS) k3_sort(SortParams P) {
         uint32_t* gq = P.g_pb + (size_t)blockIdx.x * P.scratch_len;
         const double fmin = reinterpret_cast<double*>(S.scan)[0], fmax = reinterpret_cast<double*>(S.scan)[1];
         {
-            const uint32_t per = (uint32_t)P.cap - (uint32_t)P.cap / 4u;
+#ifndef SB_SPLIT_SLACK_DIV
+#define SB_SPLIT_SLACK_DIV 4
+#endif
+            const uint32_t per = (uint32_t)P.cap - (uint32_t)P.cap / (unsigned)SB_SPLIT_SLACK_DIV;
             const uint32_t R = (total + per - 1u) / per;
             uint32_t m_split = 0;
-            if (R <= SPLIT_MAX_RANGES && (int64_t)R * P.cap <= P.scratch_len && fmax > fmin &&
+            if (R <= SPLIT_MAX_RANGES && (int64_t)R * P.cap <= P.scratch_len && fmax > fmin && (uint32_t)P.cap >= SPLIT_BINS &&
                 sample_split_unit(P, S, total, vbase, n, G, soff, ga, gp, fmin, fmax, R, &m_split)) {
                 if (tid == 0) P.unit_m[t0] = m_split;
                 continue;
@@ -2027,7 +2117,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
 
     ctx->stream_lab.reserve((size_t)stream_len * 2 + 64);
     ctx->unit_m.reserve((size_t)ntasks * 4 + 64);
-    ctx->jobs.reserve((size_t)(ntasks + 2) * 8 + 64);
+    ctx->jobs.reserve((size_t)(ntasks + 2) * 16 + 64);  // jobs | order | (first, end) task of the jobs in order
     ctx->flags.reserve(64);
     unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->flags.as<char>() + 16);
     int32_t* njobs = reinterpret_cast<int32_t*>(ctx->flags.as<char>() + 32);
@@ -2052,7 +2142,8 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     const uint32_t small_max = (uint32_t)cap_large / 2, window = (uint32_t)cap_large - small_max;
     const int maxb = std::max(1, std::min(MAXB, segcap / (L.maxG + 1)));
     SB_LAUNCH(ctx, k3_plan, 1, 1024, 0, ut, small_max, window, maxb, jobs, njobs);
-    SB_LAUNCH(ctx, k3_order, 1, 1024, 0, ut, jobs, njobs, 16384u, order, nbig);
+    int2* order_range = reinterpret_cast<int2*>(order + (ntasks + 2));
+    SB_LAUNCH(ctx, k3_order, 1, 1024, 0, ut, jobs, njobs, 16384u, order, order_range, nbig);
 
     // ---- sort ----
     int64_t max_cells = 0;
@@ -2091,6 +2182,7 @@ void run_wilcox(scranb200_ctx* ctx, const Transposed& T, const PairLayout& L, do
     sp.jobs = jobs;
     sp.njobs = njobs;
     sp.order = order;
+    sp.order_range = order_range;
     sp.job_counter = counter;
     allow_smem(k3_sort, (size_t)cap_large * 12 + sort_fixed_bytes(cap_large, segcap));
     sp.cap = cap_large;
