@@ -499,7 +499,7 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                     if (part_lo >= part_hi) continue;
                     const uint32_t k_lo = part_lo - base, k_hi = min(part_hi - base, n);
                     const uint32_t rolebit = role ? ROLE_L : 0u;
-                    uint32_t lab = 0;
+                    uint32_t lab = 0, next_b = want_label && G > 1u ? segb[1] : 0xffffffffu;  // first position of the next group
                     for (uint32_t k = k_lo + lane; k < k_hi; k += 128) {  // four loads in flight per thread
                         double v[4];
                         bool ok[4];
@@ -513,8 +513,9 @@ __device__ void bucket_sort_job(const SortParams& P, const SortSmem& S, int nb, 
                             if (ok[q]) {
                                 const uint32_t kk = k + 32 * q;
                                 const bool keep = v[q] != 0.0;  // stored zeros count as zeros (src/overlap_exprs.cpp:43-47)
-                                if (want_label) {
-                                    while (lab + 1u < G && segb[lab + 1u] <= kk) ++lab;  // label = last boundary <= kk
+                                while (kk >= next_b) {  // label = last boundary <= kk
+                                    ++lab;
+                                    next_b = lab + 1u < G ? segb[lab + 1u] : 0xffffffffu;
                                 }
                                 const double vv = role ? v[q] - P.shift : v[q];
                                 const uint64_t key = keep ? key_of(vv) : ~0ull;
@@ -820,64 +821,77 @@ __device__ bool sample_split_unit(const SortParams& P, const SortSmem& S, uint32
 
     // ---- the one pass: every entry to the next free place of its range ----
     {
+#ifndef SB_SPLIT_LOADS
+#define SB_SPLIT_LOADS 4
+#endif
+        constexpr int U = SB_SPLIT_LOADS;  // loads in flight per thread
         const uint64_t pol_keep = l2_policy_evict_last();
+#ifdef SB_SPLIT_EVICT_FIRST
+        const uint64_t pol_stream = l2_policy_evict_first();
+#endif
         constexpr uint32_t nwarps = SORT_THREADS / 32;
-        const uint32_t chunk = ((total + nwarps * 128u - 1u) / (nwarps * 128u)) * 128u;
+        const uint32_t chunk = ((total + nwarps * 32u * U - 1u) / (nwarps * 32u * U)) * 32u * U;
         const uint32_t c_lo = min(total, (uint32_t)warp * chunk), c_hi = min(total, c_lo + chunk);
         const unsigned below = (1u << lane) - 1u;
-        uint32_t cur_lab = 0;
+        const bool two_roles = P.ut.mult == 2;
+        // group label of the lane's entries: moves forward only; next_b = first position of the next group
+        uint32_t cur_lab = 0, next_b = G > 1 ? S.seg[1] : 0xffffffffu;
         bool cur_role = false;
-        for (uint32_t t = c_lo; t < c_hi; t += 128) {  // the whole warp takes every step: match_any needs all lanes
-            uint64_t key[4];
-            uint32_t lab[4];
-            bool keep[4];
+        for (uint32_t t = c_lo; t < c_hi; t += 32u * U) {  // the whole warp takes every step: match_any needs all lanes
+            double v[U];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < U; ++q) {
                 const uint32_t e = t + lane + q * 32;
-                key[q] = ~0ull;
-                lab[q] = 0;
-                keep[q] = false;
-                if (e < c_hi) {
-                    const bool role = e > n;
-                    const uint32_t k = role ? e - (n + 1u) : e;
-                    if (role != cur_role) {
-                        cur_role = role;
-                        cur_lab = 0;
-                    }
-                    double v = 0.0;
-                    keep[q] = true;
-                    lab[q] = (uint32_t)G;
-                    if (k < n) {
-                        v = P.vals[vbase + k];
-                        keep[q] = v != 0.0;
-                        while (cur_lab + 1u < (uint32_t)G && S.seg[cur_lab + 1u] <= k) ++cur_lab;
-                        lab[q] = cur_lab;
-                    }
-                    if (role) {
-                        v = v - P.shift;
-                        lab[q] |= ROLE_L;
-                    }
-                    key[q] = key_of(v);
-                }
+                const uint32_t k = e > n ? e - (n + 1u) : e;
+#ifdef SB_SPLIT_EVICT_FIRST
+                v[q] = e < c_hi && k < n ? ld_hint(P.vals + vbase + k, pol_stream) : 1.0;
+#else
+                v[q] = e < c_hi && k < n ? P.vals[vbase + k] : 1.0;  // (the probes are not stored zeros)
+#endif
             }
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < U; ++q) {
+                const uint32_t e = t + lane + q * 32;
+                const bool valid = e < c_hi;
+                const bool role = e > n;
+                const uint32_t k = role ? e - (n + 1u) : e;
+                uint32_t lab = (uint32_t)G;
+                double x = 0.0;
+                if (two_roles && valid && role != cur_role) {
+                    cur_role = role;
+                    cur_lab = 0;
+                    next_b = G > 1 ? S.seg[1] : 0xffffffffu;
+                }
+                if (valid && k < n) {
+                    while (k >= next_b) {
+                        ++cur_lab;
+                        next_b = cur_lab + 1u < (uint32_t)G ? S.seg[cur_lab + 1u] : 0xffffffffu;
+                    }
+                    lab = cur_lab;
+                    x = v[q];
+                }
+                const bool keep = valid && v[q] != 0.0;  // stored zeros are not part of the stream
+                if (role) {
+                    x = x - P.shift;
+                    lab |= ROLE_L;
+                }
+                const uint64_t key = key_of(x);
                 uint32_t r = 0xffffffffu;
-                if (keep[q]) {
+                if (keep) {
                     r = 0;
                     for (uint32_t step = Rp >> 1; step > 0; step >>= 1)
-                        if (sp[r + step] <= key[q]) r += step;
+                        if (sp[r + step] <= key) r += step;
                     r = min(r, R - 1u);
                 }
                 const unsigned peers = __match_any_sync(0xffffffffu, r);
                 const int leader = __ffs(peers) - 1;
                 uint32_t base = 0;
-                if (lane == leader && keep[q]) base = atomicAdd(&S.gcur[r], (uint32_t)__popc(peers));
+                if (lane == leader && keep) base = atomicAdd(&S.gcur[r], (uint32_t)__popc(peers));
                 base = __shfl_sync(0xffffffffu, base, leader);
                 const uint32_t pos = base + (uint32_t)__popc(peers & below);
-                if (keep[q] && pos < cap) {
-                    st_hint(ga + (size_t)r * cap + pos, key[q], pol_keep);
-                    st_hint(gp + (size_t)r * cap + pos, lab[q], pol_keep);
+                if (keep && pos < cap) {
+                    st_hint(ga + (size_t)r * cap + pos, key, pol_keep);
+                    st_hint(gp + (size_t)r * cap + pos, lab, pol_keep);
                 }
             }
         }
