@@ -447,6 +447,12 @@ def main():
     w = dict(WORKLOADS[args.workload])
     args.warmup = max(args.warmup, 0)
 
+    # stdout carries the JSON line and nothing else: whatever libraries print on file descriptor 1 while the
+    # job runs (NCCL's version banner, for one) goes to stderr; Python's own prints still reach the real stdout
+    sys.stdout.flush()
+    sys.stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
     if args.workload == "config4":
         run_config4(args, w)
         return
