@@ -22,7 +22,11 @@ namespace {
 constexpr int K1_THREADS = 1024;
 constexpr int K1_SUB_SHIFT = 8;  // gene sub-ranges of 256: one scatter warp each
 constexpr int K1_SUB = 1 << K1_SUB_SHIFT;
-constexpr int K1_MAXCOLS = MAX_CHUNK_COLS;  // columns per chunk (their bounds are staged in shared memory)
+constexpr int K1_MAXCOLS = MAX_CHUNK_COLS;
+#ifndef SB_K1C_LOADS
+#define SB_K1C_LOADS 16
+#endif
+constexpr int K1C_LOADS = SB_K1C_LOADS;  // columns per chunk (their bounds are staged in shared memory)
 
 // Stages the bounds of the chunk's columns in shared memory. Returns the number of columns.
 __device__ inline int stage_bounds(const int64_t* __restrict__ p, const int32_t* __restrict__ perm, int c_lo, int c_hi,
@@ -40,7 +44,7 @@ __device__ inline int stage_bounds(const int64_t* __restrict__ p, const int32_t*
 // Pass A: table[chunk][gene] = stored entries of `gene` in the chunk's columns. Counting does not
 // care about order, so the warps of a CTA take columns independently (32 columns in flight per
 // CTA) and bump the shared-memory counters with atomics; no barrier between columns.
-__global__ void __launch_bounds__(K1_THREADS)
+__global__ void __launch_bounds__(K1_THREADS, 1)
 k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const int32_t* __restrict__ perm,
          const int32_t* __restrict__ chunk_start, int ngenes, int g0, int glen, uint32_t* __restrict__ table,
          int* __restrict__ bad, uint32_t* __restrict__ sub_split, int nsub) {
@@ -65,15 +69,16 @@ k1_count(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const i
         if (srow && n == 0) {
             for (int r = lane; r <= nsub; r += 32) srow[r] = 0u;
         }
-        for (int k0 = 0; k0 < n; k0 += 128) {  // four loads in flight per lane
-            int g[4];
+        // K1C_LOADS loads in flight per lane: with 32 warps per SM the bytes in flight decide the bandwidth
+        for (int k0 = 0; k0 < n; k0 += 32 * K1C_LOADS) {
+            int g[K1C_LOADS];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < K1C_LOADS; ++q) {
                 const int k = k0 + 32 * q + lane;
                 g[q] = k < n ? idx[lo + k] : -2;
             }
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < K1C_LOADS; ++q) {
                 const int k = k0 + 32 * q + lane;
                 // strictly increasing rows inside a column: compare with the left neighbour
                 int prev = __shfl_up_sync(0xffffffffu, g[q], 1);
@@ -175,7 +180,7 @@ __global__ void __launch_bounds__(1024) k1_scan_rows(const uint32_t* __restrict_
 // current one is applied (K1W_DEPTH in flight). Per gene the write cursor and the last up-to-4 values
 // are staged in shared memory, so that HBM sees whole 32-byte sectors.
 constexpr int K1W_WARPS = 4;
-constexpr int K1W_DEPTH = 8;
+constexpr int K1W_DEPTH = 8;  // (6, 12, 16 measured: 35.2, 39.9, 42.2 ms against 33.0 at config 3)
 
 __global__ void __launch_bounds__(K1W_WARPS * 32)
 k1_scatter_warp(const int64_t* __restrict__ p, const int32_t* __restrict__ idx, const double* __restrict__ x,
