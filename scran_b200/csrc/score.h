@@ -33,6 +33,7 @@ struct scranb200_plan {
     int K = 0;
     int64_t ndesired = 0;
     std::vector<int32_t> out_group, right_ptr, right_group, q_direct, q_flipped;
+    std::vector<int32_t> q_packed;  // q_direct, or -2 - q_flipped, or -1: one load per entry
     std::vector<double> right_weight;
 
     // self./other. averages (:395-411): avg[group] = sum_c proj[group][c] * y[c]; sparse rows.
@@ -46,7 +47,7 @@ struct scranb200_plan {
     int32_t *d_left = nullptr, *d_right = nullptr, *d_avg_ptr = nullptr, *d_avg_idx = nullptr, *d_out_group = nullptr,
             *d_right_ptr = nullptr, *d_q_direct = nullptr, *d_q_flipped = nullptr, *d_proj_ptr = nullptr,
             *d_proj_comb = nullptr, *d_other_ptr = nullptr, *d_other_group = nullptr, *d_need = nullptr,
-            *d_q_lgroup = nullptr, *d_q_rgroup = nullptr, *d_group_table = nullptr;
+            *d_q_lgroup = nullptr, *d_q_rgroup = nullptr, *d_group_table = nullptr, *d_q_packed = nullptr;
     double *d_ncells_comb = nullptr, *d_proj_coef = nullptr;
     std::vector<int32_t> q_need;       // bit 0: ranked as is (direct), bit 1: ranked reversed (flipped)
     std::vector<int32_t> group_table;  // group -> output table index or -1

@@ -319,6 +319,10 @@ void upload_plan(scranb200_ctx* ctx, scranb200_plan& P) {
         if (ints.size() & 1) ints.push_back(0);
         return at;
     };
+    P.q_packed.assign(P.q_direct.size(), -1);
+    for (size_t j = 0; j < P.q_direct.size(); ++j)
+        P.q_packed[j] = P.q_direct[j] >= 0 ? P.q_direct[j] : (P.q_flipped[j] >= 0 ? -2 - P.q_flipped[j] : -1);
+    const size_t o_packed = put(P.q_packed);
     const size_t o_left = put(P.left), o_right = put(P.right), o_avg_ptr = put(P.avg_ptr), o_avg_idx = put(P.avg_idx),
                  o_out_group = put(P.out_group), o_right_ptr = put(P.right_ptr), o_qd = put(P.q_direct),
                  o_qf = put(P.q_flipped), o_pp = put(P.proj_ptr), o_pc = put(P.proj_comb), o_op = put(P.other_ptr),
@@ -337,6 +341,7 @@ void upload_plan(scranb200_ctx* ctx, scranb200_plan& P) {
     P.d_right_ptr = b + o_right_ptr;
     P.d_q_direct = b + o_qd;
     P.d_q_flipped = b + o_qf;
+    P.d_q_packed = b + o_packed;
     P.d_proj_ptr = b + o_pp;
     P.d_proj_comb = b + o_pc;
     P.d_other_ptr = b + o_op;

@@ -12,6 +12,8 @@
 //                values are REVERSE(x) = -x, or 1 - x for the AUC (R/scoreMarkers.R:373-377).
 #include <cfloat>
 
+#include <cstdlib>
+
 #include "score.h"
 #include "sort.cuh"
 
@@ -208,6 +210,224 @@ __global__ void __launch_bounds__(SUM_WARPS * 32, 4) k5_summaries(SumParams P) {
             base[P.ld] = mn;
             base[2 * P.ld] = cnt > 0 ? ((cnt & 1) ? v_lo : (v_lo + v_next) / 2.0) : nan;
             base[3 * P.ld] = mx;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// k5_summaries_gene: the same summaries for tables of 65 - 256 comparisons (hundreds of groups), one CTA per
+// (gene, effect). The warp-per-(gene tile, table) kernel above streams a table's comparison columns three to five
+// times, and with 200 tables of 199 comparisons the resident warps' columns (240 MB) no longer fit L2: every pass
+// came from HBM (79 GB of reads for 9.55 GB of effects at config 5). Here the gene's value in EVERY comparison
+// column is fetched once into shared memory (Q x 8 bytes: 159 KB at Q = 19,900; the 32-byte sectors are shared
+// with the CTAs of the three neighbouring genes through L2), and each warp then serves some of the tables from
+// there: a lane holds up to eight of the table's values in registers; sum (double-double), range and counts by
+// warp reductions; the median by the same histogram selection as above, with the 32 bins counted by
+// shared-memory atomics and the chosen bin (at most 32 values) ranked across the lanes.
+// ------------------------------------------------------------------------------------------
+constexpr int SG_WARPS = 16;
+constexpr int SG_VPL = 8;  // values per lane: tables of up to 256 comparisons
+
+struct SumGeneParams {
+    int ngenes, K, Q;
+    int64_t ld, row0;
+    const double* eff;  // [3][Q][ld]
+    const int32_t *right_ptr, *q_packed;
+    double* out;  // [K][19][ld]
+};
+
+__device__ __forceinline__ double warp_min_f64(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_max_f64(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__global__ void __launch_bounds__(SG_WARPS * 32) k5_summaries_gene(SumGeneParams P) {
+    extern __shared__ __align__(16) unsigned char sg_smem[];
+    double* vals = reinterpret_cast<double*>(sg_smem);                           // [Q]
+    double* slots = vals + ((P.Q + 1) & ~1);                                     // [SG_WARPS][32]
+    uint32_t* hist = reinterpret_cast<uint32_t*>(slots + SG_WARPS * 32);         // [SG_WARPS][32]
+    uint32_t* nslot = hist + SG_WARPS * 32;                                      // [SG_WARPS]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int e = (int)(blockIdx.x / (unsigned)P.ngenes), g = (int)(blockIdx.x % (unsigned)P.ngenes);
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    const double inf = __longlong_as_double(0x7ff0000000000000ll);
+    {
+        const double* col = P.eff + (size_t)e * P.Q * P.ld + P.row0 + g;
+#pragma unroll 8
+        for (int q = threadIdx.x; q < P.Q; q += SG_WARPS * 32) vals[q] = col[(size_t)q * P.ld];
+    }
+    __syncthreads();
+    double* myslots = slots + warp * 32;
+    uint32_t* myhist = hist + warp * 32;
+
+    for (int k = warp; k < P.K; k += SG_WARPS) {
+        const int j0 = P.right_ptr[k], nr = P.right_ptr[k + 1] - j0;
+        double x[SG_VPL];
+#pragma unroll
+        for (int u = 0; u < SG_VPL; ++u) {
+            const int j = lane + 32 * u;
+            x[u] = nan;
+            if (j < nr) {
+                const int pk = P.q_packed[j0 + j];  // >= 0: the comparison as it is; <= -2: comparison -2 - pk mirrored
+                if (pk >= 0) {
+                    x[u] = vals[pk];
+                } else if (pk <= -2) {
+                    const double y = vals[-2 - pk];
+                    x[u] = e == 1 ? 1.0 - y : -y;
+                }
+            }
+        }
+        // ---- sum, counts, range of the finite values ----
+        DD sum = {0.0, 0.0};
+        double fmn = inf, fmx = -inf;
+        int cnt = 0, n_ninf = 0, n_pinf = 0;
+#pragma unroll
+        for (int u = 0; u < SG_VPL; ++u) {
+            if (!isnan(x[u])) {
+                dd_add(sum, x[u]);
+                ++cnt;
+                if (isinf(x[u])) {
+                    if (x[u] < 0.0) ++n_ninf; else ++n_pinf;
+                } else {
+                    fmn = fmin(fmn, x[u]);
+                    fmx = fmax(fmx, x[u]);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double oh = __shfl_xor_sync(0xffffffffu, sum.hi, o), ol = __shfl_xor_sync(0xffffffffu, sum.lo, o);
+            dd_add(sum, oh);
+            sum.lo += ol;
+        }
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        n_ninf = __reduce_add_sync(0xffffffffu, n_ninf);
+        n_pinf = __reduce_add_sync(0xffffffffu, n_pinf);
+        fmn = warp_min_f64(fmn);
+        fmx = warp_max_f64(fmx);
+        const int n_fin = cnt - n_ninf - n_pinf;
+        const double mn = n_ninf > 0 ? -inf : (n_fin > 0 ? fmn : inf);
+        const double mx = n_pinf > 0 ? inf : (n_fin > 0 ? fmx : -inf);
+
+        // ---- the values at sorted positions r_lo = (cnt - 1) / 2 and r_lo + 1 (everything below is warp-uniform) ----
+        double v_lo = nan, v_next = nan;
+        const int r_lo = (cnt - 1) / 2;
+        bool searching = false;
+        int target = 0;
+        double lo = fmn, hi = fmx;
+        double above = n_pinf > 0 ? inf : nan;
+        if (cnt > 0) {
+            if (r_lo < n_ninf) {
+                v_lo = -inf;
+                v_next = r_lo + 1 < n_ninf ? -inf : (n_fin > 0 ? fmn : (n_pinf > 0 ? inf : nan));
+            } else if (r_lo >= n_ninf + n_fin) {
+                v_lo = inf;
+                v_next = inf;
+            } else {
+                searching = true;
+                target = r_lo - n_ninf;
+            }
+        }
+        int ncand = n_fin;
+        while (searching) {
+            if (lo == hi) {  // all candidates are one value
+                v_lo = lo;
+                v_next = target + 1 < ncand ? lo : above;
+                break;
+            }
+            const double sc = 1.0 / 32.0;
+            const double width = (hi * sc - lo * sc) * sc;
+            const double inv = width > 0.0 ? 1.0 / width : 0.0;
+            const bool by_inv = inv < inf;
+            auto bin_of = [&](double v) {
+                const double t = v * sc - lo * sc;
+                return min(31, (int)(by_inv ? t * inv : t / width));
+            };
+            myhist[lane] = 0;
+            __syncwarp();
+            int bin[SG_VPL];
+#pragma unroll
+            for (int u = 0; u < SG_VPL; ++u) {
+                bin[u] = -1;
+                if (!isnan(x[u]) && x[u] >= lo && x[u] <= hi) {
+                    bin[u] = bin_of(x[u]);
+                    atomicAdd(&myhist[bin[u]], 1u);
+                }
+            }
+            __syncwarp();
+            const int c_lane = (int)myhist[lane];
+            int incl = c_lane;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += y;
+            }
+            const int bstar = __ffs(__ballot_sync(0xffffffffu, target < incl)) - 1;  // the first bin that reaches the rank
+            const int c = __shfl_sync(0xffffffffu, c_lane, bstar);
+            const int before = __shfl_sync(0xffffffffu, incl - c_lane, bstar);
+            // the smallest candidate above the bin
+            double up = inf;
+            bool any_up = false;
+#pragma unroll
+            for (int u = 0; u < SG_VPL; ++u) {
+                if (bin[u] > bstar) {
+                    up = fmin(up, x[u]);
+                    any_up = true;
+                }
+            }
+            up = warp_min_f64(up);
+            const double up_total = __any_sync(0xffffffffu, any_up) ? up : above;
+            if (c <= 32) {  // rank the bin's values across the lanes
+                if (lane == 0) nslot[warp] = 0;
+                __syncwarp();
+#pragma unroll
+                for (int u = 0; u < SG_VPL; ++u)
+                    if (bin[u] == bstar) myslots[atomicAdd(&nslot[warp], 1u)] = x[u];
+                __syncwarp();
+                const double xi = lane < c ? myslots[lane] : inf;
+                int rank = 0;
+                for (int j = 0; j < c; ++j) {
+                    const double xj = __shfl_sync(0xffffffffu, xi, j);
+                    rank += (xj < xi || (xj == xi && j < lane)) ? 1 : 0;
+                }
+                const int idx = target - before;
+                const int src_lo = __ffs(__ballot_sync(0xffffffffu, lane < c && rank == idx)) - 1;
+                v_lo = __shfl_sync(0xffffffffu, xi, src_lo);
+                if (idx + 1 < c) {
+                    const int src_next = __ffs(__ballot_sync(0xffffffffu, lane < c && rank == idx + 1)) - 1;
+                    v_next = __shfl_sync(0xffffffffu, xi, src_next);
+                } else {
+                    v_next = up_total;
+                }
+                __syncwarp();
+                break;
+            }
+            double bmin = inf, bmax = -inf;
+#pragma unroll
+            for (int u = 0; u < SG_VPL; ++u) {
+                if (bin[u] == bstar) {
+                    bmin = fmin(bmin, x[u]);
+                    bmax = fmax(bmax, x[u]);
+                }
+            }
+            lo = warp_min_f64(bmin);
+            hi = warp_max_f64(bmax);
+            target -= before;
+            ncand = c;
+            above = up_total;
+        }
+        if (lane < 4) {
+            const double total = sum.hi + sum.lo;
+            const double mean = cnt > 0 ? total / (double)cnt : nan;
+            const double med = cnt > 0 ? ((cnt & 1) ? v_lo : (v_lo + v_next) / 2.0) : nan;
+            const double w = lane == 0 ? mean : lane == 1 ? mn : lane == 2 ? med : mx;
+            P.out[((size_t)k * SCRANB200_NCOLS + 4 + 5 * e + lane) * P.ld + P.row0 + g] = w;
         }
     }
 }
@@ -768,6 +988,29 @@ void run_summaries(scranb200_ctx* ctx, const scranb200_plan& P, int ngenes, int6
     sp.q_direct = P.d_q_direct;
     sp.q_flipped = P.d_q_flipped;
     sp.out = d_out;
+    // tables of 65 - 256 comparisons: one CTA per (gene, effect) with the gene's Q values in shared memory
+    // (SCRANB200_SUMMARIES=gene / tile forces one or the other kernel: the tests run both on the same inputs)
+    {
+        const size_t smem = (size_t)((P.Q + 1) & ~1) * 8 + (size_t)SG_WARPS * 32 * 8 + (size_t)SG_WARPS * 32 * 4 + (size_t)SG_WARPS * 4 + 16;
+        const char* force = std::getenv("SCRANB200_SUMMARIES");
+        const bool can = maxr <= 32 * SG_VPL && smem <= ctx->smem_optin && (int64_t)3 * ngenes < 2147483647ll;
+        const bool want = force && force[0] == 'g' ? true : force && force[0] == 't' ? false : maxr > 64;
+        if (can && want) {
+            SumGeneParams gp;
+            gp.ngenes = ngenes;
+            gp.K = P.K;
+            gp.Q = P.Q;
+            gp.ld = ld;
+            gp.row0 = row0;
+            gp.eff = d_eff;
+            gp.right_ptr = P.d_right_ptr;
+            gp.q_packed = P.d_q_packed;
+            gp.out = d_out;
+            allow_smem(k5_summaries_gene, smem);
+            SB_LAUNCH(ctx, k5_summaries_gene, (unsigned)(3 * ngenes), SG_WARPS * 32, smem, gp);
+            return;
+        }
+    }
     const int64_t items = ceil_div(ngenes, 32) * P.K;
     const size_t slots = sizeof(double) * SUM_WARPS * SUM_SLOTS * 32;
     if (maxr > 64 && maxr <= 255) {

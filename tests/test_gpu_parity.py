@@ -461,6 +461,51 @@ def test_score_markers_one_cell_groups(sb):
     assert_tables_match(got, want)
 
 
+@pytest.mark.parametrize("case", ["one_cell", "seventy", "blocked_missing", "two_hundred"])
+def test_score_markers_both_summary_kernels(sb, case, monkeypatch):
+    """The summaries have two kernels (a warp per gene tile and table; a CTA per gene with all its comparison
+    values in shared memory, taken for tables of 65 - 256 comparisons). Both are run on the same inputs - NA
+    effects, infinite effects, heavy ties, even and odd counts - and must agree with each other (order
+    statistics exactly, means to the last bits) and with the oracle."""
+    rng = np.random.default_rng(31)
+    kw = {}
+    if case == "one_cell":
+        x = make_matrix(100, 90, seed=108)
+        groups = np.arange(90) % 3
+        groups[0] = 3
+    elif case == "seventy":
+        x = make_matrix(60, 2100, seed=108, rate=0.8)
+        x[3] = 0.0
+        groups = np.random.default_rng(7).integers(0, 70, 2100)
+        groups[groups == 69] = 68
+        groups[0] = 69
+    elif case == "blocked_missing":
+        x = make_matrix(80, 600, seed=109)
+        x[5] = 1.0                     # zero variance everywhere: infinite or undefined Cohen's d
+        groups = rng.integers(0, 6, 600)
+        kw["block"] = rng.integers(0, 3, 600)
+        groups[kw["block"] == 2] = np.minimum(groups[kw["block"] == 2], 3)  # groups 4, 5 are absent from batch 2
+    else:
+        x = make_matrix(24, 3000, seed=110, rate=0.6)
+        x[2] = 0.0
+        groups = rng.integers(0, 200, 3000)   # 199 comparisons per table
+    res = {}
+    for mode in ("tile", "gene"):
+        monkeypatch.setenv("SCRANB200_SUMMARIES", mode)
+        res[mode] = sb.score_markers(as_csc(x), groups, **kw)
+    monkeypatch.delenv("SCRANB200_SUMMARIES")
+    for g in res["tile"]:
+        for c in res["tile"][g]:
+            a, b = np.asarray(res["tile"][g][c], np.float64), np.asarray(res["gene"][g][c], np.float64)
+            if c.startswith("mean."):
+                assert np.allclose(a, b, rtol=1e-14, atol=0.0, equal_nan=True), (g, c)
+            else:
+                assert np.array_equal(a, b, equal_nan=True), (g, c)
+    from oracle import native, rlevel
+    want = rlevel.score_markers(as_csc(x), groups, lib=native.load("best"), **kw)
+    assert_tables_match(res["gene"], want)
+
+
 # ---------------------------------------------------------------------------------------------
 # pairwiseWilcox / pairwiseTTests (tests/testthat/test-pairwise-wilcox.R, test-pairwise-t.R): device
 # U / tie term / means / variances under the host p-value layer, against the oracle's restatement
