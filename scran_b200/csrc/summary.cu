@@ -225,7 +225,10 @@ __global__ void __launch_bounds__(SUM_WARPS * 32, 4) k5_summaries(SumParams P) {
 // warp reductions; the median by the same histogram selection as above, with the 32 bins counted by
 // shared-memory atomics and the chosen bin (at most 32 values) ranked across the lanes.
 // ------------------------------------------------------------------------------------------
-constexpr int SG_WARPS = 16;
+#ifndef SB_SG_WARPS
+#define SB_SG_WARPS 32
+#endif
+constexpr int SG_WARPS = SB_SG_WARPS;
 constexpr int SG_VPL = 8;  // values per lane: tables of up to 256 comparisons
 
 struct SumGeneParams {
@@ -257,6 +260,19 @@ __global__ void __launch_bounds__(SG_WARPS * 32) k5_summaries_gene(SumGeneParams
     const int e = (int)(blockIdx.x / (unsigned)P.ngenes), g = (int)(blockIdx.x % (unsigned)P.ngenes);
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
     const double inf = __longlong_as_double(0x7ff0000000000000ll);
+    // the comparison indices of a warp's next table are requested before the current table is worked on
+    int pk_next[SG_VPL];
+    auto fetch_indices = [&](int k) {
+#pragma unroll
+        for (int u = 0; u < SG_VPL; ++u) pk_next[u] = -1;
+        if (k < P.K) {
+            const int j0 = P.right_ptr[k], nr = P.right_ptr[k + 1] - j0;
+#pragma unroll
+            for (int u = 0; u < SG_VPL; ++u)
+                if (lane + 32 * u < nr) pk_next[u] = P.q_packed[j0 + lane + 32 * u];
+        }
+    };
+    fetch_indices(warp);
     {
         const double* col = P.eff + (size_t)e * P.Q * P.ld + P.row0 + g;
 #pragma unroll 8
@@ -267,14 +283,16 @@ __global__ void __launch_bounds__(SG_WARPS * 32) k5_summaries_gene(SumGeneParams
     uint32_t* myhist = hist + warp * 32;
 
     for (int k = warp; k < P.K; k += SG_WARPS) {
-        const int j0 = P.right_ptr[k], nr = P.right_ptr[k + 1] - j0;
         double x[SG_VPL];
+        int pks[SG_VPL];
+#pragma unroll
+        for (int u = 0; u < SG_VPL; ++u) pks[u] = pk_next[u];
+        fetch_indices(k + SG_WARPS);
 #pragma unroll
         for (int u = 0; u < SG_VPL; ++u) {
-            const int j = lane + 32 * u;
             x[u] = nan;
-            if (j < nr) {
-                const int pk = P.q_packed[j0 + j];  // >= 0: the comparison as it is; <= -2: comparison -2 - pk mirrored
+            {
+                const int pk = pks[u];  // >= 0: the comparison as it is; <= -2: comparison -2 - pk mirrored; -1: none
                 if (pk >= 0) {
                     x[u] = vals[pk];
                 } else if (pk <= -2) {
