@@ -628,20 +628,36 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
             const double v = col[i];
             return flip ? 1.0 - v : v;
         };
+        // f(i, value) for every row of the column, four loads in flight per thread (every pass below is a
+        // handful of dependent round trips to L2 per thread otherwise: 20 rows a thread at 20,000 genes)
+        auto for_each_row = [&](auto&& f) {
+            for (int i0 = tid; i0 < n; i0 += 4 * (int)blockDim.x) {
+                double v[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int i = i0 + q * (int)blockDim.x;
+                    v[q] = i < n ? col[i] : 0.0;
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int i = i0 + q * (int)blockDim.x;
+                    if (i < n) f(i, flip ? 1.0 - v[q] : v[q]);
+                }
+            }
+        };
         __syncthreads();
         // ---- valid count and finite range ----
         {
             double lo = inf, hi = -inf;
             uint32_t nans = 0;
-            for (int i = tid; i < n; i += blockDim.x) {
-                const double v = value(i);
+            for_each_row([&](int, double v) {
                 if (isnan(v)) {
                     ++nans;
                 } else if (!isinf(v)) {
                     lo = fmin(lo, v);
                     hi = fmax(hi, v);
                 }
-            }
+            });
             for (int o = 16; o > 0; o >>= 1) {
                 lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
                 hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
@@ -677,13 +693,12 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
         const uint32_t nv = (uint32_t)n - misc[0];
         if (nv == 0) continue;
         // ---- coarse counts -> offsets ----
-        for (int i = tid; i < n; i += blockDim.x) {
-            const double v = value(i);
+        for_each_row([&](int, double v) {
             if (!isnan(v)) {  // the same expression as rb_fine
                 const double xx = (value_of(key_of(v)) - fmin_v) * scale;
                 atomicAdd(&coff[min(__double2uint_rz(xx), (uint32_t)RB_COARSE - 1u)], 1u);
             }
-        }
+        });
         __syncthreads();
         if (warp == 0) {  // exclusive scan of RB_COARSE counts: 32 per lane
             uint32_t c[RB_COARSE / 32], sum = 0;
@@ -708,13 +723,12 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
         }
         __syncthreads();
         // ---- fine counts -> start offsets (in place), large buckets noted ----
-        for (int i = tid; i < n; i += blockDim.x) {
-            const double v = value(i);
+        for_each_row([&](int, double v) {
             if (!isnan(v)) {
                 const uint32_t b = rb_fine(key_of(v), coff, fmin_v, scale);
                 atomicAdd(&bk[b >> 1], 1u << ((b & 1u) * 16u));
             }
-        }
+        });
         __syncthreads();
         {
             const uint32_t per = (nv + blockDim.x - 1) / blockDim.x;
@@ -824,9 +838,8 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
                 continue;
             }
             // scatter the window's keys into bucket order: afterwards bh[b] is the END of bucket b
-            for (int i = tid; i < n; i += blockDim.x) {
-                const double v = value(i);
-                if (isnan(v)) continue;
+            for_each_row([&](int, double v) {
+                if (isnan(v)) return;
                 const uint64_t key = key_of(v);
                 const uint32_t b = rb_fine(key, coff, fmin_v, scale);
                 if (b >= b0 && b < b1) {
@@ -834,7 +847,7 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
                     const uint32_t pos = (atomicAdd(&bk[b >> 1], 1u << sh) >> sh) & 0xffffu;
                     skeys[pos - wstart] = key;
                 }
-            }
+            });
             __syncthreads();
             // large buckets of the window: one warp each; left alone if all keys are equal, else sorted
             for (uint32_t w = warp; w < nbig; w += nwarps) {
@@ -849,12 +862,11 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
                 if (!__all_sync(0xffffffffu, same)) rb_warp_sort(k, sz, lane);
             }
             __syncthreads();
-            for (int i = tid; i < n; i += blockDim.x) {
-                const double v = value(i);
-                if (isnan(v)) continue;
+            for_each_row([&](int i, double v) {
+                if (isnan(v)) return;
                 const uint64_t key = key_of(v);
                 const uint32_t b = rb_fine(key, coff, fmin_v, scale);
-                if (b < b0 || b >= b1) continue;
+                if (b < b0 || b >= b1) return;
                 const uint32_t start = b ? (uint32_t)bh[b - 1] : 0u, end = bh[b];
                 const uint64_t* k = skeys + (start - wstart);
                 const uint32_t sz = end - start;
@@ -881,7 +893,7 @@ __global__ void __launch_bounds__(1024) k5_rank_buckets(RankRunParams P) {
                 }
                 if (tg >= 0) atomicMin(&P.minrank[(size_t)tg * n + i], (int)(1u + (nv - end) + greater));
                 if (tl >= 0) atomicMin(&P.minrank[(size_t)tl * n + i], (int)(1u + start + less));
-            }
+            });
             b0 = b1;
         }
     }
